@@ -1,0 +1,170 @@
+/* lora_phy_cuda.h -- C ABI of the B200 (sm_100a) batched LoRa PHY.
+ *
+ * This is the drop-in boundary for the reference's PHY hot path.  The reference has no
+ * FFI of its own: its boundary is the C++ free-function API in
+ * include/lora_phy/phy.hpp.  Each entry point below names the reference interface it
+ * replaces (file:line relative to the reference tree); include/lora_phy/phy.hpp in THIS
+ * repository re-implements those C++ signatures as thin inline wrappers over this ABI.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no CUDA or torch types in any signature
+ *     (`stream` is a cudaStream_t passed as void*, NULL = the context's own stream);
+ *   - `d_` pointers are DEVICE pointers, `h_` pointers are HOST pointers;
+ *   - IQ is interleaved float32 I,Q (std::complex<float> layout), packets are rows of a
+ *     [n_packets][packet_stride] array, a packet holds whole symbols of (1<<sf)*osr samples;
+ *   - every function returns 0 / a count on success or a NEGATIVE errno, exactly like the
+ *     reference (phy.hpp:100-141): -EINVAL bad argument, -ERANGE capacity / <2 symbols /
+ *     missing scratch, -ENOMEM missing buffer, plus -EIO for a CUDA failure
+ *     (text via lora_phy_cuda_last_error);
+ *   - there is NO CPU fallback: without a CUDA device create() fails with -ENODEV.
+ */
+#ifndef LORA_PHY_CUDA_H
+#define LORA_PHY_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LORA_PHY_CUDA_ABI_VERSION 1
+
+typedef struct lora_phy_cuda_ctx lora_phy_cuda_ctx;
+
+/* lora_params (phy.hpp:53-60) + the call-site choices the reference makes per function. */
+typedef struct lora_phy_cuda_cfg {
+    uint32_t sf;        /* spreading factor 2..12 (N = 1<<sf); phy.hpp:54 */
+    uint32_t bw_hz;     /* 125000 / 250000 / 500000; phy.hpp:40-44 */
+    uint32_t osr;       /* oversampling ratio >= 1; phy.hpp:57 */
+    uint32_t window;    /* 0 = none, 1 = Hann; phy.hpp:31-34 */
+    uint32_t flags;     /* LORA_PHY_CUDA_F_* */
+    uint32_t sync_word; /* modulator only; phy.hpp:59 */
+    float    amplitude; /* modulator only; clamped to [-1,1] like LoRaMod.cpp:18 */
+    uint32_t reserved;
+} lora_phy_cuda_cfg;
+
+/* demodulate_batch flags */
+#define LORA_PHY_CUDA_F_DECHIRP     0x1u /* high-level demodulate(): multiply by the on-chip conjugate
+                                            downchirp first and estimate offsets on the raw symbols
+                                            without index tie-break (phy.cpp:182-243, :116) */
+#define LORA_PHY_CUDA_F_NO_SCRATCH  0x2u /* model a lora_demod_workspace without scratch: packets whose
+                                            max |I|,|Q| exceeds 1 get status -ERANGE (LoRaDemod.cpp:70-72) */
+
+/* ---- context -------------------------------------------------------------------------- */
+/* replaces lora_demod_init / init (LoRaDemod.cpp:11-33, phy.cpp:27-52): builds, ON THE DEVICE,
+ * the kissfft twiddle tables, Hann windows and downchirp tables for SF 2..12.            */
+int  lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device);
+void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx);              /* lora_demod_free, LoRaDemod.cpp:35 */
+const char* lora_phy_cuda_last_error(const lora_phy_cuda_ctx* ctx);
+int  lora_phy_cuda_abi_version(void);
+int  lora_phy_cuda_device(const lora_phy_cuda_ctx* ctx);
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+uint64_t lora_phy_cuda_launch_count(const lora_phy_cuda_ctx* ctx);
+/* Make every later call of this context enqueue on `stream` (cudaStream_t as void*). */
+int  lora_phy_cuda_set_stream(lora_phy_cuda_ctx* ctx, void* stream);
+int  lora_phy_cuda_synchronize(lora_phy_cuda_ctx* ctx);
+
+/* ---- demodulator: K1 + K2a ------------------------------------------------------------- */
+/* replaces lora_demodulate (LoRaDemod.cpp:50-197) -- and, with F_DECHIRP, demodulate
+ * (phy.cpp:182-243) -- for n_packets independent packets.
+ *   d_iq            [n_packets][packet_stride] complex64
+ *   d_sample_counts NULL (every packet has samples_per_packet samples) or [n_packets] ragged lengths
+ *                   (<= samples_per_packet); a trailing partial symbol is ignored (LoRaDemod.cpp:57)
+ *   d_symbols       [n_packets][symbol_stride] uint16: the data symbols (sync symbols stripped when
+ *                   the packet has >= 2 symbols, LoRaDemod.cpp:166-175)
+ *   d_sync          [n_packets] recovered sync word (LoRaDemod.cpp:178-193), may be NULL
+ *   d_cfo, d_time_offset  [n_packets] lora_metrics (phy.hpp:67-71), may be NULL
+ *   d_status        [n_packets] symbols written, or -ERANGE, may be NULL
+ * Asynchronous on the context's stream.                                                     */
+int lora_phy_cuda_demodulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                   const void* d_iq, size_t packet_stride,
+                                   const uint32_t* d_sample_counts, size_t samples_per_packet,
+                                   size_t n_packets,
+                                   uint16_t* d_symbols, size_t symbol_stride,
+                                   uint8_t* d_sync, float* d_cfo, float* d_time_offset,
+                                   int32_t* d_status);
+
+/* Same call with HOST buffers: stages through pinned memory and device scratch owned by the
+ * context, copies results back and synchronises.  This is what the C++ wrappers use.       */
+int lora_phy_cuda_demodulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                        const void* h_iq, size_t packet_stride,
+                                        const uint32_t* h_sample_counts, size_t samples_per_packet,
+                                        size_t n_packets,
+                                        uint16_t* h_symbols, size_t symbol_stride,
+                                        uint8_t* h_sync, float* h_cfo, float* h_time_offset,
+                                        int32_t* h_status);
+
+/* replaces estimate_offsets (phy.cpp:81-148): every whole symbol of each packet contributes.
+ * Outputs [n_packets] cfo / time_offset; packets with no whole symbol leave them untouched. */
+int lora_phy_cuda_estimate_offsets_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                         const void* d_iq, size_t packet_stride,
+                                         const uint32_t* d_sample_counts, size_t samples_per_packet,
+                                         size_t n_packets, float* d_cfo, float* d_time_offset);
+
+/* replaces compensate_offsets (phy.cpp:150-180), in place, per packet. */
+int lora_phy_cuda_compensate_offsets_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                           void* d_iq, size_t packet_stride,
+                                           size_t samples_per_packet, size_t n_packets,
+                                           const float* d_cfo, const float* d_time_offset);
+
+/* One N-point window per row through the detector (LoRaDetector.hpp:39-74): spectrum (may be
+ * NULL), first-max index, power, powerAvg and fIndex.  Used by the parity tests.           */
+int lora_phy_cuda_detect_batch(lora_phy_cuda_ctx* ctx, uint32_t sf, const void* d_windows,
+                               size_t n_windows, void* d_spectrum, uint32_t* d_index,
+                               float* d_power, float* d_power_avg, float* d_findex);
+
+/* ---- modulator: K3 ---------------------------------------------------------------------- */
+/* replaces lora_modulate / modulate (LoRaMod.cpp:8-43, phy.cpp:68-79).
+ *   d_symbols [n_packets][symbol_stride] uint16, symbols_per_packet used from each row
+ *   d_iq      [n_packets][packet_stride] complex64, (symbols_per_packet+2)*N*osr samples written
+ * Returns samples per packet, or -ERANGE if packet_stride is too small (checked BEFORE launch,
+ * unlike phy.cpp:74-77 which reports it after writing).                                      */
+long lora_phy_cuda_modulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                  const uint16_t* d_symbols, size_t symbol_stride,
+                                  size_t symbols_per_packet, size_t n_packets,
+                                  void* d_iq, size_t packet_stride);
+long lora_phy_cuda_modulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                       const uint16_t* h_symbols, size_t symbol_stride,
+                                       size_t symbols_per_packet, size_t n_packets,
+                                       void* h_iq, size_t packet_stride);
+
+/* Multiply every symbol window by the conjugate downchirp of (sf, osr, bw) in place: the
+ * caller-side dechirp every reference test performs before lora_demodulate
+ * (tests/e2e_chain_test.cpp:83-92, tests/performance_test.cpp:117-122).                      */
+int lora_phy_cuda_dechirp_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                void* d_iq, size_t packet_stride, size_t samples_per_packet,
+                                size_t n_packets);
+
+/* ---- bit pipeline: K4 (shipped coder) ----------------------------------------------------- */
+/* replaces lora_encode / encode (LoRaEncoder.cpp:6-18, phy.cpp:58-66): 2 symbols per byte.   */
+long lora_phy_cuda_encode_batch(lora_phy_cuda_ctx* ctx, const uint8_t* d_payload,
+                                size_t payload_stride, size_t payload_len, size_t n_packets,
+                                uint16_t* d_symbols, size_t symbol_stride);
+/* replaces lora_decode / decode (LoRaDecoder.cpp:7-21, phy.cpp:245-261): returns bytes per
+ * packet or -EINVAL for an odd symbol count; d_crc_ok[n_packets] (may be NULL) gets the
+ * phy.cpp:252-259 check (bytes [2,n-2) vs little-endian CRC in the last two bytes).
+ * d_symbol_counts NULL or [n_packets] int32 (e.g. the status array of demodulate_batch;
+ * negative or odd counts yield 0 bytes and crc_ok = 0).                                       */
+long lora_phy_cuda_decode_batch(lora_phy_cuda_ctx* ctx, const uint16_t* d_symbols,
+                                size_t symbol_stride, const int32_t* d_symbol_counts,
+                                size_t symbols_per_packet, size_t n_packets,
+                                uint8_t* d_payload, size_t payload_stride, uint8_t* d_crc_ok);
+long lora_phy_cuda_encode_batch_host(lora_phy_cuda_ctx* ctx, const uint8_t* h_payload,
+                                     size_t payload_stride, size_t payload_len, size_t n_packets,
+                                     uint16_t* h_symbols, size_t symbol_stride);
+long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_symbols,
+                                     size_t symbol_stride, const int32_t* h_symbol_counts,
+                                     size_t symbols_per_packet, size_t n_packets,
+                                     uint8_t* h_payload, size_t payload_stride, uint8_t* h_crc_ok);
+
+/* ---- tables (parity tests read these back) -------------------------------------------------- */
+/* which: 0 = kissfft twiddles (kissfft.hh:24-29), 1 = Hann window (LoRaDemod.cpp:18-24),
+ * 2 = downchirp for cfg bw (phy.cpp:205-208).  Copies N entries to host memory.                */
+int lora_phy_cuda_copy_table(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t bw_hz, int which,
+                             void* h_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LORA_PHY_CUDA_H */

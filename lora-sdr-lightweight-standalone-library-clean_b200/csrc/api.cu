@@ -1,0 +1,554 @@
+// api.cu -- the C ABI of include/lora_phy_cuda.h: context, plan tables, argument checks with
+// the reference's errno contract, launches, and the host-buffer staging variants.
+#include "../../include/lora_phy_cuda.h"
+#include "demod_device.cuh"
+#include "internal.h"
+
+#include <cerrno>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+#include <string>
+#include <tuple>
+
+using lk::cf;
+
+namespace {
+
+struct SfTables { cf* tw = nullptr; cf* ct = nullptr; float* hann = nullptr; };
+
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct PinBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+} // namespace
+
+struct lora_phy_cuda_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    uint64_t launches = 0;
+    SfTables tab[13];
+    std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
+    DevBuf state, phases, tmp;                          // PacketState[], modulator phases, compensate scratch
+    DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
+    PinBuf h_in, h_out;
+    std::mutex mu;
+};
+
+namespace {
+
+int fail(lora_phy_cuda_ctx* c, int code, const char* what, cudaError_t e = cudaSuccess)
+{
+    if (c) {
+        c->err = what;
+        if (e != cudaSuccess) { c->err += ": "; c->err += cudaGetErrorString(e); }
+    }
+    return code;
+}
+
+#define CK(call)                                                                  \
+    do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, -EIO, #call, e_); } while (0)
+
+bool bw_ok(uint32_t hz) { return hz == 125000u || hz == 250000u || hz == 500000u; }
+
+int check_cfg(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg)
+{
+    if (!ctx) return -EINVAL;
+    if (!cfg) return fail(ctx, -EINVAL, "cfg is NULL");
+    if (cfg->sf < 2 || cfg->sf > 12) return fail(ctx, -EINVAL, "sf out of range 2..12");
+    if (cfg->osr < 1 || cfg->osr > 64) return fail(ctx, -EINVAL, "osr out of range 1..64");
+    if (!bw_ok(cfg->bw_hz)) return fail(ctx, -EINVAL, "bw_hz must be 125000, 250000 or 500000");
+    if (cfg->window > 1) return fail(ctx, -EINVAL, "window must be 0 (none) or 1 (Hann)");
+    return 0;
+}
+
+int get_chirp(lora_phy_cuda_ctx* ctx, int sf, int bw_hz, int osr, cf** out)
+{
+    auto key = std::make_tuple(sf, bw_hz, osr);
+    auto it = ctx->chirps.find(key);
+    if (it != ctx->chirps.end()) { *out = it->second; return 0; }
+    cf* p = nullptr;
+    CK(cudaMalloc(&p, sizeof(cf) * ((size_t)1 << sf) * osr));
+    CK(lk::launch_build_chirp(sf, osr, (float)bw_hz / 125000.0f, p, ctx->stream));
+    ++ctx->launches;
+    ctx->chirps[key] = p;
+    *out = p;
+    return 0;
+}
+
+struct Guard {
+    int prev = -1;
+    explicit Guard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~Guard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+} // namespace
+
+extern "C" {
+
+int lora_phy_cuda_abi_version(void) { return LORA_PHY_CUDA_ABI_VERSION; }
+
+int lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device)
+{
+    if (!out) return -EINVAL;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return -ENODEV;
+    lora_phy_cuda_ctx* ctx = new (std::nothrow) lora_phy_cuda_ctx;
+    if (!ctx) return -ENOMEM;
+    ctx->device = device;
+    Guard g(device);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return -ENODEV; }
+    if (prop.major < 10) { delete ctx; return -ENODEV; }     // sm_100a code only: no other architecture, no fallback
+    ctx->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return -EIO; }
+    ctx->own_stream = true;
+    for (int sf = 2; sf <= 12; ++sf) {
+        const size_t N = (size_t)1 << sf;
+        SfTables& t = ctx->tab[sf];
+        const int cs = lk::compact_size_of(sf);
+        if (cudaMalloc(&t.tw, N * sizeof(cf)) != cudaSuccess || cudaMalloc(&t.ct, (size_t)cs * sizeof(cf)) != cudaSuccess ||
+            cudaMalloc(&t.hann, N * sizeof(float)) != cudaSuccess ||
+            lk::launch_build_tables(sf, t.tw, t.ct, cs, t.hann, ctx->stream) != cudaSuccess) {
+            lora_phy_cuda_destroy(ctx);
+            return -EIO;
+        }
+        ctx->launches += 2;
+    }
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { lora_phy_cuda_destroy(ctx); return -EIO; }
+    *out = ctx;
+    return 0;
+}
+
+void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
+{
+    if (!ctx) return;
+    Guard g(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (int sf = 2; sf <= 12; ++sf) {
+        if (ctx->tab[sf].tw) cudaFree(ctx->tab[sf].tw);
+        if (ctx->tab[sf].ct) cudaFree(ctx->tab[sf].ct);
+        if (ctx->tab[sf].hann) cudaFree(ctx->tab[sf].hann);
+    }
+    for (auto& kv : ctx->chirps) cudaFree(kv.second);
+    ctx->state.release(); ctx->phases.release(); ctx->tmp.release();
+    ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
+    ctx->h_in.release(); ctx->h_out.release();
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* lora_phy_cuda_last_error(const lora_phy_cuda_ctx* ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+int lora_phy_cuda_device(const lora_phy_cuda_ctx* ctx) { return ctx ? ctx->device : -1; }
+uint64_t lora_phy_cuda_launch_count(const lora_phy_cuda_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int lora_phy_cuda_set_stream(lora_phy_cuda_ctx* ctx, void* stream)
+{
+    if (!ctx) return -EINVAL;
+    Guard g(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    ctx->stream = static_cast<cudaStream_t>(stream);
+    ctx->own_stream = false;
+    return 0;
+}
+
+int lora_phy_cuda_synchronize(lora_phy_cuda_ctx* ctx)
+{
+    if (!ctx) return -EINVAL;
+    Guard g(ctx->device);
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, int mode, const void* d_iq,
+                        size_t packet_stride, const uint32_t* d_counts, size_t spp, size_t n_packets,
+                        uint16_t* d_symbols, size_t symbol_stride, uint8_t* d_sync, float* d_cfo,
+                        float* d_to, int32_t* d_status)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if (!d_iq && n_packets && spp) return fail(ctx, -EINVAL, "d_iq is NULL");
+    if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
+    if (spp > 0xffffffffull || n_packets > 0xffffffffull) return fail(ctx, -EINVAL, "batch too large");
+    const size_t N = (size_t)1 << cfg->sf, step = N * cfg->osr;
+    const size_t total_max = spp / step;
+    uint32_t dsm = 0, est_uniform = 2;
+    if (mode == lk::MODE_EST_ONLY) {
+        est_uniform = (uint32_t)total_max;
+    } else {
+        if (!d_symbols && total_max) return fail(ctx, -EINVAL, "d_symbols is NULL");
+        if (mode == lk::MODE_HIGHLEVEL && !d_counts) {           // phy.cpp:190-194
+            if (spp % step != 0) return fail(ctx, -EINVAL, "sample count is not a multiple of (1<<sf)*osr");
+            if (total_max < 2) return fail(ctx, -ERANGE, "fewer than two symbols");
+        }
+        dsm = total_max >= 2 ? (uint32_t)(total_max - 2) : (uint32_t)total_max;
+        if (d_counts && total_max >= 2 && dsm == 0) dsm = 1;     // a ragged 1-symbol packet still emits one
+        if (dsm > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than the data symbols per packet");
+    }
+    if (n_packets == 0) return 0;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CK(ctx->state.reserve(n_packets * sizeof(lk::PacketState)));
+
+    lk::DemodArgs a;
+    a.iq = static_cast<const cf*>(d_iq);
+    a.packet_stride = packet_stride;
+    a.sample_counts = d_counts;
+    a.samples_per_packet = (uint32_t)spp;
+    a.n_packets = (uint32_t)n_packets;
+    a.osr = cfg->osr;
+    a.mode = mode;
+    a.no_scratch = (cfg->flags & LORA_PHY_CUDA_F_NO_SCRATCH) ? 1 : 0;
+    a.est_uniform = est_uniform;
+    a.data_symbols_max = dsm;
+    a.window = cfg->window ? ctx->tab[cfg->sf].hann : nullptr;
+    a.down = nullptr;
+    if (mode == lk::MODE_HIGHLEVEL) {
+        cf* d = nullptr;
+        rc = get_chirp(ctx, (int)cfg->sf, (int)cfg->bw_hz, 1, &d);   // phy.cpp:205-208: osr = 1 table
+        if (rc) return rc;
+        a.down = d;
+    }
+    a.tw = ctx->tab[cfg->sf].tw;
+    a.ct = ctx->tab[cfg->sf].ct;
+    a.power_scale = lk::power_scale_of((int)cfg->sf);
+    a.state = static_cast<lk::PacketState*>(ctx->state.p);
+    a.symbols = d_symbols;
+    a.symbol_stride = symbol_stride;
+    a.sync = d_sync;
+    a.cfo = d_cfo;
+    a.time_offset = d_to;
+    a.status = d_status;
+    unsigned launches = 0;
+    cudaError_t e = lk::launch_demod((int)cfg->sf, a, ctx->sm_count, ctx->stream, true, mode != lk::MODE_EST_ONLY, &launches);
+    ctx->launches += launches;
+    if (e != cudaSuccess) return fail(ctx, -EIO, "demodulator launch", e);
+    return 0;
+}
+
+int lora_phy_cuda_demodulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const void* d_iq,
+                                   size_t packet_stride, const uint32_t* d_sample_counts,
+                                   size_t samples_per_packet, size_t n_packets, uint16_t* d_symbols,
+                                   size_t symbol_stride, uint8_t* d_sync, float* d_cfo, float* d_time_offset,
+                                   int32_t* d_status)
+{
+    const int mode = (cfg && (cfg->flags & LORA_PHY_CUDA_F_DECHIRP)) ? lk::MODE_HIGHLEVEL : lk::MODE_LEGACY;
+    return demod_common(ctx, cfg, mode, d_iq, packet_stride, d_sample_counts, samples_per_packet, n_packets,
+                        d_symbols, symbol_stride, d_sync, d_cfo, d_time_offset, d_status);
+}
+
+int lora_phy_cuda_estimate_offsets_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const void* d_iq,
+                                         size_t packet_stride, const uint32_t* d_sample_counts,
+                                         size_t samples_per_packet, size_t n_packets, float* d_cfo,
+                                         float* d_time_offset)
+{
+    return demod_common(ctx, cfg, lk::MODE_EST_ONLY, d_iq, packet_stride, d_sample_counts, samples_per_packet,
+                        n_packets, nullptr, 0, nullptr, d_cfo, d_time_offset, nullptr);
+}
+
+int lora_phy_cuda_demodulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const void* h_iq,
+                                        size_t packet_stride, const uint32_t* h_counts, size_t spp,
+                                        size_t n_packets, uint16_t* h_symbols, size_t symbol_stride,
+                                        uint8_t* h_sync, float* h_cfo, float* h_to, int32_t* h_status)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if ((!h_iq && n_packets && spp) || (!h_symbols && n_packets && symbol_stride)) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
+    if (n_packets == 0) return demod_common(ctx, cfg, (cfg->flags & LORA_PHY_CUDA_F_DECHIRP) ? lk::MODE_HIGHLEVEL : lk::MODE_LEGACY,
+                                            h_iq, packet_stride, nullptr, spp, 0, h_symbols, symbol_stride, nullptr, nullptr, nullptr, nullptr);
+    Guard g(ctx->device);
+    const size_t iq_bytes = n_packets * packet_stride * sizeof(cf);
+    const size_t sym_bytes = n_packets * symbol_stride * sizeof(uint16_t);
+    // device scratch layout (d_out): symbols | cfo | time_offset | status | sync
+    const size_t off_cfo = (sym_bytes + 15) & ~(size_t)15;
+    const size_t off_to = off_cfo + n_packets * 4, off_st = off_to + n_packets * 4, off_sync = off_st + n_packets * 4;
+    const size_t out_bytes = off_sync + n_packets;
+    CK(ctx->d_in.reserve(iq_bytes + 16));
+    CK(ctx->d_out.reserve(out_bytes));
+    CK(ctx->h_out.reserve(out_bytes));
+    uint32_t* d_counts = nullptr;
+    if (h_counts) {
+        CK(ctx->d_aux.reserve(n_packets * 4));
+        d_counts = static_cast<uint32_t*>(ctx->d_aux.p);
+        CK(cudaMemcpyAsync(d_counts, h_counts, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CK(cudaMemcpyAsync(ctx->d_in.p, h_iq, iq_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_out.p, 0, out_bytes, ctx->stream));
+    unsigned char* o = static_cast<unsigned char*>(ctx->d_out.p);
+    rc = lora_phy_cuda_demodulate_batch(ctx, cfg, ctx->d_in.p, packet_stride, d_counts, spp, n_packets,
+                                        reinterpret_cast<uint16_t*>(o), symbol_stride, o + off_sync,
+                                        reinterpret_cast<float*>(o + off_cfo), reinterpret_cast<float*>(o + off_to),
+                                        reinterpret_cast<int32_t*>(o + off_st));
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const unsigned char* h = static_cast<const unsigned char*>(ctx->h_out.p);
+    const int32_t* st = reinterpret_cast<const int32_t*>(h + off_st);
+    for (size_t p = 0; p < n_packets; ++p) {           // only the symbols the reference would have written
+        const int32_t cnt = st[p];
+        if (cnt > 0) memcpy(h_symbols + p * symbol_stride, h + p * symbol_stride * 2, (size_t)cnt * 2);
+    }
+    if (h_cfo) memcpy(h_cfo, h + off_cfo, n_packets * 4);
+    if (h_to) memcpy(h_to, h + off_to, n_packets * 4);
+    if (h_status) memcpy(h_status, h + off_st, n_packets * 4);
+    if (h_sync) memcpy(h_sync, h + off_sync, n_packets);
+    return 0;
+}
+
+int lora_phy_cuda_compensate_offsets_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, void* d_iq,
+                                           size_t packet_stride, size_t spp, size_t n_packets,
+                                           const float* d_cfo, const float* d_to)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if (!d_iq || !d_cfo || !d_to) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
+    if (!n_packets || !spp) return 0;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    const size_t bytes = n_packets * packet_stride * sizeof(cf);
+    CK(ctx->tmp.reserve(bytes));
+    CK(lk::launch_compensate(static_cast<const cf*>(d_iq), static_cast<cf*>(ctx->tmp.p), packet_stride, (uint32_t)spp,
+                             (uint32_t)n_packets, (int)cfg->sf, cfg->osr, d_cfo, d_to, ctx->stream));
+    ++ctx->launches;
+    CK(cudaMemcpy2DAsync(d_iq, packet_stride * sizeof(cf), ctx->tmp.p, packet_stride * sizeof(cf), spp * sizeof(cf),
+                         n_packets, cudaMemcpyDeviceToDevice, ctx->stream));
+    return 0;
+}
+
+int lora_phy_cuda_detect_batch(lora_phy_cuda_ctx* ctx, uint32_t sf, const void* d_windows, size_t n_windows,
+                               void* d_spectrum, uint32_t* d_index, float* d_power, float* d_power_avg,
+                               float* d_findex)
+{
+    if (!ctx) return -EINVAL;
+    if (sf < 2 || sf > 12) return fail(ctx, -EINVAL, "sf out of range 2..12");
+    if (!d_windows && n_windows) return fail(ctx, -EINVAL, "d_windows is NULL");
+    if (!n_windows) return 0;
+    Guard g(ctx->device);
+    lk::DetectArgs a;
+    a.windows = static_cast<const cf*>(d_windows);
+    a.n_windows = (uint32_t)n_windows;
+    a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
+    a.spectrum = static_cast<cf*>(d_spectrum); a.index = d_index; a.power = d_power;
+    a.power_avg = d_power_avg; a.findex = d_findex;
+    CK(lk::launch_detect((int)sf, a, ctx->sm_count, ctx->stream));
+    ++ctx->launches;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+long lora_phy_cuda_modulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const uint16_t* d_symbols,
+                                  size_t symbol_stride, size_t spp_sym, size_t n_packets, void* d_iq,
+                                  size_t packet_stride)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if ((!d_symbols && spp_sym && n_packets) || (!d_iq && n_packets)) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spp_sym > symbol_stride && n_packets > 1) return fail(ctx, -EINVAL, "symbols_per_packet exceeds symbol_stride");
+    const size_t produced = (spp_sym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
+    if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
+    if (!n_packets) return (long)produced;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CK(ctx->phases.reserve(n_packets * (spp_sym + 2) * sizeof(float)));
+    lk::ModArgs a;
+    a.symbols = d_symbols; a.symbol_stride = symbol_stride; a.symbols_per_packet = (uint32_t)spp_sym;
+    a.n_packets = (uint32_t)n_packets; a.iq = static_cast<cf*>(d_iq); a.packet_stride = packet_stride;
+    a.sf = (int)cfg->sf; a.osr = cfg->osr; a.bw_scale = (float)cfg->bw_hz / 125000.0f;
+    a.amplitude = cfg->amplitude; a.sync = cfg->sync_word & 0xff;
+    a.phase_scratch = static_cast<float*>(ctx->phases.p);
+    unsigned launches = 0;
+    cudaError_t e = lk::launch_modulate(a, ctx->sm_count, ctx->stream, &launches);
+    ctx->launches += launches;
+    if (e != cudaSuccess) return fail(ctx, -EIO, "modulator launch", e);
+    return (long)produced;
+}
+
+long lora_phy_cuda_modulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const uint16_t* h_symbols,
+                                       size_t symbol_stride, size_t spp_sym, size_t n_packets, void* h_iq,
+                                       size_t packet_stride)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if ((!h_symbols && spp_sym && n_packets) || (!h_iq && n_packets)) return fail(ctx, -EINVAL, "NULL buffer");
+    const size_t produced = (spp_sym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
+    if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
+    if (!n_packets) return (long)produced;
+    Guard g(ctx->device);
+    const size_t sym_bytes = (n_packets * symbol_stride + 1) * 2, iq_bytes = n_packets * packet_stride * sizeof(cf);
+    CK(ctx->d_in.reserve(sym_bytes));
+    CK(ctx->d_out.reserve(iq_bytes));
+    if (spp_sym) CK(cudaMemcpyAsync(ctx->d_in.p, h_symbols, ((n_packets - 1) * symbol_stride + spp_sym) * 2, cudaMemcpyHostToDevice, ctx->stream));
+    long r = lora_phy_cuda_modulate_batch(ctx, cfg, static_cast<const uint16_t*>(ctx->d_in.p), symbol_stride, spp_sym,
+                                          n_packets, ctx->d_out.p, packet_stride);
+    if (r < 0) return r;
+    CK(cudaMemcpy2DAsync(h_iq, packet_stride * sizeof(cf), ctx->d_out.p, packet_stride * sizeof(cf), produced * sizeof(cf),
+                         n_packets, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return r;
+}
+
+int lora_phy_cuda_dechirp_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, void* d_iq, size_t packet_stride,
+                                size_t spp, size_t n_packets)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if (!d_iq && n_packets && spp) return fail(ctx, -EINVAL, "d_iq is NULL");
+    if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
+    if (!n_packets || !spp) return 0;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    cf* table = nullptr;
+    rc = get_chirp(ctx, (int)cfg->sf, (int)cfg->bw_hz, (int)cfg->osr, &table);
+    if (rc) return rc;
+    CK(lk::launch_dechirp(static_cast<cf*>(d_iq), packet_stride, (uint32_t)spp, (uint32_t)n_packets, table,
+                          (uint32_t)(((size_t)1 << cfg->sf) * cfg->osr), ctx->stream));
+    ++ctx->launches;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+long lora_phy_cuda_encode_batch(lora_phy_cuda_ctx* ctx, const uint8_t* d_payload, size_t payload_stride,
+                                size_t payload_len, size_t n_packets, uint16_t* d_symbols, size_t symbol_stride)
+{
+    if (!ctx) return -EINVAL;
+    if ((!d_payload || !d_symbols) && n_packets && payload_len) return fail(ctx, -EINVAL, "NULL buffer");
+    if (payload_len > payload_stride && n_packets > 1) return fail(ctx, -EINVAL, "payload_len exceeds payload_stride");
+    if (2 * payload_len > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than 2*payload_len");
+    Guard g(ctx->device);
+    CK(lk::launch_encode(d_payload, payload_stride, (uint32_t)payload_len, (uint32_t)n_packets, d_symbols, symbol_stride, ctx->stream));
+    if (n_packets && payload_len) ++ctx->launches;
+    return (long)(2 * payload_len);
+}
+
+long lora_phy_cuda_decode_batch(lora_phy_cuda_ctx* ctx, const uint16_t* d_symbols, size_t symbol_stride,
+                                const int32_t* d_counts, size_t spp, size_t n_packets, uint8_t* d_payload,
+                                size_t payload_stride, uint8_t* d_crc_ok)
+{
+    if (!ctx) return -EINVAL;
+    if ((!d_symbols || !d_payload) && n_packets && spp) return fail(ctx, -EINVAL, "NULL buffer");
+    if (!d_counts && (spp & 1)) return fail(ctx, -EINVAL, "odd symbol count");      // LoRaDecoder.cpp:10
+    if (spp / 2 > payload_stride) return fail(ctx, -ERANGE, "payload_stride smaller than symbols/2");
+    Guard g(ctx->device);
+    CK(lk::launch_decode(d_symbols, symbol_stride, d_counts, (uint32_t)spp, (uint32_t)n_packets, d_payload, payload_stride, d_crc_ok, ctx->stream));
+    if (n_packets) ctx->launches += (spp / 2 ? 1 : 0) + (d_crc_ok ? 1 : 0);
+    return (long)(spp / 2);
+}
+
+long lora_phy_cuda_encode_batch_host(lora_phy_cuda_ctx* ctx, const uint8_t* h_payload, size_t payload_stride,
+                                     size_t payload_len, size_t n_packets, uint16_t* h_symbols, size_t symbol_stride)
+{
+    if (!ctx) return -EINVAL;
+    if ((!h_payload || !h_symbols) && n_packets && payload_len) return fail(ctx, -EINVAL, "NULL buffer");
+    if (2 * payload_len > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than 2*payload_len");
+    if (!n_packets || !payload_len) return (long)(2 * payload_len);
+    Guard g(ctx->device);
+    const size_t in_bytes = (n_packets - 1) * payload_stride + payload_len, out_bytes = n_packets * symbol_stride * 2;
+    CK(ctx->d_in.reserve(in_bytes));
+    CK(ctx->d_out.reserve(out_bytes));
+    CK(cudaMemcpyAsync(ctx->d_in.p, h_payload, in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    long r = lora_phy_cuda_encode_batch(ctx, static_cast<const uint8_t*>(ctx->d_in.p), payload_stride, payload_len, n_packets,
+                                        static_cast<uint16_t*>(ctx->d_out.p), symbol_stride);
+    if (r < 0) return r;
+    CK(cudaMemcpy2DAsync(h_symbols, symbol_stride * 2, ctx->d_out.p, symbol_stride * 2, 2 * payload_len * 2, n_packets,
+                         cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return r;
+}
+
+long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_symbols, size_t symbol_stride,
+                                     const int32_t* h_counts, size_t spp, size_t n_packets, uint8_t* h_payload,
+                                     size_t payload_stride, uint8_t* h_crc_ok)
+{
+    if (!ctx) return -EINVAL;
+    if ((!h_symbols || !h_payload) && n_packets && spp) return fail(ctx, -EINVAL, "NULL buffer");
+    if (!h_counts && (spp & 1)) return fail(ctx, -EINVAL, "odd symbol count");
+    if (spp / 2 > payload_stride) return fail(ctx, -ERANGE, "payload_stride smaller than symbols/2");
+    if (!n_packets) return (long)(spp / 2);
+    Guard g(ctx->device);
+    const size_t in_bytes = ((n_packets - 1) * symbol_stride + spp) * 2;
+    const size_t pay_bytes = n_packets * payload_stride;
+    CK(ctx->d_in.reserve(in_bytes + 16));
+    CK(ctx->d_out.reserve(pay_bytes + n_packets + 16));
+    CK(ctx->d_aux.reserve(n_packets * 4));
+    if (in_bytes) CK(cudaMemcpyAsync(ctx->d_in.p, h_symbols, in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    int32_t* d_counts = nullptr;
+    if (h_counts) {
+        d_counts = static_cast<int32_t*>(ctx->d_aux.p);
+        CK(cudaMemcpyAsync(d_counts, h_counts, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    uint8_t* d_pay = static_cast<uint8_t*>(ctx->d_out.p);
+    uint8_t* d_crc = d_pay + pay_bytes;
+    CK(cudaMemsetAsync(d_pay, 0, pay_bytes + n_packets, ctx->stream));
+    long r = lora_phy_cuda_decode_batch(ctx, static_cast<const uint16_t*>(ctx->d_in.p), symbol_stride, d_counts, spp,
+                                        n_packets, d_pay, payload_stride, d_crc);
+    if (r < 0) return r;
+    CK(ctx->h_out.reserve(pay_bytes + n_packets));
+    CK(cudaMemcpyAsync(ctx->h_out.p, d_pay, pay_bytes + n_packets, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const uint8_t* h = static_cast<const uint8_t*>(ctx->h_out.p);
+    for (size_t p = 0; p < n_packets; ++p) {
+        int32_t cnt = h_counts ? h_counts[p] : (int32_t)spp;
+        size_t nb = (cnt < 0 || (cnt & 1)) ? 0 : (size_t)cnt / 2;
+        if (nb > spp / 2) nb = spp / 2;
+        memcpy(h_payload + p * payload_stride, h + p * payload_stride, nb);
+    }
+    if (h_crc_ok) memcpy(h_crc_ok, h + pay_bytes, n_packets);
+    return r;
+}
+
+int lora_phy_cuda_copy_table(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t bw_hz, int which, void* h_out)
+{
+    if (!ctx || !h_out) return -EINVAL;
+    if (sf < 2 || sf > 12) return fail(ctx, -EINVAL, "sf out of range 2..12");
+    Guard g(ctx->device);
+    const size_t N = (size_t)1 << sf;
+    if (which == 0) { CK(cudaMemcpyAsync(h_out, ctx->tab[sf].tw, N * sizeof(cf), cudaMemcpyDeviceToHost, ctx->stream)); }
+    else if (which == 1) { CK(cudaMemcpyAsync(h_out, ctx->tab[sf].hann, N * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream)); }
+    else if (which == 2) {
+        if (!bw_ok(bw_hz)) return fail(ctx, -EINVAL, "bad bw_hz");
+        cf* t = nullptr;
+        int rc = get_chirp(ctx, (int)sf, (int)bw_hz, 1, &t);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h_out, t, N * sizeof(cf), cudaMemcpyDeviceToHost, ctx->stream));
+    } else return fail(ctx, -EINVAL, "unknown table");
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,363 @@
+// glibc_math.cuh -- device restatements of the glibc 2.39 libm entry points the
+// reference's hot path resolves to (SURVEY.md section 1, L0 "Below" column):
+//
+//   std::cos/std::sin(float)  -> cosf / sinf     (LoRaDemod.cpp:156-157, phy.cpp:221-222,
+//                                                 ChirpGenerator.hpp:39,47 via std::polar,
+//                                                 kissfft.hh:28 via cexpf)
+//   std::abs(complex<float>)  -> hypotf          (LoRaDetector.hpp:66-67)
+//   std::arg(complex<float>)  -> atan2f          (LoRaDemod.cpp:115, phy.cpp:125)
+//   std::log10(float)         -> log10f          (LoRaDetector.hpp:63-64)
+//
+// Why restate instead of calling CUDA's libdevice: the reference rotates every sample
+// by (cosf(ph), sinf(ph)) before the FFT and takes argmax of |X|^2 with a strict
+// first-max tie-break.  Demodulated symbols are required to be bit-exact, so the
+// rotated samples must be the same floats the reference produces.  glibc's sinf/cosf
+// evaluate fixed double-precision polynomials (error 0.56 ulp, NOT correctly rounded),
+// so only the same polynomial reproduces them; CUDA's sinf (<= 2 ulp) does not.  B200
+// executes FP64 at half the FP32 rate, which makes the double-precision evaluation
+// affordable per sample ("K1 instruction budget").
+//
+// Everything is __host__ __device__ so tests/cpu/test_glibc_math.cpp can compare each
+// function with the real glibc over hundreds of millions of arguments on the CPU.
+// Compile with -fmad=false (nvcc) / -ffp-contract=off (g++): float-path functions
+// (atanf, atan2f, log10f) rely on one rounding per operation.
+#pragma once
+
+#include <stdint.h>
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define GM_HD __host__ __device__ __forceinline__
+#else
+#define GM_HD static inline
+#endif
+
+namespace gm {
+
+GM_HD uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    union { float f; uint32_t u; } v; v.f = f; return v.u;
+#endif
+}
+GM_HD float u2f(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    union { float f; uint32_t u; } v; v.u = u; return v.f;
+#endif
+}
+GM_HD double ll2d_bits(uint64_t u) {
+#if defined(__CUDA_ARCH__)
+    return __longlong_as_double((long long)u);
+#else
+    union { double d; uint64_t u; } v; v.u = u; return v.d;
+#endif
+}
+
+// ------------------------------------------------------------------------------------
+// sinf / cosf : glibc sysdeps/ieee754/flt-32/{s_sinf.c,s_cosf.c,sincosf.h}
+// ------------------------------------------------------------------------------------
+struct SinCosPoly { double c0, c1, c2, c3, c4, s1, s2, s3; };
+
+GM_HD double sc_hpi_inv() { return 0x1.45F306DC9C883p+23; }   // 2/pi * 2^24
+GM_HD double sc_hpi()     { return 0x1.921FB54442D18p0; }      // pi/2
+
+// polynomial pair; neg_cos selects __sincosf_table[1] (cosine coefficients negated)
+GM_HD double sc_sin_poly(double x, double x2)
+{
+    const double s1 = -0x1.555545995a603p-3, s2 = 0x1.1107605230bc4p-7, s3 = -0x1.994eb3774cf24p-13;
+    double x3 = x * x2;
+    double t1 = s2 + x2 * s3;
+    double x7 = x3 * x2;
+    double s = x + x3 * s1;
+    return s + x7 * t1;
+}
+GM_HD double sc_cos_poly(double x2, bool neg)
+{
+    double c0 = 0x1p0, c1 = -0x1.ffffffd0c621cp-2, c2 = 0x1.55553e1068f19p-5,
+           c3 = -0x1.6c087e89a359dp-10, c4 = 0x1.99343027bf8c3p-16;
+    if (neg) { c0 = -c0; c1 = -c1; c2 = -c2; c3 = -c3; c4 = -c4; }
+    double x4 = x2 * x2;
+    double t2 = c3 + x2 * c4;
+    double t1 = c0 + x2 * c1;
+    double x6 = x4 * x2;
+    double c = t1 + x4 * c2;
+    return c + x6 * t2;
+}
+
+// sinf_poly(x, x2, p, n): odd n -> cosine polynomial
+GM_HD float sc_eval(double x, double x2, bool neg, int n)
+{
+    return (n & 1) ? (float)sc_cos_poly(x2, neg) : (float)sc_sin_poly(x, x2);
+}
+
+GM_HD uint32_t sc_inv_pio4(int i)
+{
+    // __inv_pio4[]: consecutive 32-bit windows (8-bit steps) of 4/pi's binary expansion
+    const uint32_t t[24] = {
+        0xa2u, 0xa2f9u, 0xa2f983u, 0xa2f9836eu, 0xf9836e4eu, 0x836e4e44u, 0x6e4e4415u, 0x4e441529u,
+        0x441529fcu, 0x1529fc27u, 0x29fc2757u, 0xfc2757d1u, 0x2757d1f5u, 0x57d1f534u, 0xd1f534ddu,
+        0xf534ddc0u, 0x34ddc0dbu, 0xddc0db62u, 0xc0db6295u, 0xdb629599u, 0x6295993cu, 0x95993c43u,
+        0x993c4390u, 0x3c439041u };
+    return t[i];
+}
+
+GM_HD double sc_reduce_large(uint32_t xi, int* np)
+{
+    const int a = (xi >> 26) & 15;
+    const int shift = (xi >> 23) & 7;
+    uint64_t n, res0, res1, res2;
+    xi = (xi & 0xffffff) | 0x800000;
+    xi <<= shift;
+    res0 = (uint32_t)(xi * sc_inv_pio4(a));           // 32-bit product promoted, as in glibc
+    res1 = (uint64_t)xi * sc_inv_pio4(a + 4);
+    res2 = (uint64_t)xi * sc_inv_pio4(a + 8);
+    res0 = (res2 >> 32) | (res0 << 32);
+    res0 += res1;
+    n = (res0 + (1ULL << 61)) >> 62;
+    res0 -= n << 62;
+    double x = (double)(int64_t)res0;
+    *np = (int)n;
+    return x * 0x1.921FB54442D18p-62;                   // pi63
+}
+
+// Common reduction: returns reduced |.|<=pi/4 argument already multiplied by the
+// quadrant sign, its square, the table selector and quadrant n.
+// cls: 0 = tiny (|y| < 2^-12), 1 = |y| < pi/4, 2 = reduced, 3 = inf/nan
+struct SinCosArg { double xs, x2; int n; bool neg; int cls; };
+
+GM_HD SinCosArg sc_reduce(float y)
+{
+    SinCosArg r;
+    const uint32_t iy = f2u(y);
+    const uint32_t top = (iy >> 20) & 0x7ff;
+    double x = (double)y;
+    r.n = 0; r.neg = false;
+    if (top < ((0x3f490fdbu >> 20) & 0x7ff)) {               // |y| < pi/4 (abstop12 compare)
+        r.xs = x; r.x2 = x * x;
+        r.cls = (top < ((0x39800000u >> 20) & 0x7ff)) ? 0 : 1; // 2^-12
+        return r;
+    }
+    if (top < ((0x42f00000u >> 20) & 0x7ff)) {               // |y| < 120
+        double q = x * sc_hpi_inv();
+        int n = ((int32_t)q + 0x800000) >> 24;
+        x = x - (double)n * sc_hpi();
+        const double s = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+        r.neg = (n & 2) != 0;
+        r.xs = x * s; r.x2 = x * x; r.n = n; r.cls = 2;
+        return r;
+    }
+    if (top < ((0x7f800000u >> 20) & 0x7ff)) {
+        int n;
+        const int sign = (int)(iy >> 31);
+        x = sc_reduce_large(iy, &n);
+        const int q = (n + sign) & 3;
+        const double s = (q == 1 || q == 2) ? -1.0 : 1.0;
+        r.neg = ((n + sign) & 2) != 0;
+        r.xs = x * s; r.x2 = x * x; r.n = n; r.cls = 2;
+        return r;
+    }
+    r.xs = r.x2 = 0.0; r.cls = 3;
+    return r;
+}
+
+GM_HD float sinf_g(float y)
+{
+    SinCosArg a = sc_reduce(y);
+    if (a.cls == 0) return y;
+    if (a.cls == 3) return y - y;                 // NaN (and raises invalid in glibc)
+    return sc_eval(a.xs, a.x2, a.neg, a.n);
+}
+
+GM_HD float cosf_g(float y)
+{
+    SinCosArg a = sc_reduce(y);
+    if (a.cls == 0) return 1.0f;
+    if (a.cls == 3) return y - y;
+    if (a.cls == 1) return (float)sc_cos_poly(a.x2, false);
+    return sc_eval(a.xs, a.x2, a.neg, a.n ^ 1);
+}
+
+// (cosf(y), sinf(y)) with the argument reduction shared -- same results as the two
+// separate calls above (both polynomials are evaluated on the same reduced argument).
+GM_HD void sincosf_g(float y, float* sn, float* cs)
+{
+    SinCosArg a = sc_reduce(y);
+    if (a.cls == 0) { *sn = y; *cs = 1.0f; return; }
+    if (a.cls == 3) { *sn = *cs = y - y; return; }
+    const float ps = (float)sc_sin_poly(a.xs, a.x2);
+    const float pc = (float)sc_cos_poly(a.x2, a.neg);
+    if (a.n & 1) { *sn = pc; *cs = ps; } else { *sn = ps; *cs = pc; }
+}
+
+// ------------------------------------------------------------------------------------
+// hypotf : glibc sysdeps/ieee754/flt-32/e_hypotf.c (2.35+): double-precision sqrt
+// ------------------------------------------------------------------------------------
+GM_HD float hypotf_g(float x, float y)
+{
+    const uint32_t ax = f2u(x) & 0x7fffffffu, ay = f2u(y) & 0x7fffffffu;
+    if (ax == 0x7f800000u || ay == 0x7f800000u) return u2f(0x7f800000u);  // inf wins over NaN
+    if (ax > 0x7f800000u || ay > 0x7f800000u) return x + y;
+#if defined(__CUDA_ARCH__)
+    return (float)__dsqrt_rn((double)x * (double)x + (double)y * (double)y);
+#else
+    return (float)sqrt((double)x * (double)x + (double)y * (double)y);
+#endif
+}
+
+// ------------------------------------------------------------------------------------
+// atanf / atan2f : glibc sysdeps/ieee754/flt-32/{s_atanf.c,e_atan2f.c} (fdlibm, float ops)
+// ------------------------------------------------------------------------------------
+GM_HD float atanf_g(float x)
+{
+    const float hi[4] = { 4.6364760399e-01f, 7.8539812565e-01f, 9.8279368877e-01f, 1.5707962513e+00f };
+    const float lo[4] = { 5.0121582440e-09f, 3.7748947079e-08f, 3.4473217170e-08f, 7.5497894159e-08f };
+    const float aT[11] = { 3.3333334327e-01f, -2.0000000298e-01f, 1.4285714924e-01f, -1.1111110449e-01f,
+                           9.0908870101e-02f, -7.6918758452e-02f, 6.6610731184e-02f, -5.8335702866e-02f,
+                           4.9768779427e-02f, -3.6531571299e-02f, 1.6285819933e-02f };
+    const int32_t hx = (int32_t)f2u(x);
+    const int32_t ix = hx & 0x7fffffff;
+    int id;
+    if (ix >= 0x4c000000) {                    // |x| >= 2^25
+        if (ix > 0x7f800000) return x + x;
+        return hx > 0 ? hi[3] + lo[3] : -hi[3] - lo[3];
+    }
+    if (ix < 0x3ee00000) {                     // |x| < 0.4375
+        if (ix < 0x31000000) return x;         // |x| < 2^-29
+        id = -1;
+    } else {
+        x = fabsf(x);
+        if (ix < 0x3f980000) {
+            if (ix < 0x3f300000) { id = 0; x = (2.0f * x - 1.0f) / (2.0f + x); }
+            else                 { id = 1; x = (x - 1.0f) / (x + 1.0f); }
+        } else {
+            if (ix < 0x401c0000) { id = 2; x = (x - 1.5f) / (1.0f + 1.5f * x); }
+            else                 { id = 3; x = -1.0f / x; }
+        }
+    }
+    float z = x * x;
+    float w = z * z;
+    float s1 = z * (aT[0] + w * (aT[2] + w * (aT[4] + w * (aT[6] + w * (aT[8] + w * aT[10])))));
+    float s2 = w * (aT[1] + w * (aT[3] + w * (aT[5] + w * (aT[7] + w * aT[9]))));
+    if (id < 0) return x - x * (s1 + s2);
+    z = hi[id] - ((x * (s1 + s2) - lo[id]) - x);
+    return hx < 0 ? -z : z;
+}
+
+GM_HD float atan2f_g(float y, float x)
+{
+    const float tiny = 1.0e-30f, pi_o_4 = 7.8539818525e-01f, pi_o_2 = 1.5707963705e+00f,
+                pi = 3.1415927410e+00f, pi_lo = -8.7422776573e-08f;
+    const int32_t hx = (int32_t)f2u(x), hy = (int32_t)f2u(y);
+    const int32_t ix = hx & 0x7fffffff, iy = hy & 0x7fffffff;
+    if (ix > 0x7f800000 || iy > 0x7f800000) return x + y;
+    if (hx == 0x3f800000) return atanf_g(y);
+    const int m = ((hy >> 31) & 1) | ((hx >> 30) & 2);
+    if (iy == 0) {
+        switch (m) {
+        case 0: case 1: return y;
+        case 2: return pi + tiny;
+        default: return -pi - tiny;
+        }
+    }
+    if (ix == 0) return hy < 0 ? -pi_o_2 - tiny : pi_o_2 + tiny;
+    if (ix == 0x7f800000) {
+        if (iy == 0x7f800000) {
+            switch (m) {
+            case 0: return pi_o_4 + tiny;
+            case 1: return -pi_o_4 - tiny;
+            case 2: return 3.0f * pi_o_4 + tiny;
+            default: return -3.0f * pi_o_4 - tiny;
+            }
+        } else {
+            switch (m) {
+            case 0: return 0.0f;
+            case 1: return -0.0f;
+            case 2: return pi + tiny;
+            default: return -pi - tiny;
+            }
+        }
+    }
+    if (iy == 0x7f800000) return hy < 0 ? -pi_o_2 - tiny : pi_o_2 + tiny;
+    const int k = (iy - ix) >> 23;
+    float z;
+    if (k > 60) z = pi_o_2 + 0.5f * pi_lo;
+    else if (hx < 0 && k < -60) z = 0.0f;
+    else z = atanf_g(fabsf(y / x));
+    switch (m) {
+    case 0: return z;
+    case 1: return u2f(f2u(z) ^ 0x80000000u);
+    case 2: return pi - (z - pi_lo);
+    default: return (z - pi_lo) - pi;
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// logf / log10f : glibc sysdeps/ieee754/flt-32/{e_logf.c,e_log10f.c}
+// ------------------------------------------------------------------------------------
+GM_HD void logf_tab(int i, double* invc, double* logc)
+{
+    const double t[32] = {
+        0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2, 0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2,
+        0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2, 0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3,
+        0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3, 0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3,
+        0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4, 0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4,
+        0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5, 0x1p+0, 0x0p+0,
+        0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5, 0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4,
+        0x1.b2036576afce6p-1, 0x1.526e57720db08p-3, 0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3,
+        0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2, 0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2 };
+    *invc = t[2 * i]; *logc = t[2 * i + 1];
+}
+
+GM_HD float logf_g(float x)
+{
+    uint32_t ix = f2u(x);
+    if (ix == 0x3f800000u) return 0.0f;
+    if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
+        if (ix * 2 == 0) return -u2f(0x7f800000u);                     // log(+-0) = -inf
+        if (ix == 0x7f800000u) return x;
+        if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return (x - x) / (x - x); // NaN
+        ix = f2u(x * 0x1p23f);
+        ix -= 23u << 23;
+    }
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (int)((tmp >> 19) % 16);
+    const int k = (int32_t)tmp >> 23;
+    const uint32_t iz = ix - (tmp & (0x1ffu << 23));
+    double invc, logc;
+    logf_tab(i, &invc, &logc);
+    const double z = (double)u2f(iz);
+    const double r = z * invc - 1;
+    const double y0 = logc + (double)k * 0x1.62e42fefa39efp-1;
+    const double r2 = r * r;
+    double y = 0x1.5575b0be00b6ap-2 * r + -0x1.ffffef20a4123p-2;
+    y = -0x1.00ea348b88334p-2 * r2 + y;
+    y = y * r2 + (y0 + r);
+    return (float)y;
+}
+
+GM_HD float log10f_g(float x)
+{
+    const float two25 = 3.3554432000e+07f, ivln10 = 4.3429449201e-01f,
+                log10_2hi = 3.0102920532e-01f, log10_2lo = 7.9034151668e-07f;
+    int32_t hx = (int32_t)f2u(x);
+    int32_t k = 0;
+    if (hx < 0x00800000) {
+        if ((hx & 0x7fffffff) == 0) return -two25 / fabsf(x);   // -inf
+        if (hx < 0) return (x - x) / (x - x);                   // NaN
+        k -= 25; x *= two25;
+        hx = (int32_t)f2u(x);
+    }
+    if (hx >= 0x7f800000) return x + x;
+    k += (hx >> 23) - 127;
+    const int32_t i = (int32_t)(((uint32_t)k & 0x80000000u) >> 31);
+    hx = (hx & 0x007fffff) | ((0x7f - i) << 23);
+    const float y = (float)(k + i);
+    x = u2f((uint32_t)hx);
+    const float z = y * log10_2lo + ivln10 * logf_g(x);
+    return z + y * log10_2hi;
+}
+
+} // namespace gm

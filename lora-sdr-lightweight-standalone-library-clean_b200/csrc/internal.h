@@ -1,0 +1,56 @@
+// internal.h -- launcher prototypes shared by the .cu translation units (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "fft_exact.cuh"
+
+namespace lk {
+
+using fx::cf;
+struct DemodArgs;
+
+struct DetectArgs {
+    const cf* windows; uint32_t n_windows;
+    const cf* tw; const cf* ct; float power_scale;
+    cf* spectrum; uint32_t* index; float* power; float* power_avg; float* findex;
+};
+
+// float(20*log10(double(N))) for N = 1<<sf (LoRaDetector.hpp:29), bit patterns checked against
+// the oracle by tests/test_tables.py
+__host__ __device__ inline float power_scale_of(int sf)
+{
+    const uint32_t bits[13] = { 0x0u, 0x40c0a8c1u, 0x4140a8c1u, 0x41907e91u, 0x41c0a8c1u, 0x41f0d2f1u,
+                                0x42107e91u, 0x422893a9u, 0x4240a8c1u, 0x4258bdd9u, 0x4270d2f1u,
+                                0x42847405u, 0x42907e91u };
+    union { uint32_t u; float f; } v; v.u = bits[sf]; return v.f;
+}
+
+cudaError_t launch_demod(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream, bool prepass,
+                         bool symbols, unsigned* launches);
+cudaError_t launch_detect(int sf, const DetectArgs& a, int sm_count, cudaStream_t stream);
+
+// tables.cu
+cudaError_t launch_build_tables(int sf, cf* tw, cf* ct, int ct_size, float* hann, cudaStream_t stream);
+cudaError_t launch_build_chirp(int sf, int osr, float bw_scale, cf* out /* N*osr */, cudaStream_t stream);
+int compact_size_of(int sf);
+
+// modcodes.cu
+struct ModArgs {
+    const uint16_t* symbols; size_t symbol_stride; uint32_t symbols_per_packet; uint32_t n_packets;
+    cf* iq; size_t packet_stride; int sf; uint32_t osr; float bw_scale; float amplitude; uint32_t sync;
+    float* phase_scratch;   // [n_packets][symbols_per_packet + 2] start phase of every chirp
+};
+cudaError_t launch_modulate(const ModArgs& a, int sm_count, cudaStream_t stream, unsigned* launches);
+cudaError_t launch_dechirp(cf* iq, size_t packet_stride, uint32_t samples_per_packet, uint32_t n_packets,
+                           const cf* table, uint32_t table_len, cudaStream_t stream);
+cudaError_t launch_encode(const uint8_t* payload, size_t payload_stride, uint32_t payload_len, uint32_t n_packets,
+                          uint16_t* symbols, size_t symbol_stride, cudaStream_t stream);
+cudaError_t launch_decode(const uint16_t* symbols, size_t symbol_stride, const int32_t* counts,
+                          uint32_t symbols_per_packet, uint32_t n_packets, uint8_t* payload,
+                          size_t payload_stride, uint8_t* crc_ok, cudaStream_t stream);
+cudaError_t launch_compensate(const cf* in, cf* out, size_t packet_stride, uint32_t samples_per_packet,
+                              uint32_t n_packets, int sf, uint32_t osr, const float* cfo,
+                              const float* time_offset, cudaStream_t stream);
+
+} // namespace lk
