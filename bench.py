@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- demodulated symbols/s of the batched LoRa PHY hot path on B200 (driver contract).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload sf7|sf12] [--impl reference]
+
+A "step" is one pass of the demodulator (lora_phy_cuda_demodulate_batch: prepass + symbols
+kernels) over one batch of synthetic, clean, pre-dechirped IQ already resident in HBM.
+Workloads (BASELINE.json configs[1] / configs[2]):
+  sf7   SF7 BW125k, 32-byte payloads (66 symbols = 8448 samples = 67.6 KB per packet), 1 Mi packets
+  sf12  SF12 BW125k, 64-byte payloads (130 symbols = 4.26 MB per packet), 16 Ki packets resident
+Under torchrun every rank owns its own packet range (weak scaling, no collective on the data path).
+`--impl reference` times the reference's own CPU code (oracle/_ref, else the oracle port) on a
+bounded sample with all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    "sf7": dict(sf=7, payload=32, packets=1 << 20, name="SF7 BW125k, 1Mi packets x 32-byte payload, clean pre-dechirped IQ, demodulate-only"),
+    "sf12": dict(sf=12, payload=64, packets=1 << 14, name="SF12 BW125k, 16Ki-packet resident chunk x 64-byte payload (of the 64Ki batch), clean pre-dechirped IQ, demodulate-only"),
+}
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                for line in out.strip().splitlines():
+                    self.rows.append([c.strip() for c in line.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        sm = sorted(int(r[1]) for r in self.rows if len(r) > 8 and r[1].isdigit())
+        mx = [int(r[2]) for r in self.rows if len(r) > 8 and r[2].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) > 8 for n, v in zip(names, r[5:9]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_arm(wl, seconds_target=12.0):
+    """Reference CPU implementation (lora_demodulate, one packet per thread) on a bounded sample."""
+    import numpy as np
+    import cpu_libs
+    lib = cpu_libs.load_ref()
+    kind = "reference"
+    if lib is None:
+        lib, kind = cpu_libs.load_oracle(), "port"
+    oracle = cpu_libs.load_oracle()
+    sf, L = wl["sf"], wl["payload"]
+    N = 1 << sf
+    nsym = 2 * L + 2
+    cores = os.cpu_count() or 1
+    # ~38 Msamples/s/core measured in SURVEY section 6; size the sample for ~seconds_target of work
+    per_pkt = nsym * N
+    n_pkt = max(cores, int(seconds_target * 30e6 * cores / per_pkt))
+    n_pkt = min(n_pkt, max(cores, int(2e9 // (per_pkt * 8))))          # <= 2 GB of IQ
+    rng = np.random.default_rng(0x10AA51F7)
+    base = []
+    down = oracle.downchirp(sf)
+    for _ in range(min(n_pkt, 16)):                                       # 16 distinct packets, tiled
+        pay = rng.integers(0, 256, L, dtype=np.uint8)
+        iq = oracle.lora_modulate(oracle.lora_encode(pay), sf)
+        base.append((iq.reshape(-1, N) * down[None, :]).astype(np.complex64).ravel())
+    base = np.stack(base)
+    iq = np.ascontiguousarray(np.tile(base, ((n_pkt + len(base) - 1) // len(base), 1))[:n_pkt])
+    return lib, kind, cores, n_pkt, nsym, per_pkt, iq
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    lib, kind, cores, n_pkt, nsym, per_pkt, iq = cpu_arm(wl, seconds_target=max(2.0, 40.0 / max(args.steps + args.warmup, 1)))
+    secs = []
+    for i in range(args.warmup + args.steps):
+        s, _, _ = lib.demod_batch_mt(iq, n_pkt, per_pkt, wl["sf"], 1, 0, cores)
+        if i >= args.warmup:
+            secs.append(s)
+    t = sum(secs) / len(secs)
+    value = n_pkt * nsym / t
+    sample = f"{n_pkt} packets ({n_pkt * per_pkt * 8 / 1e6:.0f} MB IQ) per step, {cores} threads, one packet per thread"
+    print(json.dumps({
+        "impl": "reference", "metric": "demod symbols/s", "value": value, "unit": "symbols/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "msamples_per_s": n_pkt * per_pkt / t / 1e6,
+        "config": {"workload": wl["name"], "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "symbols/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "symbols/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ours(args, wl):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import lora_phy_b200 as lp
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    phy = lp.LoraPhyCuda(local_rank)
+
+    sf, L = wl["sf"], wl["payload"]
+    P = args.packets or wl["packets"]
+    N = 1 << sf
+    nsym = 2 * L + 2
+    spp = nsym * N
+    cfg = lp.make_cfg(sf)
+
+    # ---- synthetic batch, generated on the device by our own modulator (per-rank packet range) ----
+    g = torch.Generator(device="cpu").manual_seed(0x10AA51F7 + rank)
+    iq = torch.empty((P, spp), dtype=torch.complex64, device=dev)
+    chunk = max(1, min(P, (1 << 28) // spp))
+    payload_all = torch.randint(0, 256, (P, L), dtype=torch.uint8, generator=g)
+    for lo in range(0, P, chunk):
+        hi = min(P, lo + chunk)
+        sym = phy.encode_batch(payload_all[lo:hi].to(dev))
+        phy.modulate_batch(cfg, sym, iq[lo:hi])
+        phy.dechirp_batch(cfg, iq[lo:hi])
+    out = phy.alloc_demod_outputs(P, nsym - 2)
+    torch.cuda.synchronize()
+
+    cfg_pre = lp.make_cfg(sf, flags=lp.F_ONLY_PREPASS)
+    cfg_sym = lp.make_cfg(sf, flags=lp.F_ONLY_SYMBOLS)
+
+    def step(ev=None):
+        if ev is None:
+            phy.demodulate_batch(cfg, iq, out=out)
+        else:                                  # same two launches, with an event between them
+            phy.demodulate_batch(cfg_pre, iq, out=out)
+            ev[0].record()
+            phy.demodulate_batch(cfg_sym, iq, out=out)
+            ev[1].record()
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    # correctness guard: the batch must decode back to the payload it was made from
+    _, pay, _ = phy.decode_batch(out["symbols"])
+    assert torch.equal(pay.cpu(), payload_all), "bench batch did not demodulate to its payload"
+    assert bool((out["status"] == nsym - 2).all())
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    launches0 = phy.launch_count()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t0.record()
+    for i in range(args.steps):
+        step(evs[i])
+    t1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    launches = phy.launch_count() - launches0
+    sampler.stop_flag = True
+    sampler.join(timeout=3)
+    ms_total = t0.elapsed_time(t1)
+    if world > 1:
+        tt = torch.tensor([ms_total], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    sym_kernel_ms = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+
+    # ---- end-to-end through the host-buffer C-ABI call (pinned host IQ in, host symbols out) ----
+    Pe = min(P, args.e2e_packets)
+    h_iq = torch.empty((Pe, spp), dtype=torch.complex64).pin_memory()
+    h_iq.copy_(iq[:Pe])
+    h_iq_np = h_iq.numpy()
+    e2e_steps = max(2, min(args.steps, 5))
+    rc, o = phy.demodulate_batch_host(cfg, h_iq_np)      # warm-up (allocates staging)
+    assert rc == 0
+    if world > 1:
+        dist.barrier()
+    te = time.perf_counter()
+    for _ in range(e2e_steps):
+        rc, o = phy.demodulate_batch_host(cfg, h_iq_np)
+    te = (time.perf_counter() - te) / e2e_steps
+    assert rc == 0 and np.array_equal(o["symbols"], out["symbols"][:Pe].cpu().numpy())
+    if world > 1:
+        tt = torch.tensor([te], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        te = float(tt.item())
+    e2e_value = world * Pe * nsym / te
+    h2d = Pe * spp * 8
+    d2h = Pe * ((nsym - 2) * 2 + 4 + 4 + 4 + 1)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks, peak_kind = load_peaks()
+    peak = float(peaks["hbm_gbs"])
+    b_sym = 8 * N + 2                                   # algorithmic bytes per demodulated symbol
+    sym_bytes = P * (nsym - 2) * b_sym                  # symbols kernel: data symbols of every packet, once
+    achieved = sym_bytes / (sym_kernel_ms * 1e-3) / 1e9
+    step_bytes = P * nsym * b_sym
+    line = {
+        "metric": "demod symbols/s", "value": world * P * nsym / (ms_step * 1e-3), "unit": "symbols/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "msamples_per_s": world * P * spp / (ms_step * 1e-3) / 1e6,
+        "step_hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
+        "config": {"workload": wl["name"], "packets_per_gpu": P, "symbols_per_packet": nsym, "sf": sf,
+                   "l2_policy": "inputs larger than L2 (%.1f GB per GPU per step)" % (P * spp * 8 / 1e9)},
+        "roofline": {"bound": "hbm", "kernel": "symbols_kernel<SF%d>" % sf, "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                     "kernel_ms": sym_kernel_ms, "algorithmic_bytes_per_launch": sym_bytes},
+        "e2e": {"value": e2e_value, "unit": "symbols/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "packets_per_step": Pe},
+        "gpu_launches": launches,
+        "clocks": sampler.summary(),
+    }
+    if not args.no_cpu and world == 1:
+        lib, kind, cores, n_pkt, nsym_c, per_pkt, ciq = cpu_arm(wl)
+        s, _, _ = lib.demod_batch_mt(ciq, n_pkt, per_pkt, sf, 1, 0, cores)
+        line["cpu_baseline"] = {"value": n_pkt * nsym_c / s, "unit": "symbols/s", "cores": cores, "kind": kind,
+                                "sample": f"{n_pkt} packets ({n_pkt * per_pkt * 8 / 1e6:.0f} MB IQ), one packet per thread, {s:.1f} s"}
+    else:
+        line["cpu_baseline"] = None
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="sf7", choices=sorted(WORKLOADS))
+    ap.add_argument("--packets", type=int, default=0, help="packets per GPU (default: the workload's)")
+    ap.add_argument("--e2e-packets", type=int, default=1 << 15)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

@@ -51,6 +51,12 @@ typedef struct lora_phy_cuda_cfg {
 #define LORA_PHY_CUDA_F_NO_SCRATCH  0x2u /* model a lora_demod_workspace without scratch: packets whose
                                             max |I|,|Q| exceeds 1 get status -ERANGE (LoRaDemod.cpp:70-72) */
 
+/* Split one demodulate_batch call into its two launches (bench.py times the kernels separately
+ * with CUDA events; a normal call sets neither):                                            */
+#define LORA_PHY_CUDA_F_ONLY_PREPASS 0x10u /* run only the per-packet prepass (max-abs, estimator, sync) */
+#define LORA_PHY_CUDA_F_ONLY_SYMBOLS 0x20u /* run only the data-symbol kernel, reusing the packet state
+                                              the previous prepass of the same batch left in the context */
+
 /* ---- context -------------------------------------------------------------------------- */
 /* replaces lora_demod_init / init (LoRaDemod.cpp:11-33, phy.cpp:27-52): builds, ON THE DEVICE,
  * the kissfft twiddle tables, Hann windows and downchirp tables for SF 2..12.            */

@@ -254,7 +254,9 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.time_offset = d_to;
     a.status = d_status;
     unsigned launches = 0;
-    cudaError_t e = lk::launch_demod((int)cfg->sf, a, ctx->sm_count, ctx->stream, true, mode != lk::MODE_EST_ONLY, &launches);
+    const bool do_pre = !(cfg->flags & LORA_PHY_CUDA_F_ONLY_SYMBOLS);
+    const bool do_sym = mode != lk::MODE_EST_ONLY && !(cfg->flags & LORA_PHY_CUDA_F_ONLY_PREPASS);
+    cudaError_t e = lk::launch_demod((int)cfg->sf, a, ctx->sm_count, ctx->stream, do_pre, do_sym, &launches);
     ctx->launches += launches;
     if (e != cudaSuccess) return fail(ctx, -EIO, "demodulator launch", e);
     return 0;

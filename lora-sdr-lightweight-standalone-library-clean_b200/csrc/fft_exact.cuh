@@ -106,12 +106,12 @@ struct Plan {
     static constexpr bool ODD = (SF & 1) != 0;
 
     // entries of the compact twiddle table (passes >= 1): 15 * m_a each
-    static constexpr int compact_size() {
+    FX_MHD static constexpr int compact_size() {
         int n = 0;
         for (int p = 1; p < NP; ++p) n += 15 << (W0 + 4 * (p - 1));
         return n > 0 ? n : 1;
     }
-    static constexpr int compact_offset(int pass) {
+    FX_MHD static constexpr int compact_offset(int pass) {
         int n = 0;
         for (int p = 1; p < pass; ++p) n += 15 << (W0 + 4 * (p - 1));
         return n;
@@ -146,9 +146,9 @@ struct Plan {
     // that 64-bit stores/loads of all passes are bank-conflict free.
     FX_MHD static int phys(int o)
     {
-        if (SF >= 8) return o ^ ((o >> (SF - 4)) & 15);
-        if (SF == 7) return o ^ ((o >> 4) & 7);
-        return o;
+        if constexpr (SF >= 8) return o ^ ((o >> (SF - 4)) & 15);
+        else if constexpr (SF == 7) return o ^ ((o >> 4) & 7);
+        else return o;
     }
 
     // ---- pass 0: v[c] = sample (tid + T*c); resolves position bits [0, W0) ------------

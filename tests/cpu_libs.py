@@ -159,6 +159,52 @@ class CpuPhy:
             sym.ctypes.data, sym.size, out.ctypes.data, ppm, rdd)
         return out
 
+    # ---- high-level API (oracle restatement only; the reference side is RefWorkspace) -----
+    def hl_demodulate(self, iq, sf, bw_hz=125000, osr=1, window=0, cap=None):
+        assert not self.is_ref
+        iq = np.ascontiguousarray(iq, dtype=np.complex64)
+        cap = iq.size if cap is None else cap
+        out = np.zeros(max(cap, 1), dtype=np.uint16)
+        sync = C.c_uint8(0)
+        cfo, to = C.c_float(0), C.c_float(0)
+        f = self.fn("demodulate", C.c_long,
+                    [C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                     C.POINTER(C.c_uint8), f32p, f32p])
+        r = f(sf, bw_hz, osr, window, iq.ctypes.data, iq.size, out.ctypes.data, cap, C.byref(sync),
+              C.byref(cfo), C.byref(to))
+        return int(r), out[:max(int(r), 0)].copy(), sync.value, np.float32(cfo.value), np.float32(to.value)
+
+    def hl_estimate_offsets(self, iq, sf, osr=1, window=0):
+        assert not self.is_ref
+        iq = np.ascontiguousarray(iq, dtype=np.complex64)
+        cfo, to = C.c_float(0), C.c_float(0)
+        f = self.fn("estimate_offsets", None, [C.c_uint, C.c_uint, C.c_int, C.c_void_p, C.c_size_t, f32p, f32p])
+        f(sf, osr, window, iq.ctypes.data, iq.size, C.byref(cfo), C.byref(to))
+        return np.float32(cfo.value), np.float32(to.value)
+
+    def hl_compensate_offsets(self, iq, sf, osr, cfo, to):
+        assert not self.is_ref
+        iq = np.array(iq, dtype=np.complex64, copy=True)
+        f = self.fn("compensate_offsets", None, [C.c_uint, C.c_uint, C.c_float, C.c_float, C.c_void_p, C.c_size_t])
+        f(sf, osr, cfo, to, iq.ctypes.data, iq.size)
+        return iq
+
+    def hl_decode(self, symbols, cap=None):
+        assert not self.is_ref
+        symbols = np.ascontiguousarray(symbols, dtype=np.uint16)
+        cap = symbols.size if cap is None else cap
+        out = np.zeros(symbols.size // 2 + 8, dtype=np.uint8)
+        crc = C.c_int(0)
+        f = self.fn("decode", C.c_long, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, i32p])
+        r = f(symbols.ctypes.data, symbols.size, out.ctypes.data, cap, C.byref(crc))
+        return int(r), out[:max(int(r), 0)].copy(), bool(crc.value)
+
+    def window(self, sf, hann=1):
+        assert not self.is_ref
+        out = np.zeros(1 << sf, dtype=np.float32)
+        self.fn("window", None, [C.c_uint, C.c_int, C.c_void_p])(sf, hann, out.ctypes.data)
+        return out
+
     # ---- timed batch ---------------------------------------------------------------
     def demod_batch_mt(self, iq, n_packets, spp, sf, osr=1, window=0, threads=1):
         iq = np.ascontiguousarray(iq, dtype=np.complex64)
