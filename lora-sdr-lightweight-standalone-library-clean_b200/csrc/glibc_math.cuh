@@ -57,40 +57,55 @@ GM_HD double ll2d_bits(uint64_t u) {
 }
 
 // ------------------------------------------------------------------------------------
-// sinf / cosf : glibc sysdeps/ieee754/flt-32/{s_sinf.c,s_cosf.c,sincosf.h}
+// sinf / cosf : glibc sysdeps/ieee754/flt-32/{s_sinf.c,s_cosf.c,s_sincosf.c,sincosf.h}
+//
+// x86-64 glibc resolves sinf/cosf/sincosf through an ifunc to the *_fma build of those
+// files (sysdeps/x86_64/fpu/multiarch) on every CPU with FMA+AVX2 -- i.e. on every host a
+// B200 is attached to.  That build contracts each `a + b*c` of sincosf.h into one fused
+// multiply-add.  The restatement below fuses exactly those expressions (and no others), and
+// tests/cpu/test_glibc_math.cpp shows 0 mismatches against the running glibc over ALL 2^32
+// float arguments for sinf, cosf and sincosf.
 // ------------------------------------------------------------------------------------
-struct SinCosPoly { double c0, c1, c2, c3, c4, s1, s2, s3; };
+GM_HD double dfma(double a, double b, double c) {
+#if defined(__CUDA_ARCH__)
+    return __fma_rn(a, b, c);
+#else
+    return fma(a, b, c);
+#endif
+}
+GM_HD double dmul(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dmul_rn(a, b);
+#else
+    return a * b;
+#endif
+}
 
 GM_HD double sc_hpi_inv() { return 0x1.45F306DC9C883p+23; }   // 2/pi * 2^24
 GM_HD double sc_hpi()     { return 0x1.921FB54442D18p0; }      // pi/2
 
-// polynomial pair; neg_cos selects __sincosf_table[1] (cosine coefficients negated)
+// sincosf.h polynomials on the reduced argument (|x| <= pi/4), __sincosf_table[0].
+// Table [1] negates every cosine coefficient, which negates the result exactly; the
+// quadrant sign multiplies x by +-1, which negates the (odd) sine result exactly.
 GM_HD double sc_sin_poly(double x, double x2)
 {
     const double s1 = -0x1.555545995a603p-3, s2 = 0x1.1107605230bc4p-7, s3 = -0x1.994eb3774cf24p-13;
-    double x3 = x * x2;
-    double t1 = s2 + x2 * s3;
-    double x7 = x3 * x2;
-    double s = x + x3 * s1;
-    return s + x7 * t1;
+    const double x3 = dmul(x, x2);
+    const double t1 = dfma(x2, s3, s2);
+    const double x7 = dmul(x3, x2);
+    const double s = dfma(x3, s1, x);
+    return dfma(x7, t1, s);
 }
-GM_HD double sc_cos_poly(double x2, bool neg)
+GM_HD double sc_cos_poly(double x2)
 {
-    double c0 = 0x1p0, c1 = -0x1.ffffffd0c621cp-2, c2 = 0x1.55553e1068f19p-5,
-           c3 = -0x1.6c087e89a359dp-10, c4 = 0x1.99343027bf8c3p-16;
-    if (neg) { c0 = -c0; c1 = -c1; c2 = -c2; c3 = -c3; c4 = -c4; }
-    double x4 = x2 * x2;
-    double t2 = c3 + x2 * c4;
-    double t1 = c0 + x2 * c1;
-    double x6 = x4 * x2;
-    double c = t1 + x4 * c2;
-    return c + x6 * t2;
-}
-
-// sinf_poly(x, x2, p, n): odd n -> cosine polynomial
-GM_HD float sc_eval(double x, double x2, bool neg, int n)
-{
-    return (n & 1) ? (float)sc_cos_poly(x2, neg) : (float)sc_sin_poly(x, x2);
+    const double c0 = 0x1p0, c1 = -0x1.ffffffd0c621cp-2, c2 = 0x1.55553e1068f19p-5,
+                 c3 = -0x1.6c087e89a359dp-10, c4 = 0x1.99343027bf8c3p-16;
+    const double x4 = dmul(x2, x2);
+    const double t2 = dfma(x2, c4, c3);
+    const double t1 = dfma(x2, c1, c0);
+    const double x6 = dmul(x4, x2);
+    const double c = dfma(x4, c2, t1);
+    return dfma(x6, t2, c);
 }
 
 GM_HD uint32_t sc_inv_pio4(int i)
@@ -120,77 +135,50 @@ GM_HD double sc_reduce_large(uint32_t xi, int* np)
     res0 -= n << 62;
     double x = (double)(int64_t)res0;
     *np = (int)n;
-    return x * 0x1.921FB54442D18p-62;                   // pi63
+    return dmul(x, 0x1.921FB54442D18p-62);              // pi63
 }
 
-// Common reduction: returns reduced |.|<=pi/4 argument already multiplied by the
-// quadrant sign, its square, the table selector and quadrant n.
-// cls: 0 = tiny (|y| < 2^-12), 1 = |y| < pi/4, 2 = reduced, 3 = inf/nan
-struct SinCosArg { double xs, x2; int n; bool neg; int cls; };
-
-GM_HD SinCosArg sc_reduce(float y)
+// Quadrant bookkeeping (sincosf.h sincosf_poly + the callers' sign set-up): with Ps / Pc the
+// sine / cosine polynomial on the reduced argument, n the quadrant from the reduction and
+// m = n + (sign of y, large-argument path only):  S = Ps * sign[m&3], C = Pc * (m&2 ? -1 : 1),
+// and (sin, cos) = n odd ? (C, S) : (S, C).
+GM_HD void sc_assemble(float ps, float pc, unsigned n, unsigned m, float* sn, float* cs)
 {
-    SinCosArg r;
-    const uint32_t iy = f2u(y);
-    const uint32_t top = (iy >> 20) & 0x7ff;
-    double x = (double)y;
-    r.n = 0; r.neg = false;
-    if (top < ((0x3f490fdbu >> 20) & 0x7ff)) {               // |y| < pi/4 (abstop12 compare)
-        r.xs = x; r.x2 = x * x;
-        r.cls = (top < ((0x39800000u >> 20) & 0x7ff)) ? 0 : 1; // 2^-12
-        return r;
-    }
-    if (top < ((0x42f00000u >> 20) & 0x7ff)) {               // |y| < 120
-        double q = x * sc_hpi_inv();
-        int n = ((int32_t)q + 0x800000) >> 24;
-        x = x - (double)n * sc_hpi();
-        const double s = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
-        r.neg = (n & 2) != 0;
-        r.xs = x * s; r.x2 = x * x; r.n = n; r.cls = 2;
-        return r;
-    }
-    if (top < ((0x7f800000u >> 20) & 0x7ff)) {
-        int n;
-        const int sign = (int)(iy >> 31);
-        x = sc_reduce_large(iy, &n);
-        const int q = (n + sign) & 3;
-        const double s = (q == 1 || q == 2) ? -1.0 : 1.0;
-        r.neg = ((n + sign) & 2) != 0;
-        r.xs = x * s; r.x2 = x * x; r.n = n; r.cls = 2;
-        return r;
-    }
-    r.xs = r.x2 = 0.0; r.cls = 3;
-    return r;
+    const uint32_t S = f2u(ps) ^ (((m + 1u) & 2u) << 30);
+    const uint32_t Cc = f2u(pc) ^ ((m & 2u) << 30);
+    *sn = u2f((n & 1u) ? Cc : S);
+    *cs = u2f((n & 1u) ? S : Cc);
 }
 
-GM_HD float sinf_g(float y)
+// |y| < 120: branch-free.  For |y| < pi/4 the reduction yields n = 0 and x unchanged, so
+// glibc's separate small-argument branch computes the same thing; |y| < 2^-12 is patched
+// to glibc's (y, 1.0f) at the end.
+GM_HD void sincosf_mid(float y, float* sn, float* cs)
 {
-    SinCosArg a = sc_reduce(y);
-    if (a.cls == 0) return y;
-    if (a.cls == 3) return y - y;                 // NaN (and raises invalid in glibc)
-    return sc_eval(a.xs, a.x2, a.neg, a.n);
+    const double x = (double)y;
+    const double q = dmul(x, sc_hpi_inv());
+    const int n = ((int32_t)q + 0x800000) >> 24;
+    const double xr = dfma(-(double)n, sc_hpi(), x);
+    const double x2 = dmul(xr, xr);
+    float ps = (float)sc_sin_poly(xr, x2);
+    float pc = (float)sc_cos_poly(x2);
+    if ((f2u(y) & 0x7fffffffu) < 0x39800000u) { ps = y; pc = 1.0f; }
+    sc_assemble(ps, pc, (unsigned)n, (unsigned)n, sn, cs);
 }
 
-GM_HD float cosf_g(float y)
-{
-    SinCosArg a = sc_reduce(y);
-    if (a.cls == 0) return 1.0f;
-    if (a.cls == 3) return y - y;
-    if (a.cls == 1) return (float)sc_cos_poly(a.x2, false);
-    return sc_eval(a.xs, a.x2, a.neg, a.n ^ 1);
-}
-
-// (cosf(y), sinf(y)) with the argument reduction shared -- same results as the two
-// separate calls above (both polynomials are evaluated on the same reduced argument).
 GM_HD void sincosf_g(float y, float* sn, float* cs)
 {
-    SinCosArg a = sc_reduce(y);
-    if (a.cls == 0) { *sn = y; *cs = 1.0f; return; }
-    if (a.cls == 3) { *sn = *cs = y - y; return; }
-    const float ps = (float)sc_sin_poly(a.xs, a.x2);
-    const float pc = (float)sc_cos_poly(a.x2, a.neg);
-    if (a.n & 1) { *sn = pc; *cs = ps; } else { *sn = ps; *cs = pc; }
+    const uint32_t iy = f2u(y), ay = iy & 0x7fffffffu;
+    if (ay < 0x42f00000u) { sincosf_mid(y, sn, cs); return; }       // |y| < 120
+    if (ay >= 0x7f800000u) { *sn = *cs = y - y; return; }           // inf / NaN
+    int n;
+    const double xr = sc_reduce_large(iy, &n);
+    const double x2 = dmul(xr, xr);
+    sc_assemble((float)sc_sin_poly(xr, x2), (float)sc_cos_poly(x2), (unsigned)n, (unsigned)n + (iy >> 31), sn, cs);
 }
+
+GM_HD float sinf_g(float y) { float s, c; sincosf_g(y, &s, &c); return s; }
+GM_HD float cosf_g(float y) { float s, c; sincosf_g(y, &s, &c); return c; }
 
 // ------------------------------------------------------------------------------------
 // hypotf : glibc sysdeps/ieee754/flt-32/e_hypotf.c (2.35+): double-precision sqrt
@@ -329,12 +317,21 @@ GM_HD float logf_g(float x)
     double invc, logc;
     logf_tab(i, &invc, &logc);
     const double z = (double)u2f(iz);
+#if defined(GM_LOGF_NOFMA)
     const double r = z * invc - 1;
     const double y0 = logc + (double)k * 0x1.62e42fefa39efp-1;
     const double r2 = r * r;
     double y = 0x1.5575b0be00b6ap-2 * r + -0x1.ffffef20a4123p-2;
     y = -0x1.00ea348b88334p-2 * r2 + y;
     y = y * r2 + (y0 + r);
+#else   // e_logf.c as built for the x86-64 FMA ifunc variant: every a*b+c fused
+    const double r = dfma(z, invc, -1.0);
+    const double y0 = dfma((double)k, 0x1.62e42fefa39efp-1, logc);
+    const double r2 = dmul(r, r);
+    double y = dfma(0x1.5575b0be00b6ap-2, r, -0x1.ffffef20a4123p-2);
+    y = dfma(-0x1.00ea348b88334p-2, r2, y);
+    y = dfma(y, r2, y0 + r);
+#endif
     return (float)y;
 }
 

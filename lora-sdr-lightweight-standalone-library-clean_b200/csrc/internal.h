@@ -29,6 +29,9 @@ __host__ __device__ inline float power_scale_of(int sf)
 cudaError_t launch_demod(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream, bool prepass,
                          bool symbols, unsigned* launches);
 cudaError_t launch_detect(int sf, const DetectArgs& a, int sm_count, cudaStream_t stream);
+// demod_stream.cu: TMA-staged data-symbol kernel (SF 7..12, osr == 1)
+bool stream_supported(int sf, const DemodArgs& a);
+cudaError_t launch_symbols_stream(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
 
 // tables.cu
 cudaError_t launch_build_tables(int sf, cf* tw, cf* ct, int ct_size, float* hann, cudaStream_t stream);
