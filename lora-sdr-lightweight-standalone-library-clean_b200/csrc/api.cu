@@ -235,6 +235,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.no_scratch = (cfg->flags & LORA_PHY_CUDA_F_NO_SCRATCH) ? 1 : 0;
     a.est_uniform = est_uniform;
     a.data_symbols_max = dsm;
+    a.dsm_magic = dsm ? (~0ull / dsm) + 1ull : 0ull;
     a.window = cfg->window ? ctx->tab[cfg->sf].hann : nullptr;
     a.down = nullptr;
     if (mode == lk::MODE_HIGHLEVEL) {

@@ -40,6 +40,7 @@ struct DemodArgs {
     int no_scratch;
     uint32_t est_uniform;         // uniform trip count of the estimator symbol loop
     uint32_t data_symbols_max;    // symbol-kernel items per packet
+    unsigned long long dsm_magic; // floor(2^64 / data_symbols_max) + 1: item / dsm == umul64hi(item, magic) for item < 2^32
     const float* window;          // nullptr = none
     const cf* down;               // nullptr unless MODE_HIGHLEVEL
     const cf* tw;
@@ -135,7 +136,7 @@ __device__ __forceinline__ Peak local_peak(const cf (&v)[fx::Plan<SF>::R], int t
     Peak pk; pk.val = 0.0f; pk.idx = 0;
 #pragma unroll
     for (int r = 0; r < P::R; ++r) {
-        const float m = fx::fadd(fx::fmul(v[r].x, v[r].x), fx::fmul(v[r].y, v[r].y));
+        const float m = fx::cnorm(v[r]);
         const int bin = P::bin_of_reg(tid, r);
         if (P::NP > 1) {                       // registers hold ascending bins
             if (m > pk.val) { pk.val = m; pk.idx = bin; }

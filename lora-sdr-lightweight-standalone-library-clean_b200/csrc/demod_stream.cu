@@ -76,7 +76,7 @@ __device__ __forceinline__ void fft_inplace(cf (&v)[fx::Plan<SF>::R], int tid, c
     }
 }
 
-// rare path: some |phase| of the window reaches 120 rad (glibc's large-argument reduction)
+// rare path: some |phase| of the window is below 2^-12 or reaches 120 rad (glibc's other branches)
 __device__ __noinline__ float2 sincos_slow(float ph)
 {
     float sn, cs;
@@ -107,39 +107,46 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) symbols_stream_kernel(const De
     }
     __syncthreads();
 
-    const unsigned long long n_items = (unsigned long long)a.n_packets * a.data_symbols_max;
-    const unsigned long long n_units = (n_items + GD - 1) / GD;
-    const unsigned long long stride = (unsigned long long)gridDim.x * C::DOMS;
+    // the launcher guarantees n_items < 2^32 (else the generic kernel runs)
+    const uint32_t n_items = a.n_packets * a.data_symbols_max;
+    const uint32_t n_units = (n_items + GD - 1) / GD;
+    const uint32_t stride = gridDim.x * C::DOMS;
 
     // leader of window gq: describe item, publish the descriptor, start the bulk copy
-    auto prefetch = [&](unsigned long long u, int stage) {
+    auto prefetch = [&](uint32_t u, int stage) {
         if (tid != 0) return;
         WinDesc d;
         d.scale = 1.0f; d.rate = 0.0f; d.start = 0.0f; d.flags = 0; d.out_off = 0; d.pad = 0;
-        const unsigned long long item = u * GD + gq;
+        const uint32_t item = u * GD + gq;
         const cf* src = nullptr;
         if (item < n_items) {
-            const uint32_t pid = (uint32_t)(item / a.data_symbols_max);
-            const uint32_t k = (uint32_t)(item - (unsigned long long)pid * a.data_symbols_max);
+            const uint32_t pid = (uint32_t)__umul64hi((unsigned long long)item, a.dsm_magic);   // item / dsm
+            const uint32_t k = item - pid * a.data_symbols_max;
             const uint32_t count = a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet;
             const uint32_t total = count / (uint32_t)N;
             const uint32_t s = total >= 2 ? k + 2 : k;
-            const PacketState st = a.state[pid];
+            const int4 sraw = __ldg(reinterpret_cast<const int4*>(a.state + pid));
+            PacketState st;
+            st.scale = __int_as_float(sraw.x); st.rate = __int_as_float(sraw.y); st.t_off = sraw.z; st.flags = sraw.w;
             if (s < total && !(st.flags & PS_SKIP)) {
-                size_t base = (size_t)s * N;                       // LoRaDemod.cpp:143-150
+                uint32_t base = s * (uint32_t)N;                   // LoRaDemod.cpp:143-150
                 if (st.t_off > 0) {
-                    if (base + (size_t)st.t_off + N <= count) base += (size_t)st.t_off;
+                    if ((unsigned long long)base + (unsigned)st.t_off + N <= count) base += (uint32_t)st.t_off;
                 } else if (st.t_off < 0) {
-                    const size_t off = (size_t)(-(long long)st.t_off);
+                    const uint32_t off = (uint32_t)(-(long long)st.t_off);
                     if (off <= base) base -= off;
                 }
                 src = a.iq + (size_t)pid * a.packet_stride + base;
                 d.scale = st.scale;
                 d.rate = st.rate;
-                d.start = fx::fmul(st.rate, fx::fadd(__ull2float_rn((unsigned long long)s * N), __int2float_rn(st.t_off)));
+                d.start = fx::fmul(st.rate, fx::fadd(__uint2float_rn(s * (uint32_t)N), __int2float_rn(st.t_off)));
+                // phases run monotonically from `start` (i = 0) to `last` (i = N-1): the fast sincos
+                // core needs 2^-12 <= |ph| < 120 for every sample of the window
                 const float last = fx::fadd(d.start, fx::fmul(st.rate, (float)(N - 1)));
+                const float lo = fminf(fabsf(d.start), fabsf(last)), hi = fmaxf(fabsf(d.start), fabsf(last));
+                const bool same_sign = (__float_as_uint(d.start) ^ __float_as_uint(last)) < 0x80000000u;
                 d.flags = WD_ACTIVE;
-                if (!(fabsf(d.start) < 119.0f && fabsf(last) < 119.0f)) d.flags |= WD_SLOW;
+                if (!(same_sign && lo >= 0x1p-11f && hi < 119.0f)) d.flags |= WD_SLOW;
                 d.out_off = (unsigned long long)pid * a.symbol_stride + k;
             }
         }
@@ -160,14 +167,14 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) symbols_stream_kernel(const De
         }
     };
 
-    unsigned long long u = (unsigned long long)blockIdx.x * C::DOMS + dom;
+    uint32_t u = blockIdx.x * C::DOMS + dom;
     int stage = 0;
     unsigned phase_bits = 0;                     // bit s = parity the next wait on stage s expects
     const float fi0 = (float)tid;
     if (u < n_units) prefetch(u, 0);
 
     while (u < n_units) {
-        const unsigned long long u_next = u + stride;
+        const uint32_t u_next = u + stride;        // n_units + stride < 2^32 is checked by the launcher
         if (u_next < n_units) prefetch(u_next, stage ^ 1);
 
         ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
@@ -182,11 +189,11 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) symbols_stream_kernel(const De
             if (!(d.flags & WD_SLOW)) {
 #pragma unroll
                 for (int c = 0; c < P::R; ++c) {
-                    cf x = fx::cscale(raw[T * c], d.scale);                                  // LoRaDemod.cpp:75-77
+                    cf x = fx::cscale2(raw[T * c], d.scale);                                 // LoRaDemod.cpp:75-77
                     if (EXTRA && a.down) x = fx::cmul(x, ldg_cf(a.down + tid + T * c));      // phy.cpp:224
                     const float ph = fx::fadd(d.start, fx::fmul(d.rate, fx::fadd(fi0, (float)(T * c))));
                     float sn, cs;
-                    gm::sincosf_mid(ph, &sn, &cs);                                           // LoRaDemod.cpp:155-159
+                    gm::sincosf_core(ph, &sn, &cs);                                          // LoRaDemod.cpp:155-159
                     x = fx::cmul(x, fx::mk(cs, sn));
                     if (EXTRA && a.window) x = fx::cscale(x, __ldg(a.window + tid + T * c)); // LoRaDemod.cpp:160-161
                     v[c] = x;
@@ -244,7 +251,9 @@ static cudaError_t launch_stream_sf(const DemodArgs& a, int sm_count, cudaStream
 
 bool stream_supported(int sf, const DemodArgs& a)
 {
-    return sf >= 7 && sf <= 12 && a.osr == 1;
+    const unsigned long long items = (unsigned long long)a.n_packets * a.data_symbols_max;
+    return sf >= 7 && sf <= 12 && a.osr == 1 && items < 0xf0000000ull &&
+           (unsigned long long)a.samples_per_packet < 0xf0000000ull;
 }
 
 cudaError_t launch_symbols_stream(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream)

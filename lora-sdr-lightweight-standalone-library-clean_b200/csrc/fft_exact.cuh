@@ -55,12 +55,79 @@ FX_HD float fsub(float a, float b) {
 #endif
 }
 FX_HD cf mk(float x, float y) { cf r; r.x = x; r.y = y; return r; }
-FX_HD cf cadd(cf a, cf b) { return mk(fadd(a.x, b.x), fadd(a.y, b.y)); }
-FX_HD cf csub(cf a, cf b) { return mk(fsub(a.x, b.x), fsub(a.y, b.y)); }
-// std::complex<float> operator* for finite operands: (ac - bd, ad + bc)
-FX_HD cf cmul(cf a, cf b) {
-    return mk(fsub(fmul(a.x, b.x), fmul(a.y, b.y)), fadd(fmul(a.x, b.y), fmul(a.y, b.x)));
+
+// sm_100a packed FP32: one FADD2 / FMUL2 instruction performs the two IEEE round-to-nearest
+// operations of a complex add / scale (same results as two scalar ops, half the issue slots).
+// Rule kept throughout: a packed MULTIPLY never feeds a packed ADD -- ptxas 12.9 contracts
+// mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even with --fmad=false, which would round once
+// instead of twice.  Products are therefore combined with SCALAR adds (never contracted), and
+// the Makefile's sass-check target fails the build if any FFMA2 shows up in the library.
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ unsigned long long pk2(cf a)
+{
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a.x), "f"(a.y));
+    return r;
 }
+__device__ __forceinline__ cf upk2(unsigned long long v)
+{
+    cf r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+#endif
+FX_HD cf cadd(cf a, cf b)
+{
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a)), "l"(pk2(b)));
+    return upk2(r);
+#else
+    return mk(fadd(a.x, b.x), fadd(a.y, b.y));
+#endif
+}
+FX_HD cf csub(cf a, cf b)
+{
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a)), "l"(pk2(b)));
+    return upk2(r);
+#else
+    return mk(fsub(a.x, b.x), fsub(a.y, b.y));
+#endif
+}
+// (a.x*s, a.y*s); on the device the result must feed a multiply or a scalar add, never cadd/csub
+FX_HD cf cscale2(cf a, float s)
+{
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a)), "l"(pk2(mk(s, s))));
+    return upk2(r);
+#else
+    return mk(fmul(a.x, s), fmul(a.y, s));
+#endif
+}
+// std::complex<float> operator* for finite operands: (ac - bd, ad + bc).  Device: four products
+// by two FMUL2, combined by two scalar adds (bc + ad == ad + bc bit for bit).
+FX_HD cf cmul(cf a, cf b)
+{
+    const cf p1 = cscale2(a, b.x);      // (ac, bc)
+    const cf p2 = cscale2(a, b.y);      // (ad, bd)
+    return mk(fsub(p1.x, p2.y), fadd(p1.y, p2.x));
+}
+// |z|^2 = re*re + im*im (LoRaDetector.hpp:48)
+FX_HD float cnorm(cf a)
+{
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %1;" : "=l"(r) : "l"(pk2(a)));
+    const cf p = upk2(r);
+    return fadd(p.x, p.y);
+#else
+    return fadd(fmul(a.x, a.x), fmul(a.y, a.y));
+#endif
+}
+// scalar scale: safe in front of cadd/csub (see the rule above)
 FX_HD cf cscale(cf a, float s) { return mk(fmul(a.x, s), fmul(a.y, s)); }
 
 // kf_bfly4 (kissfft.hh:164-185), forward transform, one k.  f0..f3 = F[k], F[k+m], F[k+2m], F[k+3m].

@@ -150,20 +150,34 @@ GM_HD void sc_assemble(float ps, float pc, unsigned n, unsigned m, float* sn, fl
     *cs = u2f((n & 1u) ? S : Cc);
 }
 
-// |y| < 120: branch-free.  For |y| < pi/4 the reduction yields n = 0 and x unchanged, so
-// glibc's separate small-argument branch computes the same thing; |y| < 2^-12 is patched
-// to glibc's (y, 1.0f) at the end.
-GM_HD void sincosf_mid(float y, float* sn, float* cs)
+// Core of the |y| < 120 path: reduction + both polynomials + quadrant assembly.  For
+// |y| < pi/4 the reduction yields n = 0 and x unchanged, so glibc's separate small-argument
+// branch computes the same thing.  NOT valid for |y| < 2^-12 (glibc returns (y, 1.0f) there).
+GM_HD void sincosf_core(float y, float* sn, float* cs)
 {
     const double x = (double)y;
     const double q = dmul(x, sc_hpi_inv());
     const int n = ((int32_t)q + 0x800000) >> 24;
     const double xr = dfma(-(double)n, sc_hpi(), x);
     const double x2 = dmul(xr, xr);
-    float ps = (float)sc_sin_poly(xr, x2);
-    float pc = (float)sc_cos_poly(x2);
-    if ((f2u(y) & 0x7fffffffu) < 0x39800000u) { ps = y; pc = 1.0f; }
-    sc_assemble(ps, pc, (unsigned)n, (unsigned)n, sn, cs);
+    const float ps = (float)sc_sin_poly(xr, x2);
+    const float pc = (float)sc_cos_poly(x2);
+    // sc_assemble with m == n, written for few instructions: bit 31 of t is bit 1 of n
+    const uint32_t t = (uint32_t)n << 30;
+    const uint32_t S = f2u(ps) ^ ((t + 0x40000000u) & 0x80000000u);
+    const uint32_t Cc = f2u(pc) ^ (t & 0x80000000u);
+    const bool odd = (n & 1) != 0;
+    *sn = u2f(odd ? Cc : S);
+    *cs = u2f(odd ? S : Cc);
+}
+
+// |y| < 120, any magnitude: the core plus glibc's tiny-argument result.
+GM_HD void sincosf_mid(float y, float* sn, float* cs)
+{
+    float s, c;
+    sincosf_core(y, &s, &c);
+    if ((f2u(y) & 0x7fffffffu) < 0x39800000u) { s = y; c = 1.0f; }   // |y| < 2^-12 (n == 0 there)
+    *sn = s; *cs = c;
 }
 
 GM_HD void sincosf_g(float y, float* sn, float* cs)
