@@ -154,13 +154,20 @@ def run_ours(args, wl):
     out = phy.alloc_demod_outputs(P, nsym - 2)
     torch.cuda.synchronize()
 
+    two = not args.fused
     cfg_pre = lp.make_cfg(sf, flags=lp.F_ONLY_PREPASS)
     cfg_sym = lp.make_cfg(sf, flags=lp.F_ONLY_SYMBOLS)
 
     def step(ev=None):
-        if ev is None:
+        if not two:                            # experimental: ONE persistent fused launch per batch
+            if ev is not None:
+                ev[0].record()
+            phy.demodulate_batch(lp.make_cfg(sf, flags=lp.F_FUSED), iq, out=out)
+            if ev is not None:
+                ev[1].record()
+        elif ev is None:
             phy.demodulate_batch(cfg, iq, out=out)
-        else:                                  # same two launches, with an event between them
+        else:                                  # the same two launches, events around the symbols kernel
             phy.demodulate_batch(cfg_pre, iq, out=out)
             ev[0].record()
             phy.demodulate_batch(cfg_sym, iq, out=out)
@@ -230,7 +237,12 @@ def run_ours(args, wl):
     peaks, peak_kind = load_peaks()
     peak = float(peaks["hbm_gbs"])
     b_sym = 8 * N + 2                                   # algorithmic bytes per demodulated symbol
-    sym_bytes = P * (nsym - 2) * b_sym                  # symbols kernel: data symbols of every packet, once
+    if two:
+        kname = "symbols_stream_kernel<SF%d>" % sf
+        sym_bytes = P * (nsym - 2) * b_sym              # symbols kernel: data symbols of every packet, once
+    else:
+        kname = "demod_fused_kernel<SF%d>" % sf
+        sym_bytes = P * nsym * b_sym                    # fused kernel: every symbol of every packet, once
     achieved = sym_bytes / (sym_kernel_ms * 1e-3) / 1e9
     step_bytes = P * nsym * b_sym
     line = {
@@ -241,7 +253,7 @@ def run_ours(args, wl):
         "step_hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
         "config": {"workload": wl["name"], "packets_per_gpu": P, "symbols_per_packet": nsym, "sf": sf,
                    "l2_policy": "inputs larger than L2 (%.1f GB per GPU per step)" % (P * spp * 8 / 1e9)},
-        "roofline": {"bound": "hbm", "kernel": "symbols_kernel<SF%d>" % sf, "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
                      "kernel_ms": sym_kernel_ms, "algorithmic_bytes_per_launch": sym_bytes},
         "e2e": {"value": e2e_value, "unit": "symbols/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -271,6 +283,7 @@ def main():
     ap.add_argument("--packets", type=int, default=0, help="packets per GPU (default: the workload's)")
     ap.add_argument("--e2e-packets", type=int, default=1 << 15)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--fused", action="store_true", help="A/B: time the experimental fused persistent launch instead of the prepass + symbols pair")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]

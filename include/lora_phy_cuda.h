@@ -54,6 +54,9 @@ typedef struct lora_phy_cuda_cfg {
 /* Split one demodulate_batch call into its two launches (bench.py times the kernels separately
  * with CUDA events; a normal call sets neither):                                            */
 #define LORA_PHY_CUDA_F_ONLY_PREPASS 0x10u /* run only the per-packet prepass (max-abs, estimator, sync) */
+#define LORA_PHY_CUDA_F_FUSED        0x40u /* experimental: scan + estimator + data symbols in ONE persistent cooperative
+                                              launch (demod_fused.cu) instead of the prepass + symbols kernel pair;
+                                              results are identical, see DESIGN.md for when it pays */
 #define LORA_PHY_CUDA_F_ONLY_SYMBOLS 0x20u /* run only the data-symbol kernel, reusing the packet state
                                               the previous prepass of the same batch left in the context */
 

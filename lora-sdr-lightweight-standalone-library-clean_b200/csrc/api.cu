@@ -6,6 +6,7 @@
 
 #include <cerrno>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -60,7 +61,8 @@ struct lora_phy_cuda_ctx {
     uint64_t launches = 0;
     SfTables tab[13];
     std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
-    DevBuf state, phases, tmp;                          // PacketState[], modulator phases, compensate scratch
+    DevBuf state, phases, tmp, sched;                   // PacketState[], modulator phases, compensate scratch, fused-kernel counters
+    uint32_t lookahead_bytes = 64u << 20;               // fused schedule look-ahead (LORA_PHY_LOOKAHEAD_MB)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
     std::mutex mu;
@@ -135,6 +137,10 @@ int lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device)
     ctx->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return -EIO; }
     ctx->own_stream = true;
+    if (const char* mb = getenv("LORA_PHY_LOOKAHEAD_MB")) {
+        const long v = strtol(mb, nullptr, 10);
+        if (v > 0 && v < 4096) ctx->lookahead_bytes = (uint32_t)v << 20;
+    }
     for (int sf = 2; sf <= 12; ++sf) {
         const size_t N = (size_t)1 << sf;
         SfTables& t = ctx->tab[sf];
@@ -163,7 +169,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
         if (ctx->tab[sf].hann) cudaFree(ctx->tab[sf].hann);
     }
     for (auto& kv : ctx->chirps) cudaFree(kv.second);
-    ctx->state.release(); ctx->phases.release(); ctx->tmp.release();
+    ctx->state.release(); ctx->phases.release(); ctx->tmp.release(); ctx->sched.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
     ctx->h_in.release(); ctx->h_out.release();
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -255,6 +261,21 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.time_offset = d_to;
     a.status = d_status;
     unsigned launches = 0;
+    // experimental: one persistent cooperative launch for the whole demodulator ("fused schedule")
+    if ((cfg->flags & LORA_PHY_CUDA_F_FUSED) && !(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS))) {
+        lk::FusedArgs f;
+        if (lk::fused_plan((int)cfg->sf, a, ctx->lookahead_bytes, &f)) {
+            const size_t words = 4 + 3 * n_packets;
+            CK(ctx->sched.reserve(words * sizeof(uint32_t)));
+            CK(cudaMemsetAsync(ctx->sched.p, 0, words * sizeof(uint32_t), ctx->stream));
+            uint32_t* w = static_cast<uint32_t*>(ctx->sched.p);
+            f.pmax = w + 4; f.acount = w + 4 + n_packets; f.eready = w + 4 + 2 * n_packets;
+            cudaError_t e = lk::launch_demod_fused((int)cfg->sf, f, ctx->sm_count, ctx->stream);
+            ++ctx->launches;
+            if (e != cudaSuccess) return fail(ctx, -EIO, "fused demodulator launch", e);
+            return 0;
+        }
+    }
     const bool do_pre = !(cfg->flags & LORA_PHY_CUDA_F_ONLY_SYMBOLS);
     const bool do_sym = mode != lk::MODE_EST_ONLY && !(cfg->flags & LORA_PHY_CUDA_F_ONLY_PREPASS);
     cudaError_t e = lk::launch_demod((int)cfg->sf, a, ctx->sm_count, ctx->stream, do_pre, do_sym, &launches);

@@ -9,6 +9,7 @@ namespace lk {
 
 using fx::cf;
 struct DemodArgs;
+struct FusedArgs;
 
 struct DetectArgs {
     const cf* windows; uint32_t n_windows;
@@ -32,6 +33,9 @@ cudaError_t launch_detect(int sf, const DetectArgs& a, int sm_count, cudaStream_
 // demod_stream.cu: TMA-staged data-symbol kernel (SF 7..12, osr == 1)
 bool stream_supported(int sf, const DemodArgs& a);
 cudaError_t launch_symbols_stream(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
+// demod_fused.cu: scan + estimator + sync + data symbols in one persistent launch (SF 7..12, osr == 1)
+bool fused_plan(int sf, const DemodArgs& a, uint32_t lookahead_bytes, FusedArgs* f);
+cudaError_t launch_demod_fused(int sf, const FusedArgs& f, int sm_count, cudaStream_t stream);
 
 // tables.cu
 cudaError_t launch_build_tables(int sf, cf* tw, cf* ct, int ct_size, float* hann, cudaStream_t stream);

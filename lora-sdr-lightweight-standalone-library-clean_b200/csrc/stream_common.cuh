@@ -1,0 +1,156 @@
+// stream_common.cuh -- pieces shared by the streaming kernels (demod_stream.cu: data symbols
+// only; demod_fused.cu: max-abs scan + estimator + sync + data symbols in one launch).
+#pragma once
+#include "demod_device.cuh"
+#include "stream_ptx.cuh"
+
+namespace lk {
+
+#ifndef STREAM_CTAS_PER_SM
+#define STREAM_CTAS_PER_SM 3      // 24 warps per SM at <= 85 registers; 3 x ~72 KB of stages fit the 227 KB of shared memory
+#endif
+
+struct __align__(16) WinDesc {       // written by the window's leader at prefetch time
+    float scale, rate, start;
+    uint32_t flags;                   // WD_*
+    unsigned long long out_off;       // index into a.symbols (data windows) / packet id (scan windows)
+    uint32_t aux0, aux1;              // unit-type specific
+};
+enum { WD_ACTIVE = 1, WD_ODD = 2, WD_SLOW = 4, WD_DIRECT = 8, WD_DEFERRED = 16 };
+
+template <int SF>
+struct StreamCfg {
+    using P = fx::Plan<SF>;
+    static constexpr int T = P::T, N = P::N;
+    static constexpr int DOM_THREADS = T <= 32 ? 32 : CTA_THREADS;   // threads sharing one pipeline
+    static constexpr int DOMS = CTA_THREADS / DOM_THREADS;           // pipelines per CTA
+    static constexpr int GD = DOM_THREADS / T;                       // windows per pipeline step
+    static constexpr int PITCH = N + 8;     // +1 entry for the odd-aligned tail sample, +8 keeps 64-byte
+                                            // alignment and shifts neighbouring SF7 windows by 16 banks
+    static constexpr int SLOT = GD * PITCH; // cf entries per stage
+    static constexpr int STAGES = 2;
+    static constexpr size_t slot_bytes = (size_t)DOMS * STAGES * SLOT * sizeof(cf);
+    static constexpr size_t desc_bytes = (size_t)DOMS * STAGES * GD * sizeof(WinDesc);
+    static constexpr size_t bar_bytes = (size_t)DOMS * STAGES * sizeof(uint64_t);
+    static constexpr size_t bytes = slot_bytes + desc_bytes + bar_bytes + 8 * sizeof(Peak);
+};
+
+template <int SF>
+__device__ __forceinline__ void domain_sync()
+{
+    if (StreamCfg<SF>::T <= 32) __syncwarp(); else __syncthreads();
+}
+
+// exact-order FFT with every exchange done in the window's own slot (N entries at `ex`)
+template <int SF, bool FULL>
+__device__ __forceinline__ void fft_inplace(cf (&v)[fx::Plan<SF>::R], int tid, const cf* __restrict__ tw,
+                                            const cf* __restrict__ ct, cf* ex)
+{
+    using P = fx::Plan<SF>;
+    P::template pass0<FULL>(v, tw);
+#pragma unroll
+    for (int p = 1; p < P::NP; ++p) {
+        domain_sync<SF>();            // raw samples (p == 1) / previous exchange (p > 1) fully consumed
+#pragma unroll
+        for (int r = 0; r < P::R; ++r) {
+            const int o = (p == 1) ? P::pos_after_pass0(tid, r) : P::pos_in_pass(p - 1, tid, r);
+            ex[P::phys(o)] = v[r];
+        }
+        domain_sync<SF>();
+#pragma unroll
+        for (int r = 0; r < P::R; ++r) v[r] = ex[P::phys(P::pos_in_pass(p, tid, r))];
+        P::pass(p, v, tid, ct);
+    }
+}
+
+// rare path: some |phase| of the window is below 2^-12 or reaches 120 rad (glibc's other branches)
+static __device__ __noinline__ float2 sincos_slow(float ph)
+{
+    float sn, cs;
+    gm::sincosf_g(ph, &sn, &cs);
+    return make_float2(cs, sn);
+}
+
+// Window classification for the fast sincos core: phases run monotonically from `start` (i = 0)
+// to `last` (i = N-1); the core needs 2^-12 <= |ph| < 120 for every sample.
+__device__ __forceinline__ bool phases_need_slow_path(float start, float last)
+{
+    const float lo = fminf(fabsf(start), fabsf(last)), hi = fmaxf(fabsf(start), fabsf(last));
+    const bool same_sign = (__float_as_uint(start) ^ __float_as_uint(last)) < 0x80000000u;
+    return !(same_sign && lo >= 0x1p-11f && hi < 119.0f);
+}
+
+// Per-sample chain of one data / sync window held in shared memory (LoRaDemod.cpp:154-163,
+// phy.cpp:220-231): normalise -> [downchirp] -> CFO rotation -> [Hann], into pass-0 register order.
+template <int SF, bool EXTRA>
+__device__ __forceinline__ void chain_window(cf (&v)[fx::Plan<SF>::R], const cf* raw /* window + tid */, int tid,
+                                             float scale, float rate, float start, bool slow,
+                                             const cf* __restrict__ down, const float* __restrict__ w)
+{
+    using P = fx::Plan<SF>;
+    constexpr int T = P::T;
+    const float fi0 = (float)tid;
+    if (!slow) {
+#pragma unroll
+        for (int c = 0; c < P::R; ++c) {
+            cf x = fx::cscale2(raw[T * c], scale);                                   // LoRaDemod.cpp:75-77
+            if (EXTRA && down) x = fx::cmul(x, ldg_cf(down + tid + T * c));          // phy.cpp:224
+            const float ph = fx::fadd(start, fx::fmul(rate, fx::fadd(fi0, (float)(T * c))));
+            float sn, cs;
+            gm::sincosf_core(ph, &sn, &cs);                                          // LoRaDemod.cpp:155-159
+            x = fx::cmul(x, fx::mk(cs, sn));
+            if (EXTRA && w) x = fx::cscale(x, __ldg(w + tid + T * c));               // LoRaDemod.cpp:160-161
+            v[c] = x;
+        }
+    } else {
+#pragma unroll
+        for (int c = 0; c < P::R; ++c) {
+            cf x = fx::cscale(raw[T * c], scale);
+            if (EXTRA && down) x = fx::cmul(x, ldg_cf(down + tid + T * c));
+            const float ph = fx::fadd(start, fx::fmul(rate, fx::fadd(fi0, (float)(T * c))));
+            const float2 r = sincos_slow(ph);
+            x = fx::cmul(x, fx::mk(r.x, r.y));
+            if (EXTRA && w) x = fx::cscale(x, __ldg(w + tid + T * c));
+            v[c] = x;
+        }
+    }
+}
+
+// window base of symbol s with the guarded time-offset shift (LoRaDemod.cpp:143-150), osr == 1
+__device__ __forceinline__ uint32_t shifted_base(uint32_t s, uint32_t N, int t_off, uint32_t count)
+{
+    uint32_t base = s * N;
+    if (t_off > 0) {
+        if ((unsigned long long)base + (unsigned)t_off + N <= count) base += (uint32_t)t_off;
+    } else if (t_off < 0) {
+        const uint32_t off = (uint32_t)(-(long long)t_off);
+        if (off <= base) base -= off;
+    }
+    return base;
+}
+
+// start phase of symbol s (LoRaDemod.cpp:152-153), osr == 1
+__device__ __forceinline__ float start_phase(float rate, uint32_t s, uint32_t N, int t_off)
+{
+    return fx::fmul(rate, fx::fadd(__uint2float_rn(s * N), __int2float_rn(t_off)));
+}
+
+__device__ __forceinline__ bool window_is_odd(const cf* src)      // starts 8 bytes after a 16-byte boundary
+{
+    return ((reinterpret_cast<uintptr_t>(src) >> 3) & 1u) != 0;
+}
+
+// Leader-side fetch of one full window into its stage slot: aligned bulk copy plus, for an odd
+// window, the one sample the aligned copy misses (readers then start at win + 1).  The caller
+// publishes its descriptor BEFORE calling: the mbarrier arrive releases it to the waiters.
+template <int N>
+__device__ __forceinline__ void fetch_window(cf* win, const cf* src, uint64_t* bar)
+{
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(src);
+    const unsigned odd = (unsigned)(addr >> 3) & 1u;
+    if (odd) win[N] = ldg_cf(src + (N - 1));
+    ptx::mbar_arrive_expect_tx(bar, (unsigned)(N * sizeof(cf)));
+    ptx::bulk_g2s(win, reinterpret_cast<const void*>(addr - 8u * odd), (unsigned)(N * sizeof(cf)), bar);
+}
+
+} // namespace lk
