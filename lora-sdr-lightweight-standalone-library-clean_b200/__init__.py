@@ -256,3 +256,6 @@ class LoraPhyCuda:
         out = np.zeros(N, dtype=np.float32 if which == 1 else np.complex64)
         self._check(self.lib.lora_phy_cuda_copy_table(self.h, sf, bw_hz, which, out.ctypes.data))
         return out
+
+
+from .shard import packet_range, all_ranges, gather_results  # noqa: E402  (multi-GPU packet-range sharding)
