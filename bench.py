@@ -3,8 +3,8 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload sf7|sf12] [--impl reference]
 
-A "step" is one pass of the demodulator (lora_phy_cuda_demodulate_batch: prepass + symbols
-kernels) over one batch of synthetic, clean, pre-dechirped IQ already resident in HBM.
+A "step" is one pass of the demodulator (lora_phy_cuda_demodulate_batch: one launch of
+demod_packet_kernel, one CTA per packet: scan -> estimator -> symbols) over one batch of synthetic, clean, pre-dechirped IQ already resident in HBM.
 Workloads (BASELINE.json configs[1] / configs[2]):
   sf7   SF7 BW125k, 32-byte payloads (66 symbols = 8448 samples = 67.6 KB per packet), 1 Mi packets
   sf12  SF12 BW125k, 64-byte payloads (130 symbols = 4.26 MB per packet), 16 Ki packets resident
@@ -154,20 +154,21 @@ def run_ours(args, wl):
     out = phy.alloc_demod_outputs(P, nsym - 2)
     torch.cuda.synchronize()
 
-    two = not args.fused
+    two = args.two_kernel
     cfg_pre = lp.make_cfg(sf, flags=lp.F_ONLY_PREPASS)
     cfg_sym = lp.make_cfg(sf, flags=lp.F_ONLY_SYMBOLS)
+    cfg_one = lp.make_cfg(sf, flags=lp.F_FUSED) if args.fused else cfg
 
     def step(ev=None):
-        if not two:                            # experimental: ONE persistent fused launch per batch
+        if not two:                            # default: ONE launch per batch (demod_packet_kernel, one CTA per packet)
             if ev is not None:
                 ev[0].record()
-            phy.demodulate_batch(lp.make_cfg(sf, flags=lp.F_FUSED), iq, out=out)
+            phy.demodulate_batch(cfg_one, iq, out=out)
             if ev is not None:
                 ev[1].record()
         elif ev is None:
-            phy.demodulate_batch(cfg, iq, out=out)
-        else:                                  # the same two launches, events around the symbols kernel
+            phy.demodulate_batch(lp.make_cfg(sf, flags=lp.F_TWO_KERNEL), iq, out=out)
+        else:                                  # A/B: the older two launches, events around the symbols kernel
             phy.demodulate_batch(cfg_pre, iq, out=out)
             ev[0].record()
             phy.demodulate_batch(cfg_sym, iq, out=out)
@@ -241,8 +242,8 @@ def run_ours(args, wl):
         kname = "symbols_stream_kernel<SF%d>" % sf
         sym_bytes = P * (nsym - 2) * b_sym              # symbols kernel: data symbols of every packet, once
     else:
-        kname = "demod_fused_kernel<SF%d>" % sf
-        sym_bytes = P * nsym * b_sym                    # fused kernel: every symbol of every packet, once
+        kname = ("demod_fused_kernel<SF%d>" if args.fused else "demod_packet_kernel<SF%d>") % sf
+        sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
     achieved = sym_bytes / (sym_kernel_ms * 1e-3) / 1e9
     step_bytes = P * nsym * b_sym
     line = {
@@ -283,7 +284,8 @@ def main():
     ap.add_argument("--packets", type=int, default=0, help="packets per GPU (default: the workload's)")
     ap.add_argument("--e2e-packets", type=int, default=1 << 15)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--fused", action="store_true", help="A/B: time the experimental fused persistent launch instead of the prepass + symbols pair")
+    ap.add_argument("--fused", action="store_true", help="A/B: time the experimental ticket-scheduled fused launch (demod_fused.cu)")
+    ap.add_argument("--two-kernel", action="store_true", help="A/B: time the older prepass + symbols kernel pair")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]

@@ -60,6 +60,9 @@ typedef struct lora_phy_cuda_cfg {
 #define LORA_PHY_CUDA_F_ONLY_SYMBOLS 0x20u /* run only the data-symbol kernel, reusing the packet state
                                               the previous prepass of the same batch left in the context */
 
+#define LORA_PHY_CUDA_F_TWO_KERNEL   0x80u /* A/B: force the older prepass + symbols kernel pair instead of the default
+                                              single launch with one CTA per packet (demod_packet.cu) */
+
 /* ---- context -------------------------------------------------------------------------- */
 /* replaces lora_demod_init / init (LoRaDemod.cpp:11-33, phy.cpp:27-52): builds, ON THE DEVICE,
  * the kissfft twiddle tables, Hann windows and downchirp tables for SF 2..12.            */

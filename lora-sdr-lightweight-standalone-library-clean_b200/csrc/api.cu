@@ -276,6 +276,14 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
             return 0;
         }
     }
+    // default: one launch, one CTA per packet (demod_packet.cu)
+    if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_FUSED)) &&
+        lk::packet_supported((int)cfg->sf, a)) {
+        cudaError_t e = lk::launch_demod_packet((int)cfg->sf, a, ctx->sm_count, ctx->stream);
+        ++ctx->launches;
+        if (e != cudaSuccess) return fail(ctx, -EIO, "packet demodulator launch", e);
+        return 0;
+    }
     const bool do_pre = !(cfg->flags & LORA_PHY_CUDA_F_ONLY_SYMBOLS);
     const bool do_sym = mode != lk::MODE_EST_ONLY && !(cfg->flags & LORA_PHY_CUDA_F_ONLY_PREPASS);
     cudaError_t e = lk::launch_demod((int)cfg->sf, a, ctx->sm_count, ctx->stream, do_pre, do_sym, &launches);

@@ -1,0 +1,661 @@
+// demod_packet.cu -- the whole demodulator in ONE launch, one CTA per packet (SF 7..12, osr == 1):
+// lora_demodulate (LoRaDemod.cpp:50-197) and demodulate (phy.cpp:182-243) for a batch.
+//
+// The reference walks a packet three times: max-abs scan of every sample (:61-68), the
+// two-symbol CFO/STO estimator (:80-136), then the per-symbol loop (:142-176) whose inputs
+// (1/max scale, rate, t_off) come from the first two.  Here a persistent CTA owns one packet at
+// a time and runs the three walks back to back as three phases:
+//
+//   A  scan      all 256 threads stream the packet with 128-bit loads -> max(|re|,|im|) -> scale
+//   B  estimate  symbols 0 and 1 in parallel on two thread groups (full-twiddle exact FFT, peak,
+//                fIndex, atan2f phase), combined in symbol order by thread 0 -> cfo, time_offset,
+//                rate, t_off
+//   C  symbols   every symbol window of the packet (sync symbols included) through the streaming
+//                pipelines of demod_stream.cu: bulk asynchronous copy global -> shared one unit
+//                ahead, normalise -> [downchirp] -> CFO rotation -> [Hann], exact-order FFT in
+//                place, first-max argmax -> uint16
+//
+// Why this shape: the per-sample chain is issue-bound (glibc-exact sincosf in FP64), the scan is
+// HBM-bound.  Three CTAs are resident per SM and drift out of step, so one CTA's scan streams
+// from HBM while its neighbours' symbol phases fill the issue slots -- the scan costs no time of
+// its own.  Phase A leaves the packet in L2 (a CTA's packet x 444 resident CTAs is 30 MB at SF7 /
+// 66 symbols, far below the 126 MB L2), so phases B and C are served by L2 and HBM sees every IQ
+// byte once; packets too long for that (SF12: 4.3 MB each) read HBM twice, which the issue-bound
+// phase C still hides.
+#include "stream_common.cuh"
+#include "internal.h"
+
+namespace lk {
+
+struct EstSym { int idx; float fi; float phase; uint32_t t; };
+
+struct PktShared {
+    float redf[8];
+    EstSym est[2];
+    PacketState st;
+    int sw[2];
+    int status;
+    uint32_t run;
+};
+
+template <int SF>
+struct PacketCfg : StreamCfg<SF> {
+    using B = StreamCfg<SF>;
+    static constexpr size_t sh_off = (B::bytes + 15) & ~(size_t)15;
+    static constexpr size_t bytes = sh_off + sizeof(PktShared);
+};
+
+__device__ __forceinline__ float amp_of(float re, float im)      // LoRaDemod.cpp:63-66
+{
+    const float r = fabsf(re), i = fabsf(im);
+    return (r < i) ? i : r;
+}
+
+template <int SF, bool EXTRA>
+__global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_packet_kernel(const DemodArgs a)
+{
+    using C = PacketCfg<SF>;
+    using P = fx::Plan<SF>;
+    constexpr int T = C::T, N = C::N, GD = C::GD;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int dom = threadIdx.x / C::DOM_THREADS;
+    const int dt = threadIdx.x % C::DOM_THREADS;
+    const int gq = dt / T, tid = dt % T;
+    const int g = threadIdx.x / T;                 // CTA-wide group number (phase B)
+
+    cf* slots = reinterpret_cast<cf*>(smem_raw) + (size_t)dom * C::STAGES * C::SLOT;
+    WinDesc* descs = reinterpret_cast<WinDesc*>(smem_raw + C::slot_bytes) + (size_t)dom * C::STAGES * GD;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::slot_bytes + C::desc_bytes) + dom * C::STAGES;
+    Peak* red = reinterpret_cast<Peak*>(smem_raw + C::slot_bytes + C::desc_bytes + C::bar_bytes);
+    PktShared& sh = *reinterpret_cast<PktShared*>(smem_raw + C::sh_off);
+
+    if (dt == 0) {
+#pragma unroll
+        for (int s = 0; s < C::STAGES; ++s) ptx::mbar_init(&full[s], GD);
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+
+    int stage = 0;
+    unsigned phase_bits = 0;                       // bit s = parity the next wait on stage s expects
+
+    for (uint32_t pid = blockIdx.x; pid < a.n_packets; pid += gridDim.x) {
+        const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
+        const uint32_t count = a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet;
+        const uint32_t total = count / (uint32_t)N;
+        const bool have_sync = total >= 2;
+
+        // ---- phase A: max-abs scan, LoRaDemod.cpp:61-78 (legacy path only) ----------------------
+        float scale = 1.0f;
+        int flags = 0, status = 0;
+        if (a.mode == MODE_LEGACY) {
+            float m = 0.0f;
+            if ((reinterpret_cast<uintptr_t>(pkt) & 15) == 0) {
+                const float4* p4 = reinterpret_cast<const float4*>(pkt);
+                const uint32_t pairs = count >> 1;
+#pragma unroll 4
+                for (uint32_t j = threadIdx.x; j < pairs; j += CTA_THREADS) {
+                    const float4 q = __ldg(p4 + j);
+                    m = fmaxf(m, amp_of(q.x, q.y));
+                    m = fmaxf(m, amp_of(q.z, q.w));
+                }
+                if ((count & 1) && threadIdx.x == 0) {
+                    const cf x = ldg_cf(pkt + count - 1);
+                    m = fmaxf(m, amp_of(x.x, x.y));
+                }
+            } else {
+#pragma unroll 4
+                for (uint32_t j = threadIdx.x; j < count; j += CTA_THREADS) {
+                    const cf x = ldg_cf(pkt + j);
+                    m = fmaxf(m, amp_of(x.x, x.y));
+                }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+            if ((threadIdx.x & 31) == 0) sh.redf[threadIdx.x >> 5] = m;
+            __syncthreads();
+            m = sh.redf[0];
+#pragma unroll
+            for (int k = 1; k < CTA_THREADS / 32; ++k) m = fmaxf(m, sh.redf[k]);
+            if (m > 1.0f) {
+                if (a.no_scratch) { flags |= PS_SKIP; status = -34; /* -ERANGE, LoRaDemod.cpp:70-72 */ }
+                else { flags |= PS_NORM; scale = __fdiv_rn(1.0f, m); }
+            }
+        } else {
+            // phy.cpp:190-194 (argument checks; per packet when lengths are ragged)
+            if (count % (uint32_t)N != 0) { flags |= PS_SKIP; status = -22; }
+            else if (total < 2) { flags |= PS_SKIP; status = -34; }
+        }
+        const bool run = !(flags & PS_SKIP);
+        const bool norm = (flags & PS_NORM) != 0;
+        const uint32_t n_est = run ? (total < 2 ? total : 2u) : 0u;
+
+        // ---- phase B: estimator, LoRaDemod.cpp:80-136 / phy.cpp:93-147 (osr == 1) ------------------
+        // symbol s is handled by thread group s; groups own their window slots of stage 0 / 1 as
+        // exchange buffers (the ring is idle: no bulk copy is in flight between packets)
+        const bool est_here = (T > 32) ? (n_est > 0) : (n_est > 0 && (int)(threadIdx.x / 32) * 32 / T < 2);
+        if (est_here) {
+            cf* buf0 = slots + (size_t)gq * C::PITCH;
+            cf* buf1 = slots + (size_t)C::SLOT + (size_t)gq * C::PITCH;
+            int flip = 0;
+            constexpr int G = CTA_THREADS / T;
+            for (uint32_t s0 = 0; s0 < n_est; s0 += G) {       // G == 1 (SF12): two rounds
+                const uint32_t s = s0 + g;
+                const bool live = s < n_est;
+                cf v[P::R];
+                load_window<SF>(v, pkt + (size_t)(live ? s : 0) * N, tid, 1, live, norm, scale, nullptr, false, 0.0f, 0.0f,
+                                a.window);
+                fft_group<SF, true>(v, tid, a.tw, a.ct, buf0, buf1, flip);
+                const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+                cf* spec = flip ? buf1 : buf0;
+                flip ^= 1;
+#pragma unroll
+                for (int r = 0; r < P::R; ++r) spec[P::bin_of_reg(tid, r)] = v[r];
+                group_sync<T>();
+                if (tid == 0 && live) {
+                    const float fundamental = __fsqrt_rn(pk.val);
+                    const float p = fx::fsub(fx::fmul(20.0f, gm::log10f_g(fundamental)), a.power_scale);
+                    EstSym e; e.idx = 0; e.fi = 0.0f; e.phase = 0.0f; e.t = 0;
+                    cf best_bin = fx::mk(0.0f, 0.0f);
+                    if (p > -1e30f) {                              // LoRaDemod.cpp:101-108 with a single phase t = 0
+                        const cf l = spec[pk.idx > 0 ? pk.idx - 1 : N - 1];
+                        const cf r = spec[pk.idx < N - 1 ? pk.idx + 1 : 0];
+                        const float left = gm::hypotf_g(l.x, l.y), right = gm::hypotf_g(r.x, r.y);
+                        const double demon = (2.0 * (double)fundamental) - (double)right - (double)left;
+                        e.fi = (demon == 0.0) ? 0.0f : (float)(0.5 * (double)fx::fsub(right, left) / demon);
+                        e.idx = pk.idx;
+                        best_bin = spec[pk.idx];
+                    }
+                    e.phase = gm::atan2f_g(best_bin.y, best_bin.x);
+                    sh.est[s] = e;
+                }
+                group_sync<T>();                                   // spectrum read before the buffer is reused
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            PacketState st; st.scale = scale; st.rate = 0.0f; st.t_off = 0; st.flags = flags;
+            if (run) {
+                const float PI_F = 3.14159265358979323846f;
+                float sum_index = 0.0f, phase_diff = 0.0f, prev_phase = 0.0f;
+                unsigned sum_t = 0;
+                for (uint32_t s = 0; s < n_est; ++s) {
+                    const EstSym e = sh.est[s];
+                    sum_t += e.t;
+                    sum_index = fx::fadd(sum_index, fx::fadd((float)e.idx, e.fi));
+                    if (s > 0) {
+                        float d = fx::fsub(e.phase, prev_phase);
+                        while (d > PI_F) d = fx::fsub(d, 2.0f * PI_F);
+                        while (d < -PI_F) d = fx::fadd(d, 2.0f * PI_F);
+                        phase_diff = fx::fadd(phase_diff, d);
+                    }
+                    prev_phase = e.phase;
+                }
+                const float avg_index = __fdiv_rn(sum_index, (float)n_est);
+                const float cfo_coarse = __fdiv_rn(avg_index, (float)N);
+                float cfo_fine = 0.0f;
+                if (n_est > 1)
+                    cfo_fine = __fdiv_rn(__fdiv_rn(phase_diff, (float)(n_est - 1)), fx::fmul(2.0f * PI_F, (float)N));
+                const float cfo = fx::fadd(cfo_coarse, cfo_fine);
+                const float frac = fx::fsub(avg_index, floorf(fx::fadd(avg_index, 0.5f)));
+                const float avg_t = __fdiv_rn((float)sum_t, (float)n_est);
+                const float toff = fx::fsub(avg_t, fx::fmul(fx::fmul(frac, (float)N), 1.0f));
+                if (a.cfo) a.cfo[pid] = cfo;
+                if (a.time_offset) a.time_offset[pid] = toff;
+                st.t_off = (int)roundf(toff);
+                st.rate = __fdiv_rn(fx::fmul(-2.0f * PI_F, cfo), (float)N);
+                status = have_sync ? (int)(total - 2) : (int)total;
+            }
+            sh.st = st;
+            sh.sw[0] = 0; sh.sw[1] = 0;
+            sh.status = status;
+            sh.run = run ? 1u : 0u;
+        }
+        ptx::fence_proxy_async();      // phase-B generic-proxy writes to the ring precede phase-C bulk copies
+        __syncthreads();
+
+        // ---- phase C: every symbol of the packet, LoRaDemod.cpp:142-176 / phy.cpp:204-238 -----------
+        if (run) {
+            const PacketState st = sh.st;
+            const uint32_t n_units = (total + GD - 1) / GD;
+
+            auto prefetch = [&](uint32_t u, int stg) {
+                if (tid != 0) return;
+                WinDesc d;
+                d.scale = st.scale; d.rate = st.rate; d.start = 0.0f; d.flags = 0; d.out_off = 0; d.aux0 = 0; d.aux1 = 0;
+                const uint32_t s = u * GD + gq;
+                cf* win = slots + (size_t)stg * C::SLOT + (size_t)gq * C::PITCH;
+                if (s < total) {
+                    const uint32_t base = shifted_base(s, (uint32_t)N, st.t_off, count);   // LoRaDemod.cpp:143-150
+                    const cf* src = pkt + base;
+                    d.start = start_phase(st.rate, s, (uint32_t)N, st.t_off);
+                    d.flags = WD_ACTIVE;
+                    if (phases_need_slow_path(d.start, fx::fadd(d.start, fx::fmul(st.rate, (float)(N - 1))))) d.flags |= WD_SLOW;
+                    if (window_is_odd(src)) d.flags |= WD_ODD;
+                    d.aux0 = s;
+                    descs[stg * GD + gq] = d;
+                    fetch_window<N>(win, src, &full[stg]);
+                } else {
+                    descs[stg * GD + gq] = d;
+                    ptx::mbar_arrive(&full[stg]);
+                }
+            };
+
+            uint32_t u = (uint32_t)dom;
+            if (u < n_units) prefetch(u, stage);
+            while (u < n_units) {
+                const uint32_t u_next = u + C::DOMS;
+                if (u_next < n_units) prefetch(u_next, stage ^ 1);
+
+                ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+
+                const WinDesc d = descs[stage * GD + gq];
+                cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
+                const bool active = (d.flags & WD_ACTIVE) != 0;
+                cf v[P::R];
+                if (active) {
+                    chain_window<SF, EXTRA>(v, win + ((d.flags & WD_ODD) ? 1 : 0) + tid, tid, d.scale, d.rate, d.start,
+                                            (d.flags & WD_SLOW) != 0, a.down, a.window);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < P::R; ++c) v[c] = fx::mk(0.0f, 0.0f);
+                }
+                fft_inplace<SF, false>(v, tid, a.tw, a.ct, win);
+                const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+                if (tid == 0 && active) {
+                    const uint32_t s = d.aux0;
+                    if (have_sync && s < 2) sh.sw[s] = pk.idx;
+                    else a.symbols[(size_t)pid * a.symbol_stride + (have_sync ? s - 2 : s)] = (uint16_t)pk.idx;
+                }
+                ptx::fence_proxy_async();     // our generic-proxy stores to the slot precede the next bulk copy into it
+                domain_sync<SF>();
+                u = u_next;
+                stage ^= 1;
+            }
+        }
+        __syncthreads();
+
+        // ---- bookkeeping: LoRaDemod.cpp:166-196 ----------------------------------------------------------
+        if (threadIdx.x == 0) {
+            if (a.sync) {
+                const unsigned shift = SF > 4 ? SF - 4 : 0;
+                a.sync[pid] = (run && have_sync) ? (uint8_t)((((sh.sw[0] >> shift) & 0xf) << 4) | ((sh.sw[1] >> shift) & 0xf)) : 0;
+            }
+            if (a.status) a.status[pid] = sh.status;
+        }
+        __syncthreads();                       // sh and the ring are free for the next packet
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// SF 7..9: one WARP per packet, single pass, speculative scale.
+//
+// A window needs T = N/16 <= 32 threads, so a warp is a complete pipeline (demod_stream.cu) and can
+// own a packet without any CTA-level barrier.  The reference's first walk (max-abs, LoRaDemod.cpp
+// :61-68) only matters when some |re| or |im| exceeds 1: the warp therefore demodulates the packet
+// assuming it does not (scale = 1, which multiplies exactly), tracks the running max of the samples
+// it streams anyway, and only if the max turns out to exceed 1 walks the packet a second time with
+// the now known 1/max (clean unit-amplitude IQ: about 1 % of SF7 packets, whose second walk is
+// served by L2).  HBM sees every IQ byte of a packet once; the estimator's serial epilogue stalls
+// one warp of 24 per SM, not a CTA.
+//   E units  the first min(total, 2) symbols, raw: full-twiddle exact FFT in place, peak, fIndex,
+//            phase -> cfo, time_offset, rate, t_off (LoRaDemod.cpp:80-136 / phy.cpp:93-147)
+//   C units  every symbol of the packet, sync symbols included (LoRaDemod.cpp:142-176)
+// ---------------------------------------------------------------------------------------------
+struct WarpShared { EstSym est[2]; int sw[2]; };
+
+template <int SF>
+struct WarpCfg : StreamCfg<SF> {
+    using B = StreamCfg<SF>;
+    static_assert(B::T <= 32, "warp-owned packets need a window per warp");
+    static constexpr size_t ws_off = (B::bytes + 15) & ~(size_t)15;
+    static constexpr size_t bytes = ws_off + (size_t)B::DOMS * sizeof(WarpShared);
+};
+
+__device__ __forceinline__ float warp_max(float m)
+{
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+    return m;
+}
+
+// max over [0, count) of max(|re|,|im|) with one warp: 128-bit loads, eight in flight per lane
+__device__ __forceinline__ float warp_scan_max(const cf* __restrict__ pkt, uint32_t count, int lane)
+{
+    float m = 0.0f;
+    uint32_t head = 0;
+    if ((reinterpret_cast<uintptr_t>(pkt) & 15) != 0 && count > 0) {        // odd start: peel one sample
+        if (lane == 0) { const cf x = ldg_cf(pkt); m = fmaxf(m, amp_of(x.x, x.y)); }
+        head = 1;
+    }
+    const float4* p4 = reinterpret_cast<const float4*>(pkt + head);
+    const uint32_t pairs = (count - head) >> 1;
+#pragma unroll 8
+    for (uint32_t j = lane; j < pairs; j += 32) {
+        const float4 q = __ldg(p4 + j);
+        m = fmaxf(m, amp_of(q.x, q.y));
+        m = fmaxf(m, amp_of(q.z, q.w));
+    }
+    if (((count - head) & 1) && lane == 0) { const cf x = ldg_cf(pkt + count - 1); m = fmaxf(m, amp_of(x.x, x.y)); }
+    return warp_max(m);
+}
+
+template <int SF, bool EXTRA>
+__global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_kernel(const DemodArgs a)
+{
+    using C = WarpCfg<SF>;
+    using P = fx::Plan<SF>;
+    constexpr int T = C::T, N = C::N, GD = C::GD;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int dom = threadIdx.x >> 5;              // DOM_THREADS == 32: a pipeline is a warp
+    const int lane = threadIdx.x & 31;
+    const int gq = lane / T, tid = lane % T;
+
+    cf* slots = reinterpret_cast<cf*>(smem_raw) + (size_t)dom * C::STAGES * C::SLOT;
+    WinDesc* descs = reinterpret_cast<WinDesc*>(smem_raw + C::slot_bytes) + (size_t)dom * C::STAGES * GD;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::slot_bytes + C::desc_bytes) + dom * C::STAGES;
+    Peak* red = reinterpret_cast<Peak*>(smem_raw + C::slot_bytes + C::desc_bytes + C::bar_bytes);   // unused for T <= 32
+    WarpShared& ws = reinterpret_cast<WarpShared*>(smem_raw + C::ws_off)[dom];
+
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < C::STAGES; ++s) ptx::mbar_init(&full[s], GD);
+        ptx::fence_mbar_init();
+    }
+    __syncwarp();
+
+    int stage = 0;
+    unsigned phase_bits = 0;
+    const uint32_t n_warps = gridDim.x * C::DOMS;
+    constexpr int DISTRUST_PACKETS = 4;
+    float pred_max = 0.0f;                         // max-abs of the last packet this warp saw
+    int distrust = 0;                              // packets left to scan first after a misprediction
+
+    for (uint32_t pid = blockIdx.x * C::DOMS + dom; pid < a.n_packets; pid += n_warps) {
+        const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
+        const uint32_t count = a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet;
+        const uint32_t total = count / (uint32_t)N;
+        const bool have_sync = total >= 2;
+        const bool legacy = a.mode == MODE_LEGACY;
+
+        int flags = 0, status = 0;
+        if (!legacy) {                                     // phy.cpp:190-194
+            if (count % (uint32_t)N != 0) { flags |= PS_SKIP; status = -22; }
+            else if (total < 2) { flags |= PS_SKIP; status = -34; }
+        }
+        float cfo = 0.0f, toff = 0.0f;
+        bool have_metrics = false;
+
+        // Which max-abs to demodulate with (LoRaDemod.cpp:61-78).  Trusting: the previous packet's max
+        // (batches are usually homogeneous: clean unit-amplitude IQ has the same max in every packet),
+        // verified against the max tracked during the walk.  Distrusting (after a miss, or when a
+        // packet above 1 must be refused): scan first with plain loads, then walk once.
+        float use_max = pred_max;
+        bool known = !legacy;
+        if (legacy && (distrust > 0 || a.no_scratch)) {
+            use_max = warp_scan_max(pkt, count, lane);
+            known = true;
+            if (distrust > 0) distrust = (use_max == pred_max) ? distrust - 1 : DISTRUST_PACKETS;
+            pred_max = use_max;
+        }
+
+        for (int attempt = 0; attempt < 2 && !(flags & PS_SKIP); ++attempt) {
+            float scale = 1.0f;
+            flags &= ~PS_NORM;
+            if (legacy && use_max > 1.0f) {
+                if (a.no_scratch) { flags |= PS_SKIP; status = -34; have_metrics = false; break; }   // LoRaDemod.cpp:70-72
+                flags |= PS_NORM;
+                scale = __fdiv_rn(1.0f, use_max);
+            }
+            const bool norm = (flags & PS_NORM) != 0;
+            const uint32_t n_est = total < 2 ? total : 2u;
+
+            // ---- E units ---------------------------------------------------------------------------
+            for (uint32_t s0 = 0; s0 < n_est; s0 += GD) {
+                const uint32_t s = s0 + gq;
+                const bool live = s < n_est;
+                cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
+                if (tid == 0) {
+                    WinDesc d;
+                    d.scale = scale; d.rate = 0.0f; d.start = 0.0f; d.flags = 0; d.out_off = 0; d.aux0 = s; d.aux1 = 0;
+                    if (live) {
+                        const cf* src = pkt + (size_t)s * N;
+                        d.flags = WD_ACTIVE | (window_is_odd(src) ? WD_ODD : 0);
+                        descs[stage * GD + gq] = d;
+                        fetch_window<N>(win, src, &full[stage]);
+                    } else {
+                        descs[stage * GD + gq] = d;
+                        ptx::mbar_arrive(&full[stage]);
+                    }
+                }
+                ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+                const WinDesc d = descs[stage * GD + gq];
+                cf v[P::R];
+                const cf* raw = win + ((d.flags & WD_ODD) ? 1 : 0) + tid;
+#pragma unroll
+                for (int c = 0; c < P::R; ++c) {
+                    cf x = fx::mk(0.0f, 0.0f);
+                    if (live) {
+                        x = raw[T * c];
+                        if (norm) x = fx::cscale(x, scale);                                  // LoRaDemod.cpp:75-77
+                        if (EXTRA && a.window) x = fx::cscale(x, __ldg(a.window + tid + T * c));
+                    }
+                    v[c] = x;
+                }
+                fft_inplace<SF, true>(v, tid, a.tw, a.ct, win);
+                const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+                __syncwarp();                              // last exchange fully read: the slot becomes the spectrum
+#pragma unroll
+                for (int r = 0; r < P::R; ++r) win[P::bin_of_reg(tid, r)] = v[r];
+                __syncwarp();
+                if (tid == 0 && live) {
+                    EstSym e; e.idx = 0; e.fi = 0.0f; e.phase = 0.0f; e.t = 0;
+                    cf best_bin = fx::mk(0.0f, 0.0f);
+                    // one sample phase (osr == 1): the candidate is kept iff its power beats -1e30 dB, i.e.
+                    // iff 20*log10f(sqrtf(max)) is not -inf: max > 0 (LoRaDemod.cpp:96-108, LoRaDetector.hpp:60-64)
+                    if (pk.val > 0.0f) {
+                        const float fundamental = __fsqrt_rn(pk.val);
+                        const cf l = win[pk.idx > 0 ? pk.idx - 1 : N - 1];
+                        const cf r = win[pk.idx < N - 1 ? pk.idx + 1 : 0];
+                        const float left = gm::hypotf_g(l.x, l.y), right = gm::hypotf_g(r.x, r.y);
+                        const double demon = (2.0 * (double)fundamental) - (double)right - (double)left;
+                        e.fi = (demon == 0.0) ? 0.0f : (float)(0.5 * (double)fx::fsub(right, left) / demon);
+                        e.idx = pk.idx;
+                        best_bin = win[pk.idx];
+                    }
+                    e.phase = gm::atan2f_g(best_bin.y, best_bin.x);
+                    ws.est[s] = e;
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                stage ^= 1;
+            }
+
+            // ---- combine (lane 0), LoRaDemod.cpp:126-139 ---------------------------------------------
+            float rate = 0.0f;
+            int t_off = 0;
+            if (lane == 0) {
+                const float PI_F = 3.14159265358979323846f;
+                float sum_index = 0.0f, phase_diff = 0.0f, prev_phase = 0.0f;
+                for (uint32_t s = 0; s < n_est; ++s) {
+                    const EstSym e = ws.est[s];
+                    sum_index = fx::fadd(sum_index, fx::fadd((float)e.idx, e.fi));
+                    if (s > 0) {
+                        float dd = fx::fsub(e.phase, prev_phase);
+                        while (dd > PI_F) dd = fx::fsub(dd, 2.0f * PI_F);
+                        while (dd < -PI_F) dd = fx::fadd(dd, 2.0f * PI_F);
+                        phase_diff = fx::fadd(phase_diff, dd);
+                    }
+                    prev_phase = e.phase;
+                }
+                const float avg_index = __fdiv_rn(sum_index, (float)n_est);
+                const float cfo_coarse = __fdiv_rn(avg_index, (float)N);
+                float cfo_fine = 0.0f;
+                if (n_est > 1)
+                    cfo_fine = __fdiv_rn(__fdiv_rn(phase_diff, (float)(n_est - 1)), fx::fmul(2.0f * PI_F, (float)N));
+                cfo = fx::fadd(cfo_coarse, cfo_fine);
+                const float frac = fx::fsub(avg_index, floorf(fx::fadd(avg_index, 0.5f)));
+                const float avg_t = __fdiv_rn(0.0f, (float)n_est);
+                toff = fx::fsub(avg_t, fx::fmul(frac, (float)N));
+                t_off = (int)roundf(toff);
+                rate = __fdiv_rn(fx::fmul(-2.0f * PI_F, cfo), (float)N);
+                ws.sw[0] = 0; ws.sw[1] = 0;
+            }
+            rate = __shfl_sync(0xffffffffu, rate, 0);
+            t_off = __shfl_sync(0xffffffffu, t_off, 0);
+            have_metrics = true;
+
+            // ---- C units --------------------------------------------------------------------------
+            const uint32_t n_units = (total + GD - 1) / GD;
+            float m = 0.0f;
+            auto prefetch = [&](uint32_t u, int stg) {
+                if (tid != 0) return;
+                WinDesc d;
+                d.scale = scale; d.rate = rate; d.start = 0.0f; d.flags = 0; d.out_off = 0; d.aux0 = 0; d.aux1 = 0;
+                const uint32_t s = u * GD + gq;
+                cf* win = slots + (size_t)stg * C::SLOT + (size_t)gq * C::PITCH;
+                if (s < total) {
+                    const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);       // LoRaDemod.cpp:143-150
+                    const cf* src = pkt + base;
+                    d.start = start_phase(rate, s, (uint32_t)N, t_off);
+                    d.flags = WD_ACTIVE;
+                    if (phases_need_slow_path(d.start, fx::fadd(d.start, fx::fmul(rate, (float)(N - 1))))) d.flags |= WD_SLOW;
+                    if (window_is_odd(src)) d.flags |= WD_ODD;
+                    d.aux0 = s;
+                    descs[stg * GD + gq] = d;
+                    fetch_window<N>(win, src, &full[stg]);
+                } else {
+                    descs[stg * GD + gq] = d;
+                    ptx::mbar_arrive(&full[stg]);
+                }
+            };
+            if (n_units) prefetch(0, stage);
+            for (uint32_t u = 0; u < n_units; ++u) {
+                if (u + 1 < n_units) prefetch(u + 1, stage ^ 1);
+                ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+                const WinDesc d = descs[stage * GD + gq];
+                cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
+                const bool active = (d.flags & WD_ACTIVE) != 0;
+                cf v[P::R];
+                if (active) {
+                    const cf* raw = win + ((d.flags & WD_ODD) ? 1 : 0) + tid;
+                    if (!known) {                                                            // LoRaDemod.cpp:61-68 on the fly
+#pragma unroll
+                        for (int c = 0; c < P::R; ++c) { const cf x = raw[T * c]; m = fmaxf(m, amp_of(x.x, x.y)); }
+                    }
+                    chain_window<SF, EXTRA>(v, raw, tid, d.scale, d.rate, d.start, (d.flags & WD_SLOW) != 0, a.down, a.window);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < P::R; ++c) v[c] = fx::mk(0.0f, 0.0f);
+                }
+                fft_inplace<SF, false>(v, tid, a.tw, a.ct, win);
+                const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+                if (tid == 0 && active) {
+                    const uint32_t s = d.aux0;
+                    if (have_sync && s < 2) ws.sw[s] = pk.idx;
+                    else a.symbols[(size_t)pid * a.symbol_stride + (have_sync ? s - 2 : s)] = (uint16_t)pk.idx;
+                }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                stage ^= 1;
+            }
+
+            // ---- verify the trusted max against the samples actually walked ------------------------------
+            if (known) break;
+            if (t_off != 0 || count != total * (uint32_t)N) {
+                // shifted windows / a trailing partial symbol leave samples the units did not stream: scan them all
+                m = warp_scan_max(pkt, count, lane);
+            } else {
+                m = warp_max(m);
+            }
+            const bool ok = (m > 1.0f) ? (m == use_max) : !(use_max > 1.0f);
+            pred_max = m;
+            if (ok) break;
+            use_max = m;                                   // second walk with the packet's own max
+            known = true;
+            distrust = DISTRUST_PACKETS;
+        }
+
+        // ---- bookkeeping: LoRaDemod.cpp:166-196 ----------------------------------------------------------
+        __syncwarp();
+        if (lane == 0) {
+            const bool run = !(flags & PS_SKIP);
+            if (run) status = have_sync ? (int)(total - 2) : (int)total;
+            if (have_metrics) {
+                if (a.cfo) a.cfo[pid] = cfo;
+                if (a.time_offset) a.time_offset[pid] = toff;
+            }
+            if (a.sync) {
+                const unsigned shift = SF > 4 ? SF - 4 : 0;
+                a.sync[pid] = (run && have_sync) ? (uint8_t)((((ws.sw[0] >> shift) & 0xf) << 4) | ((ws.sw[1] >> shift) & 0xf)) : 0;
+            }
+            if (a.status) a.status[pid] = status;
+        }
+        __syncwarp();
+    }
+}
+
+template <int SF>
+static cudaError_t launch_warp_sf(const DemodArgs& a, int sm_count, cudaStream_t stream)
+{
+    using C = WarpCfg<SF>;
+    const bool extra = a.down != nullptr || a.window != nullptr;
+    static bool attr_done[64] = { false };
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_done[dev & 63]) {
+        cudaFuncSetAttribute(demod_warp_kernel<SF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        cudaFuncSetAttribute(demod_warp_kernel<SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        attr_done[dev & 63] = true;
+    }
+    const unsigned max_ctas = (unsigned)sm_count * STREAM_CTAS_PER_SM;    // persistent grid: every CTA resident
+    const unsigned need = (a.n_packets + C::DOMS - 1) / C::DOMS;
+    const unsigned grid = need < max_ctas ? need : max_ctas;
+    if (extra) demod_warp_kernel<SF, true><<<grid, CTA_THREADS, C::bytes, stream>>>(a);
+    else demod_warp_kernel<SF, false><<<grid, CTA_THREADS, C::bytes, stream>>>(a);
+    return cudaGetLastError();
+}
+
+template <int SF>
+static cudaError_t launch_packet_sf(const DemodArgs& a, int sm_count, cudaStream_t stream)
+{
+    using C = PacketCfg<SF>;
+    const bool extra = a.down != nullptr || a.window != nullptr;
+    static bool attr_done[64] = { false };
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_done[dev & 63]) {
+        cudaFuncSetAttribute(demod_packet_kernel<SF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        cudaFuncSetAttribute(demod_packet_kernel<SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        attr_done[dev & 63] = true;
+    }
+    const unsigned max_ctas = (unsigned)sm_count * STREAM_CTAS_PER_SM;    // persistent grid: every CTA resident
+    const unsigned grid = a.n_packets < max_ctas ? a.n_packets : max_ctas;
+    if (extra) demod_packet_kernel<SF, true><<<grid, CTA_THREADS, C::bytes, stream>>>(a);
+    else demod_packet_kernel<SF, false><<<grid, CTA_THREADS, C::bytes, stream>>>(a);
+    return cudaGetLastError();
+}
+
+bool packet_supported(int sf, const DemodArgs& a)
+{
+    return sf >= 7 && sf <= 12 && a.osr == 1 && (a.mode == MODE_LEGACY || a.mode == MODE_HIGHLEVEL) &&
+           (unsigned long long)a.samples_per_packet < 0xf0000000ull;
+}
+
+cudaError_t launch_demod_packet(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream)
+{
+    switch (sf) {
+    case 7: return launch_warp_sf<7>(a, sm_count, stream);
+    case 8: return launch_warp_sf<8>(a, sm_count, stream);
+    case 9: return launch_warp_sf<9>(a, sm_count, stream);
+    case 10: return launch_packet_sf<10>(a, sm_count, stream);
+    case 11: return launch_packet_sf<11>(a, sm_count, stream);
+    case 12: return launch_packet_sf<12>(a, sm_count, stream);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+} // namespace lk

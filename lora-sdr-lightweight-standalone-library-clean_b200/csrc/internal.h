@@ -33,6 +33,9 @@ cudaError_t launch_detect(int sf, const DetectArgs& a, int sm_count, cudaStream_
 // demod_stream.cu: TMA-staged data-symbol kernel (SF 7..12, osr == 1)
 bool stream_supported(int sf, const DemodArgs& a);
 cudaError_t launch_symbols_stream(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
+// demod_packet.cu: one CTA per packet, scan -> estimator -> symbols in one launch (SF 7..12, osr == 1)
+bool packet_supported(int sf, const DemodArgs& a);
+cudaError_t launch_demod_packet(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
 // demod_fused.cu: scan + estimator + sync + data symbols in one persistent launch (SF 7..12, osr == 1)
 bool fused_plan(int sf, const DemodArgs& a, uint32_t lookahead_bytes, FusedArgs* f);
 cudaError_t launch_demod_fused(int sf, const FusedArgs& f, int sm_count, cudaStream_t stream);

@@ -340,3 +340,49 @@ def test_fused_launch_ragged_and_scratch(phy, lp, oracle):
     check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_FUSED)
     counts = np.array([0, 128, 256, 128 * 5 + 17, 128 * 8], dtype=np.uint32)
     check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_FUSED, counts=counts)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
+@pytest.mark.parametrize("kind", ["clean", "noisy", "noise", "loud"])
+def test_two_kernel_path_parity(phy, lp, oracle, sf, kind):
+    """The older prepass + symbols kernel pair (F_TWO_KERNEL) stays bit-exact too (A/B path of bench.py)."""
+    rng = np.random.default_rng(900 + sf)
+    iq = make_packets(oracle, rng, sf, 1, 5, 6, kind="clean" if kind == "loud" else kind, amp=1.0)
+    if kind == "loud":
+        iq = (iq * np.float32(2.5)).astype(np.complex64)
+    check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_TWO_KERNEL)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf", [7, 9, 10, 12])
+def test_packet_kernel_ragged_loud_and_unaligned(phy, lp, oracle, sf):
+    """Default single-launch path on the awkward cases: ragged sample counts (trailing partial symbol,
+    fewer than two symbols, empty), amplitudes above 1 (normalised) with and without scratch, Hann window,
+    odd (8-byte) packet alignment, more packets than resident CTAs."""
+    import torch
+    rng = np.random.default_rng(950 + sf)
+    N = 1 << sf
+    n_pkt = 7 if sf >= 10 else 600
+    iq = make_packets(oracle, rng, sf, 1, 4, 5, kind="noisy")
+    iq = np.concatenate([iq, (iq[:3] * np.float32(3.0)).astype(np.complex64)])
+    reps = (n_pkt + iq.shape[0] - 1) // iq.shape[0]
+    iq = np.ascontiguousarray(np.tile(iq, (reps, 1))[:n_pkt])
+    counts = rng.integers(0, iq.shape[1] + 1, n_pkt).astype(np.uint32)
+    counts[:6] = [iq.shape[1], 0, N - 1, N, 2 * N, 2 * N + 5]
+    for window in (0, 1):
+        for flags in (0, lp.F_NO_SCRATCH):
+            check_legacy(phy, lp, oracle, iq, sf, 1, window, flags=flags, counts=counts)
+    # odd alignment: packet rows start 8 bytes after a 16-byte boundary (stride odd)
+    P, S = 5, iq.shape[1]
+    buf = torch.zeros(P * (S + 1) + 1, dtype=torch.complex64, device=phy.device)
+    view = buf[1:1 + P * (S + 1)].view(P, S + 1)
+    view[:, :S] = to_dev(phy, iq[:P])
+    cfg = lp.make_cfg(sf)
+    out = phy.demodulate_batch(cfg, view, samples_per_packet=S)
+    phy.synchronize()
+    for p in range(P):
+        r, s_, sync, cfo, to = oracle.lora_demodulate(iq[p], sf)
+        assert int(out["status"][p]) == r and int(out["sync"][p]) == sync
+        assert np.array_equal(out["symbols"][p, :r].cpu().numpy(), s_)
+        assert out["cfo"][p].cpu().numpy().tobytes() == cfo.tobytes()
