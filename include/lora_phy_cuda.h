@@ -120,6 +120,16 @@ int lora_phy_cuda_compensate_offsets_batch(lora_phy_cuda_ctx* ctx, const lora_ph
                                            size_t samples_per_packet, size_t n_packets,
                                            const float* d_cfo, const float* d_time_offset);
 
+/* HOST-buffer variants of the two calls above (stage, run, copy back, synchronise). */
+int lora_phy_cuda_estimate_offsets_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                              const void* h_iq, size_t packet_stride,
+                                              size_t samples_per_packet, size_t n_packets,
+                                              float* h_cfo, float* h_time_offset);
+int lora_phy_cuda_compensate_offsets_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                                void* h_iq, size_t packet_stride,
+                                                size_t samples_per_packet, size_t n_packets,
+                                                const float* h_cfo, const float* h_time_offset);
+
 /* One N-point window per row through the detector (LoRaDetector.hpp:39-74): spectrum (may be
  * NULL), first-max index, power, powerAvg and fIndex.  Used by the parity tests.           */
 int lora_phy_cuda_detect_batch(lora_phy_cuda_ctx* ctx, uint32_t sf, const void* d_windows,

@@ -63,6 +63,8 @@ SIGNATURES = {
     "lora_phy_cuda_demodulate_batch_host": (C.c_int, [_vp, _cfgp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_estimate_offsets_batch": (C.c_int, [_vp, _cfgp, _vp, _sz, _vp, _sz, _sz, _vp, _vp]),
     "lora_phy_cuda_compensate_offsets_batch": (C.c_int, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _vp]),
+    "lora_phy_cuda_estimate_offsets_batch_host": (C.c_int, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _vp]),
+    "lora_phy_cuda_compensate_offsets_batch_host": (C.c_int, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _vp]),
     "lora_phy_cuda_detect_batch": (C.c_int, [_vp, _u32, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_modulate_batch": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_modulate_batch_host": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),

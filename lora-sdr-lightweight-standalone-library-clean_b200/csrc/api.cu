@@ -383,6 +383,58 @@ int lora_phy_cuda_compensate_offsets_batch(lora_phy_cuda_ctx* ctx, const lora_ph
     return 0;
 }
 
+int lora_phy_cuda_estimate_offsets_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const void* h_iq,
+                                              size_t packet_stride, size_t spp, size_t n_packets, float* h_cfo,
+                                              float* h_to)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if (!h_iq || !h_cfo || !h_to) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
+    if (!n_packets) return 0;
+    Guard g(ctx->device);
+    const size_t iq_bytes = n_packets * packet_stride * sizeof(cf);
+    CK(ctx->d_in.reserve(iq_bytes + 16));
+    CK(ctx->d_out.reserve(n_packets * 8));
+    CK(cudaMemcpyAsync(ctx->d_in.p, h_iq, iq_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    float* d_cfo = static_cast<float*>(ctx->d_out.p);
+    float* d_to = d_cfo + n_packets;
+    // packets without a whole symbol leave the outputs untouched (phy.cpp:84-90): seed them with the caller's values
+    CK(cudaMemcpyAsync(d_cfo, h_cfo, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_to, h_to, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
+    rc = lora_phy_cuda_estimate_offsets_batch(ctx, cfg, ctx->d_in.p, packet_stride, nullptr, spp, n_packets, d_cfo, d_to);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_cfo, d_cfo, n_packets * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(h_to, d_to, n_packets * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int lora_phy_cuda_compensate_offsets_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, void* h_iq,
+                                                size_t packet_stride, size_t spp, size_t n_packets,
+                                                const float* h_cfo, const float* h_to)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if (!h_iq || !h_cfo || !h_to) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
+    if (!n_packets || !spp) return 0;
+    Guard g(ctx->device);
+    const size_t iq_bytes = n_packets * packet_stride * sizeof(cf);
+    CK(ctx->d_in.reserve(iq_bytes + 16));
+    CK(ctx->d_aux.reserve(n_packets * 8));
+    float* d_cfo = static_cast<float*>(ctx->d_aux.p);
+    float* d_to = d_cfo + n_packets;
+    CK(cudaMemcpyAsync(ctx->d_in.p, h_iq, iq_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_cfo, h_cfo, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_to, h_to, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
+    rc = lora_phy_cuda_compensate_offsets_batch(ctx, cfg, ctx->d_in.p, packet_stride, spp, n_packets, d_cfo, d_to);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_iq, ctx->d_in.p, iq_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
 int lora_phy_cuda_detect_batch(lora_phy_cuda_ctx* ctx, uint32_t sf, const void* d_windows, size_t n_windows,
                                void* d_spectrum, uint32_t* d_index, float* d_power, float* d_power_avg,
                                float* d_findex)
