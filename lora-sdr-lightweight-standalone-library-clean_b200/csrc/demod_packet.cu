@@ -254,13 +254,10 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_packet_
                 cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
                 const bool active = (d.flags & WD_ACTIVE) != 0;
                 cf v[P::R];
-                if (active) {
-                    chain_window<SF, EXTRA>(v, win + ((d.flags & WD_ODD) ? 1 : 0) + tid, tid, d.scale, d.rate, d.start,
-                                            (d.flags & WD_SLOW) != 0, a.down, a.window);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < P::R; ++c) v[c] = fx::mk(0.0f, 0.0f);
-                }
+                // an inactive window (past the packet's last symbol) runs the same code on whatever its slot
+                // holds: the result is discarded, and no register zeroing / branch sits in the hot path
+                chain_window<SF, EXTRA>(v, win + ((d.flags & WD_ODD) ? 1 : 0) + tid, tid, d.scale, d.rate, d.start,
+                                        (d.flags & WD_SLOW) != 0, a.down, a.window);
                 fft_inplace<SF, false>(v, tid, a.tw, a.ct, win);
                 const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
                 if (tid == 0 && active) {
@@ -508,53 +505,46 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
             have_metrics = true;
 
             // ---- C units --------------------------------------------------------------------------
+            // No descriptors in shared memory: every lane derives its window's base / start phase / path from
+            // (rate, t_off, s) in registers; the window's leader only issues the bulk copy one unit ahead.
             const uint32_t n_units = (total + GD - 1) / GD;
             float m = 0.0f;
+            bool suspicious = false;                       // a window whose spectrum had no positive bin (NaN / all-zero input)
+            const bool odd_pkt = window_is_odd(pkt);       // N is even: every window of the packet shares the parity unless shifted
             auto prefetch = [&](uint32_t u, int stg) {
                 if (tid != 0) return;
-                WinDesc d;
-                d.scale = scale; d.rate = rate; d.start = 0.0f; d.flags = 0; d.out_off = 0; d.aux0 = 0; d.aux1 = 0;
                 const uint32_t s = u * GD + gq;
-                cf* win = slots + (size_t)stg * C::SLOT + (size_t)gq * C::PITCH;
                 if (s < total) {
                     const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);       // LoRaDemod.cpp:143-150
-                    const cf* src = pkt + base;
-                    d.start = start_phase(rate, s, (uint32_t)N, t_off);
-                    d.flags = WD_ACTIVE;
-                    if (phases_need_slow_path(d.start, fx::fadd(d.start, fx::fmul(rate, (float)(N - 1))))) d.flags |= WD_SLOW;
-                    if (window_is_odd(src)) d.flags |= WD_ODD;
-                    d.aux0 = s;
-                    descs[stg * GD + gq] = d;
-                    fetch_window<N>(win, src, &full[stg]);
+                    fetch_window<N>(slots + (size_t)stg * C::SLOT + (size_t)gq * C::PITCH, pkt + base, &full[stg]);
                 } else {
-                    descs[stg * GD + gq] = d;
                     ptx::mbar_arrive(&full[stg]);
                 }
             };
             if (n_units) prefetch(0, stage);
             for (uint32_t u = 0; u < n_units; ++u) {
                 if (u + 1 < n_units) prefetch(u + 1, stage ^ 1);
+                const uint32_t s = u * GD + gq;
+                const bool active = s < total;
+                const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);
+                const bool odd = odd_pkt != ((base & 1u) != 0);
+                const float start = start_phase(rate, s, (uint32_t)N, t_off);           // LoRaDemod.cpp:152-153
+                const bool slow = phases_need_slow_path(start, fx::fadd(start, fx::fmul(rate, (float)(N - 1))));
                 ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
                 phase_bits ^= 1u << stage;
-                const WinDesc d = descs[stage * GD + gq];
                 cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
-                const bool active = (d.flags & WD_ACTIVE) != 0;
                 cf v[P::R];
-                if (active) {
-                    const cf* raw = win + ((d.flags & WD_ODD) ? 1 : 0) + tid;
-                    if (!known) {                                                            // LoRaDemod.cpp:61-68 on the fly
-#pragma unroll
-                        for (int c = 0; c < P::R; ++c) { const cf x = raw[T * c]; m = fmaxf(m, amp_of(x.x, x.y)); }
-                    }
-                    chain_window<SF, EXTRA>(v, raw, tid, d.scale, d.rate, d.start, (d.flags & WD_SLOW) != 0, a.down, a.window);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < P::R; ++c) v[c] = fx::mk(0.0f, 0.0f);
-                }
+                const cf* raw = win + (odd ? 1 : 0) + tid;
+                // an inactive window (past the packet's last symbol) runs the same code on whatever its slot
+                // holds: the result is discarded, and no register zeroing / branch sits in the hot path
+                float mw = 0.0f;
+                if (!known) chain_window<SF, EXTRA, true>(v, raw, tid, scale, rate, start, slow, a.down, a.window, &mw);
+                else chain_window<SF, EXTRA, false>(v, raw, tid, scale, rate, start, slow, a.down, a.window);
+                if (active) m = fmaxf(m, mw);
                 fft_inplace<SF, false>(v, tid, a.tw, a.ct, win);
                 const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
                 if (tid == 0 && active) {
-                    const uint32_t s = d.aux0;
+                    if (!(pk.val > 0.0f)) suspicious = true;
                     if (have_sync && s < 2) ws.sw[s] = pk.idx;
                     else a.symbols[(size_t)pid * a.symbol_stride + (have_sync ? s - 2 : s)] = (uint16_t)pk.idx;
                 }
@@ -565,8 +555,9 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
 
             // ---- verify the trusted max against the samples actually walked ------------------------------
             if (known) break;
-            if (t_off != 0 || count != total * (uint32_t)N) {
-                // shifted windows / a trailing partial symbol leave samples the units did not stream: scan them all
+            if (t_off != 0 || count != total * (uint32_t)N || __any_sync(0xffffffffu, suspicious)) {
+                // shifted windows / a trailing partial symbol leave samples the units did not stream, and NaN samples
+                // are invisible to the tracked max: scan the packet with the reference's own comparison
                 m = warp_scan_max(pkt, count, lane);
             } else {
                 m = warp_max(m);

@@ -153,22 +153,58 @@ GM_HD void sc_assemble(float ps, float pc, unsigned n, unsigned m, float* sn, fl
 // Core of the |y| < 120 path: reduction + both polynomials + quadrant assembly.  For
 // |y| < pi/4 the reduction yields n = 0 and x unchanged, so glibc's separate small-argument
 // branch computes the same thing.  NOT valid for |y| < 2^-12 (glibc returns (y, 1.0f) there).
+//
+// glibc's reduce_fast computes n = ((int32_t)(x * hpi_inv) + 0x800000) >> 24 (truncate, bias, floor)
+// and x - n * hpi.  Here the quadrant comes from the magic-number trick instead: adding 1.5 * 2^76
+// rounds q = x * hpi_inv to the nearest multiple of 2^24 (ulp of that binade), leaves n in the low
+// mantissa bits and n * 2^24 after subtracting the constant again -- two DADDs instead of
+// F2I + IADD + SHF + I2F, and no trip through the conversion pipe.  Round-to-nearest-even differs
+// from glibc's truncate-and-bias only for q within 1 of a half-way point; tests/cpu/test_glibc_math.cpp
+// walks ALL floats with 2^-12 <= |y| < 120 (both signs): sin and cos are bit-identical to glibc for
+// every one of them (0 mismatches), so the substitution is exact on the domain this core is used on.
+GM_HD uint32_t d_lo32(double d) {
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)__double2loint(d);
+#else
+    union { double d; uint64_t u; } v; v.d = d; return (uint32_t)v.u;
+#endif
+}
+GM_HD double dadd(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dadd_rn(a, b);
+#else
+    return a + b;
+#endif
+}
+// a ^ (b & 0x80000000): one LOP3 on the device
+GM_HD uint32_t xor_signbit_of(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, 0x80000000, 0x78;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+#else
+    return a ^ (b & 0x80000000u);
+#endif
+}
+
 GM_HD void sincosf_core(float y, float* sn, float* cs)
 {
     const double x = (double)y;
     const double q = dmul(x, sc_hpi_inv());
-    const int n = ((int32_t)q + 0x800000) >> 24;
-    const double xr = dfma(-(double)n, sc_hpi(), x);
+    const double magic = 0x1.8p76;
+    const double t = dadd(q, magic);
+    const uint32_t n = d_lo32(t);                         // quadrant (mod 2^32)
+    const double nd = dadd(t, -magic);                    // n * 2^24, exact
+    const double xr = dfma(-nd, 0x1.921FB54442D18p-24, x); // x - n * pi/2, one rounding like glibc's FMA build
     const double x2 = dmul(xr, xr);
     const float ps = (float)sc_sin_poly(xr, x2);
     const float pc = (float)sc_cos_poly(x2);
-    // sc_assemble with m == n, written for few instructions: bit 31 of t is bit 1 of n
-    const uint32_t t = (uint32_t)n << 30;
-    const uint32_t S = f2u(ps) ^ ((t + 0x40000000u) & 0x80000000u);
-    const uint32_t Cc = f2u(pc) ^ (t & 0x80000000u);
-    const bool odd = (n & 1) != 0;
-    *sn = u2f(odd ? Cc : S);
-    *cs = u2f(odd ? S : Cc);
+    // sc_assemble with m == n: sin = odd ? pc : ps with sign bit1(n); cos = odd ? ps : pc with sign bit1(n + 1)
+    const uint32_t t30 = n << 30;
+    const bool odd = (n & 1u) != 0;
+    const uint32_t a = f2u(odd ? pc : ps), b = f2u(odd ? ps : pc);
+    *sn = u2f(xor_signbit_of(a, t30));
+    *cs = u2f(xor_signbit_of(b, t30 + 0x40000000u));
 }
 
 // |y| < 120, any magnitude: the core plus glibc's tiny-argument result.

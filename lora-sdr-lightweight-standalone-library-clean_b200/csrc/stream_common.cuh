@@ -82,18 +82,24 @@ __device__ __forceinline__ bool phases_need_slow_path(float start, float last)
 
 // Per-sample chain of one data / sync window held in shared memory (LoRaDemod.cpp:154-163,
 // phy.cpp:220-231): normalise -> [downchirp] -> CFO rotation -> [Hann], into pass-0 register order.
-template <int SF, bool EXTRA>
+template <int SF, bool EXTRA, bool TRACK = false>
 __device__ __forceinline__ void chain_window(cf (&v)[fx::Plan<SF>::R], const cf* raw /* window + tid */, int tid,
                                              float scale, float rate, float start, bool slow,
-                                             const cf* __restrict__ down, const float* __restrict__ w)
+                                             const cf* __restrict__ down, const float* __restrict__ w,
+                                             float* track = nullptr)
 {
     using P = fx::Plan<SF>;
     constexpr int T = P::T;
     const float fi0 = (float)tid;
     if (!slow) {
+        float m = TRACK ? *track : 0.0f;
 #pragma unroll
         for (int c = 0; c < P::R; ++c) {
-            cf x = fx::cscale2(raw[T * c], scale);                                   // LoRaDemod.cpp:75-77
+            const cf r = raw[T * c];
+            // running max(|re|,|im|) of the raw samples (LoRaDemod.cpp:61-68) for finite data: one FMNMX3.
+            // NaN samples are ignored here; the caller detects them through the poisoned spectrum.
+            if (TRACK) m = fmaxf(fmaxf(m, fabsf(r.x)), fabsf(r.y));
+            cf x = fx::cscale2(r, scale);                                            // LoRaDemod.cpp:75-77
             if (EXTRA && down) x = fx::cmul(x, ldg_cf(down + tid + T * c));          // phy.cpp:224
             const float ph = fx::fadd(start, fx::fmul(rate, fx::fadd(fi0, (float)(T * c))));
             float sn, cs;
@@ -102,17 +108,22 @@ __device__ __forceinline__ void chain_window(cf (&v)[fx::Plan<SF>::R], const cf*
             if (EXTRA && w) x = fx::cscale(x, __ldg(w + tid + T * c));               // LoRaDemod.cpp:160-161
             v[c] = x;
         }
+        if (TRACK) *track = m;
     } else {
+        float m = TRACK ? *track : 0.0f;
 #pragma unroll
         for (int c = 0; c < P::R; ++c) {
-            cf x = fx::cscale(raw[T * c], scale);
+            const cf r = raw[T * c];
+            if (TRACK) m = fmaxf(fmaxf(m, fabsf(r.x)), fabsf(r.y));
+            cf x = fx::cscale(r, scale);
             if (EXTRA && down) x = fx::cmul(x, ldg_cf(down + tid + T * c));
             const float ph = fx::fadd(start, fx::fmul(rate, fx::fadd(fi0, (float)(T * c))));
-            const float2 r = sincos_slow(ph);
-            x = fx::cmul(x, fx::mk(r.x, r.y));
+            const float2 q = sincos_slow(ph);
+            x = fx::cmul(x, fx::mk(q.x, q.y));
             if (EXTRA && w) x = fx::cscale(x, __ldg(w + tid + T * c));
             v[c] = x;
         }
+        if (TRACK) *track = m;
     }
 }
 

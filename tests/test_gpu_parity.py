@@ -386,3 +386,35 @@ def test_packet_kernel_ragged_loud_and_unaligned(phy, lp, oracle, sf):
         assert int(out["status"][p]) == r and int(out["sync"][p]) == sync
         assert np.array_equal(out["symbols"][p, :r].cpu().numpy(), s_)
         assert out["cfo"][p].cpu().numpy().tobytes() == cfo.tobytes()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf", [7, 9, 10])
+def test_max_abs_prediction_edge_cases(phy, lp, oracle, sf):
+    """The warp-per-packet kernel trusts the previous packet's max-abs and verifies it from the samples it
+    streams (FMNMX ignores NaN, the reference's comparison does not count a sample whose real part is NaN):
+    homogeneous runs, alternating amplitudes, NaN / inf samples, all-zero packets, in one batch."""
+    rng = np.random.default_rng(1200 + sf)
+    N = 1 << sf
+    base = make_packets(oracle, rng, sf, 1, 4, 6, kind="clean")
+    rows = []
+    for i in range(40):
+        d = base[i % 4].copy()
+        k = i % 10
+        if k == 3:
+            d = (d * np.float32(1.7)).astype(np.complex64)
+        elif k == 4:
+            d = (d * np.float32(0.4)).astype(np.complex64)
+        elif k == 5:
+            d[3 * N + 5] = np.complex64(complex(np.nan, 5.0))      # ignored by the reference's max scan
+        elif k == 6:
+            d[2 * N + 1] = np.complex64(complex(0.5, np.nan))
+        elif k == 7:
+            d[:] = 0
+        elif k == 8:
+            d[4 * N + 9] = np.complex64(complex(np.inf, 0.0))
+        rows.append(d)
+    iq = np.stack(rows)
+    with np.errstate(all="ignore"):
+        check_legacy(phy, lp, oracle, iq, sf, 1, 0)
+        check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_NO_SCRATCH)
