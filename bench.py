@@ -244,6 +244,10 @@ def run_ours(args, wl):
     else:
         kname = ("demod_fused_kernel<SF%d>" if args.fused else "demod_packet_kernel<SF%d>") % sf
         sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if not two and not args.fused and os.path.exists(tpath):
+        traffic = (json.load(open(tpath)).get("%s:%d" % (args.workload, P)) or {}).get("bytes")
     achieved = sym_bytes / (sym_kernel_ms * 1e-3) / 1e9
     step_bytes = P * nsym * b_sym
     line = {
@@ -255,7 +259,7 @@ def run_ours(args, wl):
         "config": {"workload": wl["name"], "packets_per_gpu": P, "symbols_per_packet": nsym, "sf": sf,
                    "l2_policy": "inputs larger than L2 (%.1f GB per GPU per step)" % (P * spp * 8 / 1e9)},
         "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
                      "kernel_ms": sym_kernel_ms, "algorithmic_bytes_per_launch": sym_bytes},
         "e2e": {"value": e2e_value, "unit": "symbols/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "packets_per_step": Pe},

@@ -12,7 +12,7 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "liblora_phy_cuda.so")
+LIB_PATH = os.environ.get("LORA_PHY_LIB") or os.path.join(_HERE, "liblora_phy_cuda.so")   # override: A/B of build variants
 HEADER = os.path.join(ROOT, "include", "lora_phy_cuda.h")
 
 F_DECHIRP = 0x1

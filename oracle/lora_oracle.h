@@ -81,6 +81,19 @@ uint8_t oracle_chk_p64(uint8_t v, int* err);                       /* :357-365 *
 void oracle_interleave(const uint8_t* cw, size_t ncw, uint16_t* sym, size_t ppm, size_t rdd);   /* :376-393 */
 void oracle_deinterleave(const uint16_t* sym, size_t nsym, uint8_t* cw, size_t ppm, size_t rdd);/* :396-412 */
 
+/* Upstream coding chain (external/LoRa-SDR/LoRaEncoder.cpp:161-233, LoRaDecoder.cpp:196-397), restated in
+ * lora_chain_oracle.c.  ppm == 0 means ppm = sf. */
+typedef struct {
+    unsigned sf, ppm, rdd;          /* rdd 0..4 = coding rate 4/4 .. 4/8 */
+    int explicit_hdr, crc, whitening;
+    int error_check, crc_check, out_hdr;   /* decoder: _errorCheck, _crcc, _hdr */
+    unsigned data_length;           /* decoder, implicit-header mode */
+} oracle_chain_cfg;
+size_t oracle_chain_num_symbols(const oracle_chain_cfg* c, size_t payload_len);
+long oracle_encode_chain(const oracle_chain_cfg* c, const uint8_t* payload, size_t payload_len, uint16_t* symbols);
+long oracle_decode_chain(const oracle_chain_cfg* c, const uint16_t* symbols, size_t n_symbols, uint8_t* out,
+                         size_t cap, int* flags);
+
 /* Timed CPU arm when oracle/_ref is unavailable: one packet per thread. Returns seconds. */
 double oracle_demod_batch_mt(unsigned sf, int window, unsigned osr, const ocplx* iq,
                              size_t n_packets, size_t samples_per_packet,
