@@ -180,6 +180,40 @@ long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_s
                                      size_t symbols_per_packet, size_t n_packets,
                                      uint8_t* h_payload, size_t payload_stride, uint8_t* h_crc_ok);
 
+/* ---- bit pipeline: K4 (full upstream coding chain) -------------------------------------------- */
+/* The chain the reference vendors under external/LoRa-SDR and its README's LoRaParams{cr, explicit_header,
+ * crc_enabled} refer to (LoRaEncoder.cpp:161-233, LoRaDecoder.cpp:196-397): CRC-16, 3-byte explicit
+ * header, Hamming / parity FEC per coding rate, whitening, diagonal interleaver, gray mapping.           */
+typedef struct lora_phy_cuda_chain_cfg {
+    uint32_t sf;              /* 7..12 */
+    uint32_t ppm;             /* bits per symbol actually used; 0 = sf (LoRaEncoder.cpp:165) */
+    uint32_t cr;              /* redundancy bits 0..4 = coding rate 4/4, 4/5, 4/6, 4/7, 4/8 */
+    uint32_t explicit_header; /* LoRaEncoder.cpp:182 / LoRaDecoder.cpp:284 */
+    uint32_t crc;             /* encoder: append the CRC-16 and flag it in the header */
+    uint32_t whitening;       /* encoder: table whitening on (upstream default) */
+    uint32_t error_check;     /* decoder: drop packets with any non-zero FEC syndrome (_errorCheck) */
+    uint32_t crc_check;       /* decoder: drop packets whose CRC does not match (_crcc) */
+    uint32_t out_header;      /* decoder: keep the 3 header bytes and the CRC in the output (_hdr) */
+    uint32_t data_length;     /* decoder, implicit header: payload bytes (_dataLength) */
+} lora_phy_cuda_chain_cfg;
+
+/* Symbols one packet of payload_len bytes encodes to (LoRaEncoder.cpp:171-172), or -EINVAL. */
+long lora_phy_cuda_chain_symbols(const lora_phy_cuda_chain_cfg* cc, size_t payload_len);
+/* d_payload [n_packets][payload_stride] uint8 -> d_symbols [n_packets][symbol_stride] uint16; returns the
+ * symbols per packet, -ERANGE if symbol_stride is smaller, -EINVAL on a bad configuration.          */
+long lora_phy_cuda_encode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_chain_cfg* cc,
+                                      const uint8_t* d_payload, size_t payload_stride, size_t payload_len,
+                                      size_t n_packets, uint16_t* d_symbols, size_t symbol_stride);
+/* d_symbols [n_packets][symbol_stride] (n_symbols used per packet, or d_symbol_counts[p] when given, e.g.
+ * the status array of demodulate_batch) -> d_payload [n_packets][payload_stride].
+ * d_len[p] = bytes written, -1 = dropped by the decoder (LoRaDecoder.cpp drop()), -ERANGE = payload_stride
+ * too small.  d_flags[p] (may be NULL): bit0 a codeword had a non-zero syndrome, bit1 uncorrectable
+ * H(8,4) word, bit2 the packet carries a CRC, bit3 the CRC matched.  Returns 0 or a negative errno.   */
+int lora_phy_cuda_decode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_chain_cfg* cc,
+                                     const uint16_t* d_symbols, size_t symbol_stride,
+                                     const int32_t* d_symbol_counts, size_t n_symbols, size_t n_packets,
+                                     uint8_t* d_payload, size_t payload_stride, int32_t* d_len, uint8_t* d_flags);
+
 /* ---- tables (parity tests read these back) -------------------------------------------------- */
 /* which: 0 = kissfft twiddles (kissfft.hh:24-29), 1 = Hann window (LoRaDemod.cpp:18-24),
  * 2 = downchirp for cfg bw (phy.cpp:205-208).  Copies N entries to host memory.                */

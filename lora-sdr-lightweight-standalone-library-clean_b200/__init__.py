@@ -33,6 +33,16 @@ def make_cfg(sf, bw_hz=125000, osr=1, window=0, flags=0, sync_word=0x12, amplitu
     return Cfg(sf, bw_hz, osr, window, flags, sync_word, amplitude, 0)
 
 
+class ChainCfg(C.Structure):
+    _fields_ = [(n, C.c_uint32) for n in ("sf", "ppm", "cr", "explicit_header", "crc", "whitening", "error_check",
+                                          "crc_check", "out_header", "data_length")]
+
+
+def make_chain_cfg(sf, cr=1, explicit_header=1, crc=1, ppm=0, whitening=1, error_check=0, crc_check=1, out_header=0,
+                   data_length=0):
+    return ChainCfg(sf, ppm, cr, explicit_header, crc, whitening, error_check, crc_check, out_header, data_length)
+
+
 def build(verbose=False):
     """Compile csrc/*.cu for sm_100a into liblora_phy_cuda.so (nvcc cross-compiles without a GPU)."""
     cmd = ["make", "-j4", "-C", os.path.join(_HERE, "csrc")]
@@ -73,6 +83,9 @@ SIGNATURES = {
     "lora_phy_cuda_decode_batch": (C.c_long, [_vp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp]),
     "lora_phy_cuda_encode_batch_host": (C.c_long, [_vp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_decode_batch_host": (C.c_long, [_vp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp]),
+    "lora_phy_cuda_chain_symbols": (C.c_long, [_vp, _sz]),
+    "lora_phy_cuda_encode_chain_batch": (C.c_long, [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _sz]),
+    "lora_phy_cuda_decode_chain_batch": (C.c_int, [_vp, _vp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp, _vp]),
     "lora_phy_cuda_copy_table": (C.c_int, [_vp, _u32, _u32, C.c_int, _vp]),
 }
 
@@ -252,6 +265,31 @@ class LoraPhyCuda:
         rc = self._check(self.lib.lora_phy_cuda_decode_batch(self.h, _ptr(symbols), symbols.stride(0), _ptr(counts), S, P,
                                                              _ptr(pay), pay.stride(0), _ptr(crc)))
         return rc, pay, crc
+
+    # ---- full coding chain --------------------------------------------------------------------
+    def chain_symbols(self, cc, payload_len):
+        return int(self.lib.lora_phy_cuda_chain_symbols(C.byref(cc), payload_len))
+
+    def encode_chain_batch(self, cc, payload):
+        t = self.torch
+        P, L = payload.shape
+        nsym = self.chain_symbols(cc, L)
+        if nsym < 0:
+            raise LoraPhyError(nsym, "bad chain configuration")
+        sym = t.zeros((P, nsym), dtype=t.uint16, device=self.device)
+        self._check(self.lib.lora_phy_cuda_encode_chain_batch(self.h, C.byref(cc), _ptr(payload), payload.stride(0), L, P,
+                                                              _ptr(sym), nsym))
+        return sym
+
+    def decode_chain_batch(self, cc, symbols, counts=None, payload_stride=260):
+        t = self.torch
+        P, S = symbols.shape
+        pay = t.zeros((P, payload_stride), dtype=t.uint8, device=self.device)
+        ln = t.zeros(P, dtype=t.int32, device=self.device)
+        fl = t.zeros(P, dtype=t.uint8, device=self.device)
+        self._check(self.lib.lora_phy_cuda_decode_chain_batch(self.h, C.byref(cc), _ptr(symbols), symbols.stride(0),
+                                                              _ptr(counts), S, P, _ptr(pay), payload_stride, _ptr(ln), _ptr(fl)))
+        return pay, ln, fl
 
     def copy_table(self, sf, which, bw_hz=125000):
         import numpy as np

@@ -63,6 +63,7 @@ struct lora_phy_cuda_ctx {
     std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
     DevBuf state, phases, tmp, sched;                   // PacketState[], modulator phases, compensate scratch, fused-kernel counters
     uint32_t lookahead_bytes = 64u << 20;               // fused schedule look-ahead (LORA_PHY_LOOKAHEAD_MB)
+    DevBuf lfsr;                                         // dewhitening byte table of the coding chain (chain.cu)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
     std::mutex mu;
@@ -169,6 +170,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
         if (ctx->tab[sf].hann) cudaFree(ctx->tab[sf].hann);
     }
     for (auto& kv : ctx->chirps) cudaFree(kv.second);
+    ctx->lfsr.release();
     ctx->state.release(); ctx->phases.release(); ctx->tmp.release(); ctx->sched.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
     ctx->h_in.release(); ctx->h_out.release();
@@ -614,6 +616,80 @@ long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_s
     }
     if (h_crc_ok) memcpy(h_crc_ok, h + pay_bytes, n_packets);
     return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+static int chain_args(const lora_phy_cuda_chain_cfg* cc, lk::ChainArgs* a)
+{
+    if (!cc) return -EINVAL;
+    const uint32_t ppm = cc->ppm ? cc->ppm : cc->sf;
+    if (cc->sf < 7 || cc->sf > 12 || ppm > cc->sf || ppm < 5 || cc->cr > 4) return -EINVAL;
+    a->sf = cc->sf; a->ppm = ppm; a->rdd = cc->cr;
+    a->explicit_hdr = cc->explicit_header != 0; a->crc = cc->crc != 0; a->whitening = cc->whitening != 0;
+    a->error_check = cc->error_check != 0; a->crc_check = cc->crc_check != 0; a->out_hdr = cc->out_header != 0;
+    a->data_length = cc->data_length;
+    return 0;
+}
+
+long lora_phy_cuda_chain_symbols(const lora_phy_cuda_chain_cfg* cc, size_t payload_len)
+{
+    lk::ChainArgs a;
+    if (chain_args(cc, &a) || payload_len > 255) return -EINVAL;
+    const size_t nbytes = payload_len + (a.crc ? 2 : 0);
+    const size_t ncw = ((nbytes * 2 + (a.explicit_hdr ? 5 : 0) + a.ppm - 1) / a.ppm) * a.ppm;   // LoRaEncoder.cpp:171
+    return (long)(8 + (ncw / a.ppm - 1) * (4 + a.rdd));                                        // :172
+}
+
+long lora_phy_cuda_encode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_chain_cfg* cc,
+                                      const uint8_t* d_payload, size_t payload_stride, size_t payload_len,
+                                      size_t n_packets, uint16_t* d_symbols, size_t symbol_stride)
+{
+    if (!ctx) return -EINVAL;
+    lk::ChainArgs a;
+    if (chain_args(cc, &a)) return fail(ctx, -EINVAL, "bad chain configuration (sf 7..12, 5 <= ppm <= sf, cr 0..4)");
+    if (payload_len > 255) return fail(ctx, -EINVAL, "payload longer than 255 bytes");
+    if ((!d_payload && payload_len && n_packets) || (!d_symbols && n_packets)) return fail(ctx, -EINVAL, "NULL buffer");
+    if (payload_len > payload_stride && n_packets > 1) return fail(ctx, -EINVAL, "payload_len exceeds payload_stride");
+    const long nsym = lora_phy_cuda_chain_symbols(cc, payload_len);
+    if ((size_t)nsym > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than the symbols per packet");
+    if (n_packets > 0xffffffffull) return fail(ctx, -EINVAL, "batch too large");
+    Guard g(ctx->device);
+    CK(lk::launch_chain_encode(a, d_payload, payload_stride, (uint32_t)payload_len, (uint32_t)n_packets, d_symbols,
+                               symbol_stride, ctx->sm_count, ctx->stream));
+    if (n_packets) ++ctx->launches;
+    return nsym;
+}
+
+int lora_phy_cuda_decode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_chain_cfg* cc,
+                                     const uint16_t* d_symbols, size_t symbol_stride, const int32_t* d_counts,
+                                     size_t n_symbols, size_t n_packets, uint8_t* d_payload, size_t payload_stride,
+                                     int32_t* d_len, uint8_t* d_flags)
+{
+    if (!ctx) return -EINVAL;
+    lk::ChainArgs a;
+    if (chain_args(cc, &a)) return fail(ctx, -EINVAL, "bad chain configuration (sf 7..12, 5 <= ppm <= sf, cr 0..4)");
+    if ((!d_symbols || !d_payload || !d_len) && n_packets) return fail(ctx, -EINVAL, "NULL buffer");
+    if (n_symbols > symbol_stride && n_packets > 1) return fail(ctx, -EINVAL, "n_symbols exceeds symbol_stride");
+    const size_t rows = 4 + a.rdd, nsym = ((n_symbols + rows - 1) / rows) * rows;
+    if (n_symbols > (size_t)lk::chain_max_symbols() || (nsym / rows) * a.ppm + 32 > 2048)
+        return fail(ctx, -EINVAL, "too many symbols per packet for the coding chain (a 255-byte packet needs < 700)");
+    if (n_packets > 0xffffffffull) return fail(ctx, -EINVAL, "batch too large");
+    if (!n_packets) return 0;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    if (!ctx->lfsr.p) {
+        const size_t n = (size_t)lk::chain_lfsr_table_size();
+        std::string host(n, '\0');
+        lk::chain_lfsr_table(reinterpret_cast<uint8_t*>(&host[0]));
+        CK(ctx->lfsr.reserve(n));
+        CK(cudaMemcpyAsync(ctx->lfsr.p, host.data(), n, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    CK(lk::launch_chain_decode(a, d_symbols, symbol_stride, d_counts, (uint32_t)n_symbols, (uint32_t)n_packets,
+                               static_cast<const uint8_t*>(ctx->lfsr.p), d_payload, payload_stride, d_len, d_flags,
+                               ctx->sm_count, ctx->stream));
+    ++ctx->launches;
+    return 0;
 }
 
 int lora_phy_cuda_copy_table(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t bw_hz, int which, void* h_out)

@@ -63,4 +63,21 @@ cudaError_t launch_compensate(const cf* in, cf* out, size_t packet_stride, uint3
                               uint32_t n_packets, int sf, uint32_t osr, const float* cfo,
                               const float* time_offset, cudaStream_t stream);
 
+// chain.cu: upstream coding chain (CRC / header / FEC / whitening / interleaver / gray), one warp per packet
+struct ChainArgs {
+    unsigned sf, ppm, rdd;
+    int explicit_hdr, crc, whitening, error_check, crc_check, out_hdr;
+    unsigned data_length;
+};
+cudaError_t launch_chain_encode(const ChainArgs& a, const uint8_t* payload, size_t payload_stride, uint32_t len,
+                                uint32_t n_packets, uint16_t* symbols, size_t symbol_stride, int sm_count,
+                                cudaStream_t stream);
+cudaError_t launch_chain_decode(const ChainArgs& a, const uint16_t* symbols, size_t symbol_stride,
+                                const int32_t* counts, uint32_t n_symbols, uint32_t n_packets, const uint8_t* lfsr,
+                                uint8_t* payload, size_t payload_stride, int32_t* out_len, uint8_t* out_flags,
+                                int sm_count, cudaStream_t stream);
+void chain_lfsr_table(uint8_t* out);
+int chain_lfsr_table_size();
+int chain_max_symbols();
+
 } // namespace lk

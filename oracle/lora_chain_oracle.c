@@ -118,6 +118,7 @@ long oracle_decode_chain(const oracle_chain_cfg* c, const uint16_t* in_symbols, 
     if (n_in < N_HEADER_SYMBOLS) return -1;                              /* :208 */
     const unsigned nsym = round_up((unsigned)n_in, 4 + c->rdd);
     const unsigned ncw = (nsym / (4 + c->rdd)) * ppm;
+    if (ncw + 32 > 2048) return -22;
     uint16_t sym[1216];
     uint8_t cw[2048];
     uint8_t bytes[1032];

@@ -26,6 +26,12 @@ def _p(a, t):
     return a.ctypes.data_as(t)
 
 
+class ChainCfg(C.Structure):
+    _fields_ = [("sf", C.c_uint), ("ppm", C.c_uint), ("rdd", C.c_uint), ("explicit_hdr", C.c_int), ("crc", C.c_int),
+                ("whitening", C.c_int), ("error_check", C.c_int), ("crc_check", C.c_int), ("out_hdr", C.c_int),
+                ("data_length", C.c_uint)]
+
+
 class CpuPhy:
     def __init__(self, lib, prefix):
         self.lib, self.prefix = lib, prefix
@@ -204,6 +210,30 @@ class CpuPhy:
         out = np.zeros(1 << sf, dtype=np.float32)
         self.fn("window", None, [C.c_uint, C.c_int, C.c_void_p])(sf, hann, out.ctypes.data)
         return out
+
+    # ---- upstream coding chain (oracle restatement only) ------------------------------------
+    def chain_cfg(self, sf, cr=1, explicit_header=1, crc=1, ppm=0, whitening=1, error_check=0, crc_check=1, out_header=0,
+                  data_length=0):
+        return ChainCfg(sf, ppm, cr, explicit_header, crc, whitening, error_check, crc_check, out_header, data_length)
+
+    def encode_chain(self, cfg, payload):
+        assert not self.is_ref
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        n = self.fn("chain_num_symbols", C.c_size_t, [C.c_void_p, C.c_size_t])(C.addressof(cfg), payload.size)
+        out = np.zeros(n, dtype=np.uint16)
+        r = self.fn("encode_chain", C.c_long, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p])(
+            C.addressof(cfg), payload.ctypes.data, payload.size, out.ctypes.data)
+        assert r == n, (r, n)
+        return out
+
+    def decode_chain(self, cfg, symbols, cap=600):
+        assert not self.is_ref
+        symbols = np.ascontiguousarray(symbols, dtype=np.uint16)
+        out = np.zeros(cap, dtype=np.uint8)
+        fl = C.c_int(0)
+        r = self.fn("decode_chain", C.c_long, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, i32p])(
+            C.addressof(cfg), symbols.ctypes.data, symbols.size, out.ctypes.data, cap, C.byref(fl))
+        return int(r), out[:max(int(r), 0)].copy(), fl.value
 
     # ---- timed batch ---------------------------------------------------------------
     def demod_batch_mt(self, iq, n_packets, spp, sf, osr=1, window=0, threads=1):

@@ -418,3 +418,72 @@ def test_max_abs_prediction_edge_cases(phy, lp, oracle, sf):
     with np.errstate(all="ignore"):
         check_legacy(phy, lp, oracle, iq, sf, 1, 0)
         check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_NO_SCRATCH)
+
+
+# ---- full coding chain (K4): CUDA == oracle restatement of external/LoRa-SDR/LoRaEncoder.cpp / LoRaDecoder.cpp ----
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
+def test_chain_encode_decode_parity(phy, lp, oracle, sf):
+    import torch
+    rng = np.random.default_rng(2000 + sf)
+    for cr in range(5):
+        for ppm, L, expl, crc in ((0, 32, 1, 1), (sf - 2, 5, 1, 1), (0, 255, 1, 0), (0, 1, 1, 1), (sf - 1, 20, 0, 1)):
+            P = 33
+            pay = rng.integers(0, 256, (P, L), dtype=np.uint8)
+            cc = lp.make_chain_cfg(sf, cr=cr, explicit_header=expl, crc=crc, ppm=ppm, data_length=L)
+            oc = oracle.chain_cfg(sf, cr=cr, explicit_header=expl, crc=crc, ppm=ppm, data_length=L)
+            sym = phy.encode_chain_batch(cc, to_dev(phy, pay))
+            phy.synchronize()
+            sym_h = sym.cpu().numpy()
+            for p in range(P):
+                assert np.array_equal(sym_h[p], oracle.encode_chain(oc, pay[p])), (sf, cr, ppm, L, expl, crc, p)
+            # decode: clean, bit-flipped, truncated (ragged counts) and garbage rows
+            bad = sym_h.copy()
+            flips = rng.integers(0, 4, P)
+            for p in range(P):
+                for _ in range(int(flips[p])):
+                    bad[p, rng.integers(0, bad.shape[1])] ^= np.uint16(1 << int(rng.integers(0, sf)))
+            bad[P - 1] = rng.integers(0, 1 << sf, bad.shape[1]).astype(np.uint16)
+            counts = np.full(P, bad.shape[1], np.int32)
+            counts[3], counts[4], counts[5] = 7, 8, max(8, bad.shape[1] - 3)
+            for strict in (0, 1):
+                cc.error_check = strict
+                oc.error_check = strict
+                out, ln, fl = phy.decode_chain_batch(cc, to_dev(phy, bad), counts=to_dev(phy, counts))
+                phy.synchronize()
+                out, ln, fl = out.cpu().numpy(), ln.cpu().numpy(), fl.cpu().numpy()
+                for p in range(P):
+                    r, ob, of = oracle.decode_chain(oc, bad[p, :counts[p]], cap=260)
+                    assert ln[p] == r, (sf, cr, ppm, L, expl, crc, p, ln[p], r)
+                    assert fl[p] == of
+                    if r > 0:
+                        assert np.array_equal(out[p, :r], ob)
+
+
+@pytest.mark.gpu
+def test_config1_hello_cr45_explicit_header_crc(phy, lp, oracle):
+    """BASELINE.json configs[0] taken literally: SF7 BW125k CR4/5 explicit header CRC on, 'Hello':
+    encode chain -> modulate -> (caller-side dechirp) -> demodulate -> decode chain, every stage == oracle."""
+    import torch
+    pay = np.frombuffer(b"Hello", np.uint8)
+    P = 9
+    cc = lp.make_chain_cfg(7, cr=1)
+    oc = oracle.chain_cfg(7, cr=1)
+    cfg = lp.make_cfg(7)
+    sym = phy.encode_chain_batch(cc, to_dev(phy, np.tile(pay, (P, 1))))
+    assert sym.shape[1] == 18
+    iq = phy.modulate_batch(cfg, sym)
+    phy.dechirp_batch(cfg, iq)
+    out = phy.demodulate_batch(cfg, iq)
+    dec, ln, fl = phy.decode_chain_batch(cc, out["symbols"], counts=out["status"])
+    phy.synchronize()
+    o_sym = oracle.encode_chain(oc, pay)
+    o_iq = oracle.lora_modulate(o_sym, 7)
+    o_d = (o_iq.reshape(-1, 128) * oracle.downchirp(7)[None, :]).astype(np.complex64).ravel()
+    r, o_rx, o_sync, _, _ = oracle.lora_demodulate(o_d, 7)
+    assert r == 18 and o_sync == 0x12
+    for p in range(P):
+        assert np.array_equal(sym[p].cpu().numpy(), o_sym)
+        assert np.array_equal(out["symbols"][p, :18].cpu().numpy(), o_rx) and int(out["sync"][p]) == 0x12
+        assert int(ln[p]) == 5 and bytes(dec[p, :5].cpu().numpy()) == b"Hello" and int(fl[p]) == 0b1100
+    assert oracle.decode_chain(oc, o_rx)[1].tobytes() == b"Hello"
