@@ -180,6 +180,26 @@ long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_s
                                      size_t symbols_per_packet, size_t n_packets,
                                      uint8_t* h_payload, size_t payload_stride, uint8_t* h_crc_ok);
 
+/* ---- streaming front end: K2 -------------------------------------------------------------------- */
+/* Sliding-window preamble / sync-word detector with CFO / STO tracking on CONTINUOUS IQ, n_streams
+ * independent streams of one spreading factor: the upstream receiver the reference vendors
+ * (external/LoRa-SDR/LoRaDemod.cpp:145-327; frame format of LoRaMod.cpp:141-215: 10 up-chirps, two sync
+ * chirps at nibble*8, 2 1/4 down-chirps, data).  Per stream up to max_frames frames are reported, in
+ * order of completion:
+ *   d_frame_start [n_streams][max_frames]  sample index of the window that matched sync word0 (after STO tracking)
+ *   d_frame_err   [n_streams][max_frames]  averaged down-chirp bin error (_freqError: the integer CFO estimate)
+ *   d_frame_nsym  [n_streams][max_frames]  symbols in the frame (<= mtu; ends at mtu or when snr < thresh_db)
+ *   d_symbols     [n_streams][max_frames][mtu] int16
+ *   d_n_frames    [n_streams] frames completed (may exceed max_frames: the excess is counted, not stored)
+ *   d_end_pos     [n_streams] (may be NULL) first sample the receiver did not consume
+ * d_sample_counts NULL or [n_streams] ragged lengths.  thresh_db is upstream's squelch (default -30).     */
+int lora_phy_cuda_detect_stream(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t sync_word, float thresh_db,
+                                uint32_t mtu, const void* d_iq, size_t stream_stride,
+                                const uint32_t* d_sample_counts, size_t n_samples, size_t n_streams,
+                                size_t max_frames, uint32_t* d_frame_start, int32_t* d_frame_err,
+                                int32_t* d_frame_nsym, int16_t* d_symbols, uint32_t* d_n_frames,
+                                uint32_t* d_end_pos);
+
 /* ---- bit pipeline: K4 (full upstream coding chain) -------------------------------------------- */
 /* The chain the reference vendors under external/LoRa-SDR and its README's LoRaParams{cr, explicit_header,
  * crc_enabled} refer to (LoRaEncoder.cpp:161-233, LoRaDecoder.cpp:196-397): CRC-16, 3-byte explicit

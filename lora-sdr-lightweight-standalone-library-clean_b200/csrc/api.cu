@@ -5,6 +5,9 @@
 #include "internal.h"
 
 #include <cerrno>
+#include <cmath>
+#include <complex>
+#include <vector>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -63,6 +66,7 @@ struct lora_phy_cuda_ctx {
     std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
     DevBuf state, phases, tmp, sched;                   // PacketState[], modulator phases, compensate scratch, fused-kernel counters
     uint32_t lookahead_bytes = 64u << 20;               // fused schedule look-ahead (LORA_PHY_LOOKAHEAD_MB)
+    cf* sync_tab[13] = { nullptr };                      // stream detector tables per sf: up | down | fine (stream_sync.cu)
     DevBuf lfsr;                                         // dewhitening byte table of the coding chain (chain.cu)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
@@ -170,6 +174,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
         if (ctx->tab[sf].hann) cudaFree(ctx->tab[sf].hann);
     }
     for (auto& kv : ctx->chirps) cudaFree(kv.second);
+    for (int sf = 0; sf <= 12; ++sf) if (ctx->sync_tab[sf]) cudaFree(ctx->sync_tab[sf]);
     ctx->lfsr.release();
     ctx->state.release(); ctx->phases.release(); ctx->tmp.release(); ctx->sched.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
@@ -616,6 +621,71 @@ long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_s
     }
     if (h_crc_ok) memcpy(h_crc_ok, h + pay_bytes, n_packets);
     return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tables of the upstream receiver (LoRaDemod.cpp:96-117): std::polar(1.0, double phase) narrowed to float, built
+// with the host's libm exactly as the reference's constructor does, once per (context, sf).
+static int sync_tables(lora_phy_cuda_ctx* ctx, uint32_t sf, cf** out)
+{
+    if (ctx->sync_tab[sf]) { *out = ctx->sync_tab[sf]; return 0; }
+    const size_t N = (size_t)1 << sf, fine_n = N * 128;
+    std::vector<cf> host(2 * N + fine_n);
+    float phase = (float)-M_PI;
+    double acc = 0.0;
+    for (size_t i = 0; i < N; ++i) {
+        acc += phase;
+        const std::complex<double> e = std::polar(1.0, acc);
+        host[i] = fx::mk((float)e.real(), (float)-e.imag());          // _upChirpTable = conj(entry)
+        host[N + i] = fx::mk((float)e.real(), (float)e.imag());       // _downChirpTable
+        phase += (float)((2 * M_PI) / (double)N);
+    }
+    acc = 0.0;
+    phase = (float)(2.0 * M_PI / (double)fine_n);
+    for (size_t i = 0; i < fine_n; ++i) {
+        acc += phase;
+        const std::complex<double> e = std::polar(1.0, acc);
+        host[2 * N + i] = fx::mk((float)e.real(), (float)e.imag());
+    }
+    cf* d = nullptr;
+    CK(cudaMalloc(&d, host.size() * sizeof(cf)));
+    CK(cudaMemcpyAsync(d, host.data(), host.size() * sizeof(cf), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->sync_tab[sf] = d;
+    *out = d;
+    return 0;
+}
+
+int lora_phy_cuda_detect_stream(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t sync_word, float thresh_db, uint32_t mtu,
+                                const void* d_iq, size_t stream_stride, const uint32_t* d_counts, size_t n_samples,
+                                size_t n_streams, size_t max_frames, uint32_t* d_frame_start, int32_t* d_frame_err,
+                                int32_t* d_frame_nsym, int16_t* d_symbols, uint32_t* d_n_frames, uint32_t* d_end_pos)
+{
+    if (!ctx) return -EINVAL;
+    if (sf < 7 || sf > 12) return fail(ctx, -EINVAL, "sf out of range 7..12");
+    if (!mtu || mtu > 32767) return fail(ctx, -EINVAL, "mtu out of range 1..32767");
+    if (n_samples > stream_stride && n_streams > 1) return fail(ctx, -EINVAL, "n_samples exceeds stream_stride");
+    if (n_samples > 0xf0000000ull || n_streams > 0xffffffffull || max_frames > 0xffffffffull) return fail(ctx, -EINVAL, "too large");
+    if (n_streams && (!d_iq || !d_n_frames || (max_frames && (!d_frame_start || !d_frame_err || !d_frame_nsym || !d_symbols))))
+        return fail(ctx, -EINVAL, "NULL buffer");
+    if (!n_streams) return 0;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    cf* tab = nullptr;
+    int rc = sync_tables(ctx, sf, &tab);
+    if (rc) return rc;
+    const size_t N = (size_t)1 << sf;
+    lk::StreamSyncArgs a;
+    a.iq = static_cast<const cf*>(d_iq); a.stream_stride = stream_stride; a.counts = d_counts;
+    a.n_samples = (uint32_t)n_samples; a.n_streams = (uint32_t)n_streams;
+    a.up = tab; a.down = tab + N; a.fine = tab + 2 * N;
+    a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
+    a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
+    a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
+    a.n_frames = d_n_frames; a.end_pos = d_end_pos;
+    CK(lk::launch_stream_sync((int)sf, a, ctx->stream));
+    ++ctx->launches;
+    return 0;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -63,6 +63,17 @@ cudaError_t launch_compensate(const cf* in, cf* out, size_t packet_stride, uint3
                               uint32_t n_packets, int sf, uint32_t osr, const float* cfo,
                               const float* time_offset, cudaStream_t stream);
 
+// stream_sync.cu: sliding-window preamble / sync-word detector on continuous IQ, one thread group per stream
+struct StreamSyncArgs {
+    const cf* iq; size_t stream_stride; const uint32_t* counts; uint32_t n_samples; uint32_t n_streams;
+    const cf* up; const cf* down; const cf* fine;          // LoRaDemod.cpp:96-117 tables (N, N, N*128 entries)
+    const cf* tw; const cf* ct; float power_scale;
+    uint32_t sync; float thresh; uint32_t mtu; uint32_t max_frames;
+    uint32_t* frame_start; int32_t* frame_err; int32_t* frame_nsym; int16_t* symbols;   // [n_streams][max_frames]([mtu])
+    uint32_t* n_frames; uint32_t* end_pos;                 // [n_streams]
+};
+cudaError_t launch_stream_sync(int sf, const StreamSyncArgs& a, cudaStream_t stream);
+
 // chain.cu: upstream coding chain (CRC / header / FEC / whitening / interleaver / gray), one warp per packet
 struct ChainArgs {
     unsigned sf, ppm, rdd;

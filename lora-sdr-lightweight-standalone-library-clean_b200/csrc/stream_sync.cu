@@ -1,0 +1,251 @@
+// stream_sync.cu -- K2, the sliding-window preamble / sync-word detector on continuous IQ:
+// external/LoRa-SDR/LoRaDemod.cpp:145-327 (work loop and frame-sync state machine) over the tables of
+// :96-117, with the detector of LoRaDetector.hpp:39-74.
+//
+// A stream is inherently sequential (how far the window slides depends on the bin it just detected), so
+// the parallelism is streams x the T = N/16 threads of one window: one thread group owns one stream and
+// walks it window by window -- dechirp with the current chirp table and the 128-step fine-tune table,
+// exact-order FFT (fft_exact.cuh, full twiddles: the spectrum feeds fIndex), first-max, power / powerAvg /
+// fIndex, then the state machine on the group's thread 0:
+//   FRAMESYNC   preamble tracking: slide by N - value, accumulate fIndex into the fine frequency error;
+//               on (prev+4)/8 == 0 and sync word0 matched, look one window ahead for sync word1
+//   DOWNCHIRP0/1 signed bin error of the two down-chirps, averaged (the CFO estimate reported per frame)
+//   QUARTERCHIRP consume N/4 + err/2 (the STO correction), fold err/2 into the fine frequency error
+//   DATASYMBOLS emit symbols until mtu or squelch (snr < threshold), report the frame
+// Two pieces are serial on thread 0 because their order is observable in the results: the fine-tune index
+// recurrence (an int decremented by a float and truncated, per sample, :160-163) and the detector's
+// double-precision running total (LoRaDetector.hpp:45-52).
+#include "demod_device.cuh"
+#include "internal.h"
+
+namespace lk {
+
+namespace {
+
+constexpr int FINE_STEPS = 128;
+enum { ST_FRAMESYNC = 0, ST_DOWNCHIRP0, ST_DOWNCHIRP1, ST_QUARTERCHIRP, ST_DATASYMBOLS };
+
+struct GroupCtl {            // written by the group's thread 0, read by the whole group
+    uint32_t pos;
+    int live, down, need2, ft;
+    float fine_err;
+    int pad[2];
+};
+
+template <int SF>
+struct SyncSmem {
+    using P = fx::Plan<SF>;
+    static constexpr int G = CTA_THREADS / P::T;
+    static constexpr size_t buf_bytes = 2 * (size_t)G * P::N * sizeof(cf);
+    static constexpr size_t ft_bytes = (size_t)G * P::N * sizeof(int);
+    static constexpr size_t bytes = buf_bytes + ft_bytes + 8 * sizeof(Peak) + (size_t)G * sizeof(GroupCtl);
+};
+
+struct DetectOut { int value; float snr, findex; };
+
+// one window at `src`: dechirp + fine tune (:157-166), FFT, detect (LoRaDetector.hpp:39-74).
+// thread 0 of the group returns the detector outputs; *ft is advanced past the window.
+template <int SF>
+__device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const cf* __restrict__ src, bool live,
+                                                 const cf* __restrict__ chirp, int* ft, float fine_err, int tid,
+                                                 cf* buf0, cf* buf1, int& flip, int* ftidx, Peak* red)
+{
+    using P = fx::Plan<SF>;
+    constexpr int T = P::T, N = P::N;
+    const int wrap = N * FINE_STEPS;
+    if (tid == 0) {
+        int idx = *ft;
+        if (fine_err == 0.0f || !live) {
+            ftidx[0] = idx;                                  // constant index: lanes read entry 0 (flag below)
+        } else {
+            const float d = fx::fmul(fine_err, (float)FINE_STEPS);
+            for (int i = 0; i < N; ++i) {
+                ftidx[i] = idx;
+                idx = (int)fx::fsub((float)idx, d);          // int -= float * size_t, truncated (:160)
+                if (idx < 0) idx += wrap;
+                else if (idx >= wrap) idx -= wrap;
+            }
+            *ft = idx;
+        }
+    }
+    group_sync<T>();
+    const bool constant = fine_err == 0.0f;
+    cf v[P::R];
+#pragma unroll
+    for (int c = 0; c < P::R; ++c) {
+        const int i = tid + T * c;
+        cf x = fx::mk(0.0f, 0.0f);
+        if (live) {
+            x = fx::cmul(ldg_cf(src + i), ldg_cf(chirp + i));
+            x = fx::cmul(x, ldg_cf(a.fine + (constant ? ftidx[0] : ftidx[i])));
+        }
+        v[c] = x;
+    }
+    fft_group<SF, true>(v, tid, a.tw, a.ct, buf0, buf1, flip);
+    const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+    cf* spec = flip ? buf1 : buf0;
+    flip ^= 1;
+#pragma unroll
+    for (int r = 0; r < P::R; ++r) spec[P::bin_of_reg(tid, r)] = v[r];
+    group_sync<T>();
+    DetectOut o; o.value = 0; o.snr = 0.0f; o.findex = 0.0f;
+    if (tid == 0 && live) {
+        double total = 0.0;                                  // LoRaDetector.hpp:45-52, ascending
+        for (int i = 0; i < N; ++i)
+            total += (double)fx::fadd(fx::fmul(spec[i].x, spec[i].x), fx::fmul(spec[i].y, spec[i].y));
+        const float noise = __fsqrt_rn((float)(total - (double)pk.val));
+        const float fundamental = __fsqrt_rn(pk.val);
+        const cf l = spec[pk.idx > 0 ? pk.idx - 1 : N - 1];
+        const cf r = spec[pk.idx < N - 1 ? pk.idx + 1 : 0];
+        const float left = gm::hypotf_g(l.x, l.y), right = gm::hypotf_g(r.x, r.y);
+        const double demon = (2.0 * (double)fundamental) - (double)right - (double)left;
+        const float power = fx::fsub(fx::fmul(20.0f, gm::log10f_g(fundamental)), a.power_scale);
+        const float power_avg = fx::fsub(fx::fmul(20.0f, gm::log10f_g(noise)), a.power_scale);
+        o.value = pk.idx;
+        o.snr = fx::fsub(power, power_avg);
+        o.findex = (demon == 0.0) ? 0.0f : (float)(0.5 * (double)fx::fsub(right, left) / demon);
+    }
+    group_sync<T>();                                         // spectrum / ftidx free for the next window
+    return o;
+}
+
+template <int SF>
+__global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const StreamSyncArgs a)
+{
+    using P = fx::Plan<SF>;
+    using S = SyncSmem<SF>;
+    constexpr int T = P::T, N = P::N, G = S::G;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int g = threadIdx.x / T, tid = threadIdx.x % T;
+    cf* base = reinterpret_cast<cf*>(smem_raw);
+    cf* buf0 = base + (size_t)g * N;
+    cf* buf1 = base + (size_t)G * N + (size_t)g * N;
+    int* ftidx = reinterpret_cast<int*>(smem_raw + S::buf_bytes) + (size_t)g * N;
+    Peak* red = reinterpret_cast<Peak*>(smem_raw + S::buf_bytes + S::ft_bytes);
+    GroupCtl& ctl = reinterpret_cast<GroupCtl*>(smem_raw + S::buf_bytes + S::ft_bytes + 8 * sizeof(Peak))[g];
+    int flip = 0;
+
+    const uint32_t sid = blockIdx.x * G + g;
+    const bool have = sid < a.n_streams;
+    const cf* iq = a.iq + (size_t)(have ? sid : 0) * a.stream_stride;
+    const uint32_t n = have ? (a.counts ? a.counts[sid] : a.n_samples) : 0;
+
+    // state machine registers (thread 0 of the group)
+    int state = ST_FRAMESYNC, prev_value = 0, freq_error = 0, fine_idx = 0, down = 0;
+    float fine_err = 0.0f;
+    uint32_t pos = 0, sym_count = 0, frames = 0, cur_start = 0;
+
+    for (;;) {
+        if (tid == 0) {
+            ctl.pos = pos;
+            ctl.live = have && (unsigned long long)pos + 2ull * N <= n;       // LoRaDemod.cpp:148
+            ctl.down = down;
+            ctl.ft = fine_idx;
+            ctl.fine_err = fine_err;
+            ctl.need2 = 0;
+        }
+        __syncthreads();
+        const bool live = ctl.live != 0;
+        if (!__syncthreads_or(live)) break;
+        const uint32_t wpos = ctl.pos;
+        const float ferr = ctl.fine_err;
+        const cf* chirp = ctl.down ? a.down : a.up;
+        int ft = ctl.ft;
+        DetectOut d = sync_window<SF>(a, iq + wpos, live, chirp, &ft, ferr, tid, buf0, buf1, flip, ftidx, red);
+        bool squelched = false, syncd = false, match0 = false;
+        if (tid == 0 && live) {
+            fine_idx = ft;
+            squelched = d.snr < a.thresh;
+            if (state == ST_FRAMESYNC) {                                       // :179-185
+                syncd = !squelched && (prev_value + 4) / 8 == 0;
+                match0 = (unsigned)(d.value + 4) / 8 == (a.sync >> 4);
+                if (syncd && match0) ctl.need2 = 1;
+            }
+        }
+        __syncthreads();
+        const bool need2 = ctl.need2 != 0;
+        int value1 = 0;
+        if (__syncthreads_or(need2)) {                                         // look ahead one window for sync word1 (:188-205)
+            int ft2 = fine_idx;                                                // (a copy: _fineTuneIndex itself is not advanced)
+            if (tid != 0) ft2 = 0;
+            DetectOut d1 = sync_window<SF>(a, iq + wpos + N, live && need2, chirp, &ft2, ferr, tid, buf0, buf1, flip, ftidx, red);
+            if (tid == 0 && need2) { value1 = d1.value; d.findex = d1.findex; }
+        }
+        if (tid == 0 && live) {
+            uint32_t total = 0;
+            switch (state) {
+            case ST_FRAMESYNC: {
+                const bool match1 = need2 && (unsigned)(value1 + 4) / 8 == (a.sync & 0xfu);
+                if (syncd && match0 && match1) { total = 2 * N; state = ST_DOWNCHIRP0; down = 1; cur_start = wpos; }
+                else if (!squelched) { total = (uint32_t)(N - d.value); fine_err = fx::fadd(fine_err, d.findex); }
+                else { total = N; fine_err = 0.0f; fine_idx = 0; }
+            } break;
+            case ST_DOWNCHIRP0: {                                              // :240-250
+                state = ST_DOWNCHIRP1; total = N;
+                freq_error = d.value > N / 2 ? d.value - N : d.value;
+            } break;
+            case ST_DOWNCHIRP1: {                                              // :253-270
+                state = ST_QUARTERCHIRP; total = N; down = 0;
+                const int error = d.value > N / 2 ? d.value - N : d.value;
+                freq_error = (freq_error + error) / 2;
+            } break;
+            case ST_QUARTERCHIRP: {                                            // :273-283
+                state = ST_DATASYMBOLS;
+                total = (uint32_t)(N / 4 + freq_error / 2);
+                fine_err = fx::fadd(fine_err, (float)(freq_error / 2));
+                sym_count = 0;
+            } break;
+            default: {                                                         // ST_DATASYMBOLS, :286-310
+                total = N;
+                if (frames < a.max_frames)
+                    a.symbols[((size_t)sid * a.max_frames + frames) * a.mtu + sym_count] = (int16_t)d.value;
+                ++sym_count;
+                if (sym_count >= a.mtu || squelched) {
+                    if (frames < a.max_frames) {
+                        const size_t f = (size_t)sid * a.max_frames + frames;
+                        a.frame_start[f] = cur_start;
+                        a.frame_err[f] = freq_error;
+                        a.frame_nsym[f] = (int32_t)sym_count;
+                    }
+                    ++frames;
+                    fine_err = 0.0f;
+                    state = ST_FRAMESYNC;
+                }
+            } break;
+            }
+            pos = wpos + total;
+            prev_value = (int)(short)d.value;
+        }
+    }
+    if (tid == 0 && have) {
+        if (a.n_frames) a.n_frames[sid] = frames;
+        if (a.end_pos) a.end_pos[sid] = pos;
+    }
+}
+
+template <int SF>
+cudaError_t launch_sync_sf(const StreamSyncArgs& a, cudaStream_t stream)
+{
+    using S = SyncSmem<SF>;
+    cudaFuncSetAttribute(stream_sync_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
+    const unsigned grid = (a.n_streams + S::G - 1) / S::G;
+    stream_sync_kernel<SF><<<grid, CTA_THREADS, S::bytes, stream>>>(a);
+    return cudaGetLastError();
+}
+
+} // namespace
+
+cudaError_t launch_stream_sync(int sf, const StreamSyncArgs& a, cudaStream_t stream)
+{
+    switch (sf) {
+    case 7: return launch_sync_sf<7>(a, stream);
+    case 8: return launch_sync_sf<8>(a, stream);
+    case 9: return launch_sync_sf<9>(a, stream);
+    case 10: return launch_sync_sf<10>(a, stream);
+    case 11: return launch_sync_sf<11>(a, stream);
+    case 12: return launch_sync_sf<12>(a, stream);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+} // namespace lk

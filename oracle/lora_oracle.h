@@ -94,6 +94,13 @@ long oracle_encode_chain(const oracle_chain_cfg* c, const uint8_t* payload, size
 long oracle_decode_chain(const oracle_chain_cfg* c, const uint16_t* symbols, size_t n_symbols, uint8_t* out,
                          size_t cap, int* flags);
 
+/* Upstream streaming receiver (external/LoRa-SDR/LoRaDemod.cpp:68-117,145-327), restated in
+ * lora_stream_oracle.c: tables, per-window dechirp + fine tune + detect, frame-sync state machine. */
+void oracle_stream_tables(unsigned sf, ocplx* up, ocplx* down, ocplx* fine);
+long oracle_stream_demod(unsigned sf, unsigned sync, float thresh, unsigned mtu, const ocplx* iq, size_t n,
+                         size_t max_frames, uint32_t* frame_start, int32_t* frame_err, int32_t* frame_nsym,
+                         int16_t* symbols, uint32_t* end_pos);
+
 /* Timed CPU arm when oracle/_ref is unavailable: one packet per thread. Returns seconds. */
 double oracle_demod_batch_mt(unsigned sf, int window, unsigned osr, const ocplx* iq,
                              size_t n_packets, size_t samples_per_packet,

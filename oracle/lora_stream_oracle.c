@@ -1,0 +1,172 @@
+/* oracle/lora_stream_oracle.c -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * Plain-C restatement of the upstream streaming receiver the reference vendors under external/LoRa-SDR
+ * (LoRaDemod.cpp:68-117 tables, :145-327 work loop): continuous IQ is consumed one window at a time;
+ * each window is dechirped with the current chirp table and a 128-step fine-tune table, run through the
+ * detector (LoRaDetector.hpp:39-74, restated as oracle_detect) and fed to the frame-sync state machine
+ *   FRAMESYNC (preamble tracking, sync word0 / word1 match) -> DOWNCHIRP0 -> DOWNCHIRP1 (signed bin error
+ *   averaged) -> QUARTERCHIRP (consume N/4 + err/2) -> DATASYMBOLS (emit until mtu or squelch) -> FRAMESYNC.
+ * PARITY STATUS: pinned only by this restatement (the Pothos block is not compilable here and no in-tree
+ * test runs it); the detector and FFT underneath are pinned against the compiled reference.
+ * Upstream leaves _prevValue / _freqError / _finefreqError uninitialised before the first window; 0 here.
+ * The FFT is the in-tree kissfft restatement (oracle_fft), as everywhere else in this oracle.
+ */
+#define _USE_MATH_DEFINES
+#define _DEFAULT_SOURCE
+#include "lora_oracle.h"
+#include <math.h>
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
+#include <stdlib.h>
+#include <string.h>
+
+#define FINE_STEPS 128
+
+/* LoRaDemod.cpp:96-117: std::polar(1.0, double phaseAccum) narrowed to float.  up = conj(entry). */
+void oracle_stream_tables(unsigned sf, ocplx* up, ocplx* down, ocplx* fine /* N * 128 */)
+{
+    const size_t N = (size_t)1 << sf;
+    float phase = (float)-M_PI;
+    double acc = 0.0;
+    for (size_t i = 0; i < N; ++i) {
+        acc += phase;
+        const double re = cos(acc), im = sin(acc);
+        up[i].re = (float)re;   up[i].im = (float)(-im);
+        down[i].re = (float)re; down[i].im = (float)im;
+        phase += (float)((2 * M_PI) / (double)N);
+    }
+    acc = 0.0;
+    phase = (float)(2.0 * M_PI / (double)(N * FINE_STEPS));
+    for (size_t i = 0; i < N * FINE_STEPS; ++i) {
+        acc += phase;
+        fine[i].re = (float)cos(acc);
+        fine[i].im = (float)sin(acc);
+    }
+}
+
+static inline ocplx cmulf(ocplx a, ocplx b)
+{
+    ocplx r;
+    r.re = a.re * b.re - a.im * b.im;
+    r.im = a.re * b.im + a.im * b.re;
+    return r;
+}
+
+/* one window: LoRaDemod.cpp:157-166 (fine-tune index recurrence: int -= float * size_t, truncated) */
+static void dechirp_window(const ocplx* in, const ocplx* chirp, const ocplx* fine, size_t N, int* ft, float fine_err,
+                           ocplx* out)
+{
+    const int wrap = (int)(N * FINE_STEPS);
+    int idx = *ft;
+    for (size_t i = 0; i < N; ++i) {
+        out[i] = cmulf(cmulf(in[i], chirp[i]), fine[idx]);
+        idx = (int)((float)idx - fine_err * (float)FINE_STEPS);
+        if (idx < 0) idx += wrap;
+        else if (idx >= wrap) idx -= wrap;
+    }
+    *ft = idx;
+}
+
+/* Runs the receiver over iq[0, n).  Frames are reported when their DATASYMBOLS state ends (mtu reached or
+ * squelched) -- a frame still open at the end of the buffer is not reported, as upstream would not have
+ * posted it yet.  Per frame: start = sample index of the window that matched sync word0, err = the averaged
+ * down-chirp bin error (_freqError), nsym symbols (int16) at symbols[f * mtu].  Returns the frame count
+ * (frames beyond max_frames are counted but not stored). */
+long oracle_stream_demod(unsigned sf, unsigned sync, float thresh, unsigned mtu, const ocplx* iq, size_t n,
+                         size_t max_frames, uint32_t* frame_start, int32_t* frame_err, int32_t* frame_nsym,
+                         int16_t* symbols, uint32_t* end_pos)
+{
+    const size_t N = (size_t)1 << sf;
+    ocplx* up = (ocplx*)malloc(sizeof(ocplx) * N);
+    ocplx* down = (ocplx*)malloc(sizeof(ocplx) * N);
+    ocplx* fine = (ocplx*)malloc(sizeof(ocplx) * N * FINE_STEPS);
+    ocplx* dec = (ocplx*)malloc(sizeof(ocplx) * N);
+    ocplx* spec = (ocplx*)malloc(sizeof(ocplx) * N);
+    int16_t* cur = (int16_t*)malloc(sizeof(int16_t) * (mtu ? mtu : 1));
+    oracle_stream_tables(sf, up, down, fine);
+    enum { FRAMESYNC, DOWNCHIRP0, DOWNCHIRP1, QUARTERCHIRP, DATASYMBOLS } state = FRAMESYNC;
+    const ocplx* chirp = up;
+    short prev_value = 0;
+    int freq_error = 0, fine_idx = 0;
+    float fine_err = 0.0f;
+    size_t sym_count = 0, pos = 0, frames = 0;
+    uint32_t cur_start = 0;
+    while (pos + 2 * N <= n) {                                           /* :148 */
+        dechirp_window(iq + pos, chirp, fine, N, &fine_idx, fine_err, dec);
+        float power = 0, power_avg = 0, findex = 0;
+        const size_t value = oracle_detect(sf, dec, spec, &power, &power_avg, &findex);
+        const float snr = power - power_avg;
+        const int squelched = snr < thresh;
+        size_t total = 0;
+        switch (state) {
+        case FRAMESYNC: {                                                /* :179-237 */
+            const int syncd = !squelched && (prev_value + 4) / 8 == 0;
+            const int match0 = (value + 4) / 8 == (unsigned)(sync >> 4);
+            int match1 = 0;
+            if (syncd && match0) {
+                int ft = fine_idx;
+                dechirp_window(iq + pos + N, chirp, fine, N, &ft, fine_err, dec);
+                float p1, pa1, f1;
+                const size_t value1 = oracle_detect(sf, dec, spec, &p1, &pa1, &f1);
+                findex = f1; power = p1; power_avg = pa1;              /* detect() overwrites the same variables */
+                match1 = (value1 + 4) / 8 == (unsigned)(sync & 0xf);
+            }
+            if (syncd && match0 && match1) {
+                total = 2 * N;
+                state = DOWNCHIRP0;
+                chirp = down;
+                cur_start = (uint32_t)pos;
+            } else if (!squelched) {
+                total = N - value;
+                fine_err += findex;
+            } else {
+                total = N;
+                fine_err = 0;
+                fine_idx = 0;
+            }
+        } break;
+        case DOWNCHIRP0: {                                               /* :240-250 */
+            state = DOWNCHIRP1;
+            total = N;
+            int error = (int)value;
+            if (value > N / 2) error -= (int)N;
+            freq_error = error;
+        } break;
+        case DOWNCHIRP1: {                                               /* :253-270 */
+            state = QUARTERCHIRP;
+            total = N;
+            chirp = up;
+            int error = (int)value;
+            if (value > N / 2) error -= (int)N;
+            freq_error = (freq_error + error) / 2;
+        } break;
+        case QUARTERCHIRP: {                                             /* :273-283 */
+            state = DATASYMBOLS;
+            total = (size_t)((long)(N / 4) + (long)(freq_error / 2));
+            fine_err += (float)(freq_error / 2);
+            sym_count = 0;
+        } break;
+        case DATASYMBOLS: {                                              /* :286-310 */
+            total = N;
+            cur[sym_count++] = (int16_t)value;
+            if (sym_count >= mtu || squelched) {
+                if (frames < max_frames) {
+                    frame_start[frames] = cur_start;
+                    frame_err[frames] = freq_error;
+                    frame_nsym[frames] = (int32_t)sym_count;
+                    memcpy(symbols + frames * mtu, cur, sizeof(int16_t) * sym_count);
+                }
+                ++frames;
+                fine_err = 0;
+                state = FRAMESYNC;
+            }
+        } break;
+        }
+        pos += total;
+        prev_value = (short)value;
+    }
+    if (end_pos) *end_pos = (uint32_t)pos;
+    free(up); free(down); free(fine); free(dec); free(spec); free(cur);
+    return (long)frames;
+}

@@ -235,6 +235,49 @@ class CpuPhy:
             C.addressof(cfg), symbols.ctypes.data, symbols.size, out.ctypes.data, cap, C.byref(fl))
         return int(r), out[:max(int(r), 0)].copy(), fl.value
 
+    # ---- upstream streaming receiver (oracle restatement only) ----------------------------------
+    def stream_demod(self, iq, sf, sync=0x12, thresh=-30.0, mtu=256, max_frames=16):
+        assert not self.is_ref
+        iq = np.ascontiguousarray(iq, dtype=np.complex64)
+        start = np.zeros(max_frames, np.uint32)
+        err = np.zeros(max_frames, np.int32)
+        nsym = np.zeros(max_frames, np.int32)
+        sym = np.zeros((max_frames, mtu), np.int16)
+        end = C.c_uint32(0)
+        f = self.fn("stream_demod", C.c_long, [C.c_uint, C.c_uint, C.c_float, C.c_uint, C.c_void_p, C.c_size_t, C.c_size_t,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)])
+        n = f(sf, sync, thresh, mtu, iq.ctypes.data, iq.size, max_frames, start.ctypes.data, err.ctypes.data,
+              nsym.ctypes.data, sym.ctypes.data, C.byref(end))
+        return int(n), start, err, nsym, sym, end.value
+
+    def stream_tables(self, sf):
+        assert not self.is_ref
+        N = 1 << sf
+        up, down, fine = np.zeros(N, np.complex64), np.zeros(N, np.complex64), np.zeros(N * 128, np.complex64)
+        self.fn("stream_tables", None, [C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p])(sf, up.ctypes.data, down.ctypes.data,
+                                                                                     fine.ctypes.data)
+        return up, down, fine
+
+    def stream_frame(self, symbols, sf, sync=0x12, ampl=1.0, pad_symbols=2, cfo_bins=0.0):
+        """Upstream frame format (external/LoRa-SDR/LoRaMod.cpp:141-215): 10 upchirps, sync word0 / word1 chirps at
+        (nibble * 8), 2 1/4 downchirps, data chirps, zero padding -- synthesised in float64 on the chirp the
+        upstream receiver's own tables describe (LoRaDemod.cpp:96-106), so a clean frame lands on bin 0.
+        TEST INPUT ONLY: parity is CUDA == oracle on whatever IQ this produces."""
+        N = 1 << sf
+        i = np.arange(N)
+        acc = np.cumsum(-np.pi + 2 * np.pi * i / N)
+        upc = np.exp(1j * acc)
+        parts = [upc] * 10
+        parts.append(upc * np.exp(2j * np.pi * ((sync >> 4) * 8) * i / N))
+        parts.append(upc * np.exp(2j * np.pi * ((sync & 0xf) * 8) * i / N))
+        parts += [np.conj(upc), np.conj(upc), np.conj(upc)[: N // 4]]
+        for sym in symbols:
+            parts.append(upc * np.exp(2j * np.pi * int(sym) * i / N))
+        x = ampl * np.concatenate(parts)
+        if cfo_bins:
+            x = x * np.exp(2j * np.pi * cfo_bins * np.arange(x.size) / N)
+        return np.concatenate([x, np.zeros(pad_symbols * N)]).astype(np.complex64)
+
     # ---- timed batch ---------------------------------------------------------------
     def demod_batch_mt(self, iq, n_packets, spp, sf, osr=1, window=0, threads=1):
         iq = np.ascontiguousarray(iq, dtype=np.complex64)

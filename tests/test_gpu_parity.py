@@ -487,3 +487,55 @@ def test_config1_hello_cr45_explicit_header_crc(phy, lp, oracle):
         assert np.array_equal(out["symbols"][p, :18].cpu().numpy(), o_rx) and int(out["sync"][p]) == 0x12
         assert int(ln[p]) == 5 and bytes(dec[p, :5].cpu().numpy()) == b"Hello" and int(fl[p]) == 0b1100
     assert oracle.decode_chain(oc, o_rx)[1].tobytes() == b"Hello"
+
+
+def check_stream(phy, oracle, rows, sf, thresh, mtu, max_frames, counts=None, sync=0x12):
+    import torch
+    n = max(r.size for r in rows)
+    buf = np.zeros((len(rows), n), np.complex64)
+    for s, r in enumerate(rows):
+        buf[s, :r.size] = r
+    cnt = np.array([r.size for r in rows], np.uint32) if counts is None else counts.astype(np.uint32)
+    out = phy.detect_stream(sf, to_dev(phy, buf), sync_word=sync, thresh_db=thresh, mtu=mtu, max_frames=max_frames,
+                            sample_counts=to_dev(phy, cnt))
+    phy.synchronize()
+    out = {k: v.cpu().numpy() for k, v in out.items()}
+    found = 0
+    for s in range(len(rows)):
+        nf, start, err, nsym, sym, end = oracle.stream_demod(buf[s, :cnt[s]], sf, sync=sync, thresh=thresh, mtu=mtu,
+                                                             max_frames=max_frames)
+        assert out["n_frames"][s] == nf, (sf, s, out["n_frames"][s], nf)
+        assert out["end_pos"][s] == end, (sf, s, out["end_pos"][s], end)
+        k = min(nf, max_frames)
+        assert np.array_equal(out["frame_start"][s, :k].astype(np.uint32), start[:k]), (sf, s)
+        assert np.array_equal(out["frame_err"][s, :k], err[:k]), (sf, s)
+        assert np.array_equal(out["frame_nsym"][s, :k], nsym[:k]), (sf, s)
+        for f in range(k):
+            assert np.array_equal(out["symbols"][s, f, :nsym[f]], sym[f, :nsym[f]]), (sf, s, f)
+        found += nf
+    return found
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
+def test_stream_detector_parity(phy, lp, oracle, sf):
+    """lora_phy_cuda_detect_stream == oracle_stream_demod (upstream LoRaDemod.cpp:145-327): frame count, start sample,
+    averaged down-chirp error, symbol count, symbols and the consumed-sample position, per stream."""
+    from test_stream_oracle import make_stream
+    rng = np.random.default_rng(100 + sf)
+    N = 1 << sf
+    rows = []
+    n_rows = 9 if sf <= 9 else 4
+    for s in range(n_rows):
+        frames = [(rng.integers(0, N, int(rng.integers(3, 24))), float(rng.uniform(-0.4, 0.4)))
+                  for _ in range(int(rng.integers(1, 4)))]
+        rows.append(make_stream(oracle, rng, sf, frames, noise=(0.02, 0.2, 0.5)[s % 3])[0])
+    rows.append((0.3 * (rng.standard_normal(9 * N) + 1j * rng.standard_normal(9 * N))).astype(np.complex64))   # noise only
+    rows.append(np.zeros(5 * N, np.complex64))                                                                # silence
+    rows.append(rows[0][: 2 * N - 1])                                                                         # too short to run
+    rows.append(rows[0][: 14 * N + 7])                                                                        # cut inside a frame
+    assert check_stream(phy, oracle, rows, sf, thresh=-8.0, mtu=32, max_frames=6) >= n_rows
+    # upstream default threshold (never squelches): frames end on mtu only; more frames than max_frames are counted
+    check_stream(phy, oracle, rows[:3], sf, thresh=-30.0, mtu=8, max_frames=2)
+    # a different sync word: nothing matches 0x34 in these streams, alignment logic still replays
+    check_stream(phy, oracle, rows[:2], sf, thresh=-8.0, mtu=16, max_frames=4, sync=0x34)
