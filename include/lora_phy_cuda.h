@@ -151,6 +151,18 @@ long lora_phy_cuda_modulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cu
                                        size_t symbols_per_packet, size_t n_packets,
                                        void* h_iq, size_t packet_stride);
 
+/* Upstream transmitter frame format (external/LoRa-SDR/LoRaMod.cpp:109-238 with the chirp generator of
+ * external/LoRa-SDR/ChirpGenerator.hpp:22-47): per frame 10 up-chirps, sync word0 / word1 chirps at
+ * (nibble*8) bins, 2 1/4 down-chirps, one up-chirp per symbol, padding_symbols symbols of zeros; the phase
+ * runs through the whole frame.  cfg supplies sf, osr (power of two), amplitude (used as given, upstream
+ * default 0.3) and sync_word; bw_hz / window / flags are ignored.  This is the stream
+ * lora_phy_cuda_detect_stream consumes.  Returns samples per frame = lora_phy_cuda_frame_samples(...).   */
+long lora_phy_cuda_frame_samples(uint32_t sf, uint32_t osr, size_t n_symbols, uint32_t padding_symbols);
+long lora_phy_cuda_modulate_frames_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                         uint32_t padding_symbols, const uint16_t* d_symbols,
+                                         size_t symbol_stride, size_t symbols_per_frame, size_t n_frames,
+                                         void* d_iq, size_t frame_stride);
+
 /* Multiply every symbol window by the conjugate downchirp of (sf, osr, bw) in place: the
  * caller-side dechirp every reference test performs before lora_demodulate
  * (tests/e2e_chain_test.cpp:83-92, tests/performance_test.cpp:117-122).                      */

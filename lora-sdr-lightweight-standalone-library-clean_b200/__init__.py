@@ -78,6 +78,8 @@ SIGNATURES = {
     "lora_phy_cuda_detect_batch": (C.c_int, [_vp, _u32, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_modulate_batch": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_modulate_batch_host": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
+    "lora_phy_cuda_frame_samples": (C.c_long, [C.c_uint32, C.c_uint32, _sz, C.c_uint32]),
+    "lora_phy_cuda_modulate_frames_batch": (C.c_long, [_vp, _cfgp, C.c_uint32, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_dechirp_batch": (C.c_int, [_vp, _cfgp, _vp, _sz, _sz, _sz]),
     "lora_phy_cuda_encode_batch": (C.c_long, [_vp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_decode_batch": (C.c_long, [_vp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp]),
@@ -242,6 +244,19 @@ class LoraPhyCuda:
             iq = t.empty((P, n), dtype=t.complex64, device=self.device)
         self._check(self.lib.lora_phy_cuda_modulate_batch(self.h, C.byref(cfg), _ptr(symbols), symbols.stride(0), S, P,
                                                           _ptr(iq), iq.stride(0)))
+        return iq
+
+    def modulate_frames_batch(self, cfg, symbols, padding=1, iq=None):
+        """Upstream frame format (preamble, sync word, 2 1/4 down-chirps, data, padding), one frame per row."""
+        t = self.torch
+        P, S = symbols.shape
+        n = int(self.lib.lora_phy_cuda_frame_samples(cfg.sf, cfg.osr, S, padding))
+        if n < 0:
+            raise LoraPhyError(n, "bad frame geometry")
+        if iq is None:
+            iq = t.empty((P, n), dtype=t.complex64, device=self.device)
+        self._check(self.lib.lora_phy_cuda_modulate_frames_batch(self.h, C.byref(cfg), padding, _ptr(symbols),
+                                                                 symbols.stride(0), S, P, _ptr(iq), iq.stride(0)))
         return iq
 
     def dechirp_batch(self, cfg, iq):

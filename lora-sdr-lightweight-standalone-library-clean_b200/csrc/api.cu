@@ -483,11 +483,49 @@ long lora_phy_cuda_modulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cf
     a.sf = (int)cfg->sf; a.osr = cfg->osr; a.bw_scale = (float)cfg->bw_hz / 125000.0f;
     a.amplitude = cfg->amplitude; a.sync = cfg->sync_word & 0xff;
     a.phase_scratch = static_cast<float*>(ctx->phases.p);
+    a.frame = 0; a.padding = 0;
     unsigned launches = 0;
     cudaError_t e = lk::launch_modulate(a, ctx->sm_count, ctx->stream, &launches);
     ctx->launches += launches;
     if (e != cudaSuccess) return fail(ctx, -EIO, "modulator launch", e);
     return (long)produced;
+}
+
+long lora_phy_cuda_frame_samples(uint32_t sf, uint32_t osr, size_t n_symbols, uint32_t padding_symbols)
+{
+    if (sf < 5 || sf > 12 || osr == 0 || osr > 8) return -EINVAL;
+    const size_t NN = ((size_t)1 << sf) * osr;
+    return (long)((14 + n_symbols + padding_symbols) * NN + NN / 4);
+}
+
+long lora_phy_cuda_modulate_frames_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, uint32_t padding_symbols,
+                                         const uint16_t* d_symbols, size_t symbol_stride, size_t spf,
+                                         size_t n_frames, void* d_iq, size_t frame_stride)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if ((!d_symbols && spf && n_frames) || (!d_iq && n_frames)) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spf > symbol_stride && n_frames > 1) return fail(ctx, -EINVAL, "symbols_per_frame exceeds symbol_stride");
+    if (cfg->osr & (cfg->osr - 1)) return fail(ctx, -EINVAL, "frame format: oversampling must be a power of two");
+    const long produced = lora_phy_cuda_frame_samples(cfg->sf, cfg->osr, spf, padding_symbols);
+    if (produced < 0) return fail(ctx, (int)produced, "bad frame geometry");
+    if ((size_t)produced > frame_stride) return fail(ctx, -ERANGE, "frame_stride smaller than the frame");
+    if (!n_frames) return produced;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CK(ctx->phases.reserve(n_frames * (spf + 15) * sizeof(float)));
+    lk::ModArgs a;
+    a.symbols = d_symbols; a.symbol_stride = symbol_stride; a.symbols_per_packet = (uint32_t)spf;
+    a.n_packets = (uint32_t)n_frames; a.iq = static_cast<cf*>(d_iq); a.packet_stride = frame_stride;
+    a.sf = (int)cfg->sf; a.osr = cfg->osr; a.bw_scale = 1.0f;
+    a.amplitude = cfg->amplitude; a.sync = cfg->sync_word & 0xff;
+    a.phase_scratch = static_cast<float*>(ctx->phases.p);
+    a.frame = 1; a.padding = padding_symbols;
+    unsigned launches = 0;
+    cudaError_t e = lk::launch_modulate(a, ctx->sm_count, ctx->stream, &launches);
+    ctx->launches += launches;
+    if (e != cudaSuccess) return fail(ctx, -EIO, "frame modulator launch", e);
+    return produced;
 }
 
 long lora_phy_cuda_modulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const uint16_t* h_symbols,

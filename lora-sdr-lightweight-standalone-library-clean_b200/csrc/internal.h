@@ -49,8 +49,12 @@ int compact_size_of(int sf);
 struct ModArgs {
     const uint16_t* symbols; size_t symbol_stride; uint32_t symbols_per_packet; uint32_t n_packets;
     cf* iq; size_t packet_stride; int sf; uint32_t osr; float bw_scale; float amplitude; uint32_t sync;
-    float* phase_scratch;   // [n_packets][symbols_per_packet + 2] start phase of every chirp
+    float* phase_scratch;   // [n_packets][chirps] start phase of every chirp
+    int frame;              // 0: shipped framing (2 sync chirps + data); 1: upstream frame format (LoRaMod.cpp:109-238)
+    uint32_t padding;       // frame format: trailing zero symbols
 };
+// chirps per packet: shipped framing n+2; upstream frame 10 up + 2 sync + 2 down + quarter down + n data
+__host__ __device__ inline uint32_t mod_chirps(const ModArgs& a) { return a.symbols_per_packet + (a.frame ? 15u : 2u); }
 cudaError_t launch_modulate(const ModArgs& a, int sm_count, cudaStream_t stream, unsigned* launches);
 cudaError_t launch_dechirp(cf* iq, size_t packet_stride, uint32_t samples_per_packet, uint32_t n_packets,
                            const cf* table, uint32_t table_len, cudaStream_t stream);

@@ -48,6 +48,47 @@ __device__ __forceinline__ unsigned chirp_value(const ModArgs& a, uint32_t pid, 
     return a.symbols[(size_t)pid * a.symbol_stride + (s - 2)];
 }
 
+// ---- upstream frame format (external/LoRa-SDR/LoRaMod.cpp:109-238, ChirpGenerator.hpp:22-47) -------------
+// Constants there are double expressions narrowed to float, f0 = float((2*M_PI*v)/NN), the wrap is all double.
+constexpr double PI_D = 3.14159265358979323846;
+
+__device__ __forceinline__ ChirpConst frame_const(int N, unsigned ovs)
+{
+    ChirpConst c;
+    c.fMin = (float)(-PI_D / (double)(int)ovs);
+    c.fMax = (float)(PI_D / (double)(int)ovs);
+    c.fStep = (float)((2 * PI_D) / (double)(int)(N * ovs * ovs));
+    c.span = fx::fsub(c.fMax, c.fMin);
+    return c;
+}
+
+struct ChirpDesc { float f0; uint32_t len; uint32_t offset; bool down; };
+
+// chirp s of packet pid: start frequency, direction, length and sample offset inside the packet
+__device__ __forceinline__ ChirpDesc chirp_desc(const ModArgs& a, uint32_t pid, uint32_t s, int N, uint32_t step)
+{
+    ChirpDesc d;
+    if (!a.frame) {
+        d.f0 = symbol_f0(chirp_value(a, pid, s), N, a.osr, a.bw_scale);
+        d.len = step; d.offset = s * step; d.down = false;
+        return d;
+    }
+    int v = 0;
+    d.down = s >= 12 && s < 15;
+    d.len = s == 14 ? step / 4 : step;
+    d.offset = s <= 14 ? s * step : 14 * step + step / 4 + (s - 15) * step;
+    if (s == 10) v = (int)((a.sync >> 4) & 0xf) * 8;
+    else if (s == 11) v = (int)(a.sync & 0xf) * 8;
+    else if (s >= 15) v = (int)a.symbols[(size_t)pid * a.symbol_stride + (s - 15)];
+    d.f0 = (float)((2 * PI_D * (double)v) / (double)step);
+    return d;
+}
+
+__device__ __forceinline__ float wrap_phase_frame(float acc)
+{
+    return (float)((double)acc - floor((double)acc / (2 * PI_D)) * 2 * PI_D);
+}
+
 __device__ __forceinline__ float wrap_phase(float acc)
 {
     // ChirpGenerator.hpp:49: floor() is the C double function, the update rounds once
@@ -62,19 +103,20 @@ __global__ void __launch_bounds__(128) mod_phase_kernel(const ModArgs a)
     if (pid >= a.n_packets) return;
     const int N = 1 << a.sf;
     const uint32_t step = (uint32_t)N * a.osr;
-    const ChirpConst c = chirp_const(N, a.osr, a.bw_scale);
-    const uint32_t chirps = a.symbols_per_packet + 2;
+    const ChirpConst c = a.frame ? frame_const(N, a.osr) : chirp_const(N, a.osr, a.bw_scale);
+    const uint32_t chirps = mod_chirps(a);
     float phase = 0.0f;
     float* out = a.phase_scratch + (size_t)pid * chirps;
     for (uint32_t s = 0; s < chirps; ++s) {
         out[s] = phase;
-        float f = fx::fadd(c.fMin, symbol_f0(chirp_value(a, pid, s), N, a.osr, a.bw_scale));
-        for (uint32_t i = 0; i < step; ++i) {
+        const ChirpDesc d = chirp_desc(a, pid, s, N, step);
+        float f = fx::fadd(c.fMin, d.f0);
+        for (uint32_t i = 0; i < d.len; ++i) {
             f = fx::fadd(f, c.fStep);
             if (f > c.fMax) f = fx::fsub(f, c.span);
-            phase = fx::fadd(phase, f);
+            phase = d.down ? fx::fsub(phase, f) : fx::fadd(phase, f);
         }
-        phase = wrap_phase(phase);
+        phase = a.frame ? wrap_phase_frame(phase) : wrap_phase(phase);
     }
 }
 
@@ -86,10 +128,10 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) mod_emit_kernel(const ModArgs
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = 1 << a.sf;
     const uint32_t step = (uint32_t)N * a.osr;
-    const ChirpConst c = chirp_const(N, a.osr, a.bw_scale);
-    const uint32_t chirps = a.symbols_per_packet + 2;
+    const ChirpConst c = a.frame ? frame_const(N, a.osr) : chirp_const(N, a.osr, a.bw_scale);
+    const uint32_t chirps = mod_chirps(a);
     const unsigned long long n_chirps = (unsigned long long)a.n_packets * chirps;
-    const float amp = fmaxf(-1.0f, fminf(1.0f, a.amplitude));      // LoRaMod.cpp:18
+    const float amp = a.frame ? a.amplitude : fmaxf(-1.0f, fminf(1.0f, a.amplitude));      // LoRaMod.cpp:18 (upstream: as given)
     const unsigned long long warps_total = (unsigned long long)gridDim.x * EMIT_WARPS;
     for (unsigned long long w = (unsigned long long)blockIdx.x * EMIT_WARPS + warp; w * 32 < n_chirps; w += warps_total) {
         const unsigned long long chirp = w * 32 + lane;
@@ -97,13 +139,16 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) mod_emit_kernel(const ModArgs
         const uint32_t pid = active ? (uint32_t)(chirp / chirps) : 0;
         const uint32_t s = active ? (uint32_t)(chirp % chirps) : 0;
         float phase = active ? a.phase_scratch[chirp] : 0.0f;
-        float f = fx::fadd(c.fMin, symbol_f0(active ? chirp_value(a, pid, s) : 0, N, a.osr, a.bw_scale));
+        ChirpDesc d = chirp_desc(a, pid, active ? s : 0, N, step);
+        if (!active) d.len = 0;
+        float f = fx::fadd(c.fMin, d.f0);
         for (uint32_t j0 = 0; j0 < step; j0 += 32) {
             const uint32_t jn = min(32u, step - j0);
-            for (uint32_t j = 0; j < jn; ++j) {
+            const uint32_t jm = j0 < d.len ? min(jn, d.len - j0) : 0;
+            for (uint32_t j = 0; j < jm; ++j) {
                 f = fx::fadd(f, c.fStep);
                 if (f > c.fMax) f = fx::fsub(f, c.span);
-                phase = fx::fadd(phase, f);
+                phase = d.down ? fx::fsub(phase, f) : fx::fadd(phase, f);
                 float sn, cs;
                 gm::sincosf_g(phase, &sn, &cs);
                 tile[warp][lane][j] = fx::mk(fx::fmul(amp, cs), fx::fmul(amp, sn));
@@ -113,11 +158,23 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) mod_emit_kernel(const ModArgs
                 const unsigned long long ch = w * 32 + r;
                 if (ch < n_chirps && (uint32_t)lane < jn) {
                     const uint32_t rp = (uint32_t)(ch / chirps), rs = (uint32_t)(ch % chirps);
-                    a.iq[(size_t)rp * a.packet_stride + (size_t)rs * step + j0 + lane] = tile[warp][r][lane];
+                    uint32_t off = rs * step, len = step;
+                    if (a.frame) {
+                        len = rs == 14 ? step / 4 : step;
+                        off = rs <= 14 ? rs * step : 14 * step + step / 4 + (rs - 15) * step;
+                    }
+                    if (j0 + lane < len) a.iq[(size_t)rp * a.packet_stride + off + j0 + lane] = tile[warp][r][lane];
                 }
             }
             __syncwarp();
         }
+    }
+    if (a.frame && a.padding) {                                     // LoRaMod.cpp:226-236: padding symbols of zeros
+        const uint32_t pad = a.padding * step, body = 14 * step + step / 4 + a.symbols_per_packet * step;
+        const unsigned long long total = (unsigned long long)a.n_packets * pad;
+        for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+             i += (unsigned long long)gridDim.x * blockDim.x)
+            a.iq[(size_t)(i / pad) * a.packet_stride + body + (uint32_t)(i % pad)] = fx::mk(0.0f, 0.0f);
     }
 }
 
@@ -126,7 +183,7 @@ cudaError_t launch_modulate(const ModArgs& a, int sm_count, cudaStream_t stream,
     if (a.n_packets == 0) return cudaSuccess;
     mod_phase_kernel<<<(a.n_packets + 127) / 128, 128, 0, stream>>>(a);
     ++*launches;
-    const unsigned long long n_chirps = (unsigned long long)a.n_packets * (a.symbols_per_packet + 2);
+    const unsigned long long n_chirps = (unsigned long long)a.n_packets * mod_chirps(a);
     unsigned long long need = (n_chirps + EMIT_WARPS * 32 - 1) / (EMIT_WARPS * 32);
     unsigned max_ctas = (unsigned)sm_count * 64u;
     mod_emit_kernel<<<need < max_ctas ? (unsigned)need : max_ctas, EMIT_WARPS * 32, 0, stream>>>(a);

@@ -170,3 +170,54 @@ long oracle_stream_demod(unsigned sf, unsigned sync, float thresh, unsigned mtu,
     free(up); free(down); free(fine); free(dec); free(spec); free(cur);
     return (long)frames;
 }
+
+/* ---- upstream transmitter: frame format (external/LoRa-SDR/LoRaMod.cpp:109-238) ------------------------
+ * genChirp as vendored upstream (external/LoRa-SDR/ChirpGenerator.hpp:22-47): the constants are double
+ * expressions narrowed to float, the ramp and the phase are float recurrences, the sample is
+ * std::polar(ampl, phase) = (ampl*cosf, ampl*sinf), and the phase is wrapped in double after each chirp. */
+static size_t upstream_gen_chirp(ocplx* out, int N, int ovs, int NN, float f0, int down, float ampl, float* phase)
+{
+    const float fMin = (float)(-M_PI / ovs);
+    const float fMax = (float)(M_PI / ovs);
+    const float fStep = (float)((2 * M_PI) / (N * ovs * ovs));
+    float f = fMin + f0;
+    float acc = *phase;
+    int i;
+    for (i = 0; i < NN; ++i) {
+        f += fStep;
+        if (f > fMax) f -= (fMax - fMin);
+        if (down) acc -= f; else acc += f;
+        out[i].re = ampl * cosf(acc);
+        out[i].im = ampl * sinf(acc);
+    }
+    acc = (float)((double)acc - floor((double)acc / (2 * M_PI)) * 2 * M_PI);
+    *phase = acc;
+    return (size_t)i;
+}
+
+size_t oracle_frame_samples(unsigned sf, unsigned ovs, size_t n_symbols, unsigned padding)
+{
+    const size_t NN = ((size_t)1 << sf) * ovs;
+    return (14 + n_symbols + padding) * NN + NN / 4;
+}
+
+/* One frame: 10 up-chirps (:141-146), sync word0 / word1 at (nibble*8) bins (:151-170), two down-chirps and
+ * a quarter down-chirp (:175-202), one up-chirp per symbol (:207-221), `padding` symbols of zeros (:226-236). */
+size_t oracle_frame_modulate(const uint16_t* symbols, size_t n, ocplx* out, unsigned sf, unsigned ovs, unsigned sync,
+                             float ampl, unsigned padding)
+{
+    const int N = 1 << sf, NN = N * (int)ovs;
+    float phase = 0.0f;
+    size_t o = 0;
+    for (int k = 0; k < 10; ++k) o += upstream_gen_chirp(out + o, N, (int)ovs, NN, 0.0f, 0, ampl, &phase);
+    const int sw0 = (int)((sync >> 4) & 0xf) * 8, sw1 = (int)(sync & 0xf) * 8;
+    o += upstream_gen_chirp(out + o, N, (int)ovs, NN, (float)((2 * M_PI * sw0) / NN), 0, ampl, &phase);
+    o += upstream_gen_chirp(out + o, N, (int)ovs, NN, (float)((2 * M_PI * sw1) / NN), 0, ampl, &phase);
+    o += upstream_gen_chirp(out + o, N, (int)ovs, NN, 0.0f, 1, ampl, &phase);
+    o += upstream_gen_chirp(out + o, N, (int)ovs, NN, 0.0f, 1, ampl, &phase);
+    o += upstream_gen_chirp(out + o, N, (int)ovs, NN / 4, 0.0f, 1, ampl, &phase);
+    for (size_t s = 0; s < n; ++s)
+        o += upstream_gen_chirp(out + o, N, (int)ovs, NN, (float)((2 * M_PI * (int)symbols[s]) / NN), 0, ampl, &phase);
+    memset(out + o, 0, sizeof(ocplx) * (size_t)padding * (size_t)NN);
+    return o + (size_t)padding * (size_t)NN;
+}

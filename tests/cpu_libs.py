@@ -258,6 +258,17 @@ class CpuPhy:
                                                                                      fine.ctypes.data)
         return up, down, fine
 
+    def frame_modulate(self, symbols, sf, ovs=1, sync=0x12, ampl=0.3, padding=1):
+        assert not self.is_ref
+        symbols = np.ascontiguousarray(symbols, dtype=np.uint16)
+        n = self.fn("frame_samples", C.c_size_t, [C.c_uint, C.c_uint, C.c_size_t, C.c_uint])(sf, ovs, symbols.size, padding)
+        out = np.zeros(n, np.complex64)
+        f = self.fn("frame_modulate", C.c_size_t, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_uint, C.c_uint, C.c_uint,
+                                                   C.c_float, C.c_uint])
+        got = f(symbols.ctypes.data, symbols.size, out.ctypes.data, sf, ovs, sync, ampl, padding)
+        assert got == n
+        return out
+
     def stream_frame(self, symbols, sf, sync=0x12, ampl=1.0, pad_symbols=2, cfo_bins=0.0):
         """Upstream frame format (external/LoRa-SDR/LoRaMod.cpp:141-215): 10 upchirps, sync word0 / word1 chirps at
         (nibble * 8), 2 1/4 downchirps, data chirps, zero padding -- synthesised in float64 on the chirp the

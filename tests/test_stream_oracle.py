@@ -50,3 +50,21 @@ def test_noise_only_and_mtu(oracle):
     iq, _ = make_stream(oracle, rng, 7, [(syms, 0.0)])
     n, start, err, nsym, sym, end = oracle.stream_demod(iq, 7, thresh=-30.0, mtu=16, max_frames=4)
     assert n >= 1 and nsym[0] == 16 and np.array_equal(sym[0, :16], syms[:16])
+
+
+@pytest.mark.parametrize("sf", [7, 9, 12])
+def test_upstream_transmitter_into_upstream_receiver(oracle, sf):
+    """external/LoRa-SDR/LoRaMod.cpp:109-238 frames (restated) through the restated receiver: the preamble tracking
+    locks one sample early (the transmitter's ramp leads the receiver's table by one step) and every symbol survives."""
+    rng = np.random.default_rng(sf)
+    N = 1 << sf
+    syms = rng.integers(0, N, 24)
+    fr = oracle.frame_modulate(syms, sf, ampl=0.3, padding=2)
+    assert fr.size == (14 + 24 + 2) * N + N // 4
+    assert np.all(fr[-2 * N:] == 0) and np.allclose(np.abs(fr[:-2 * N]), 0.3, atol=1e-6)
+    lead = 3 * N + 17
+    iq = np.concatenate([np.zeros(lead, np.complex64), fr, np.zeros(3 * N, np.complex64)])
+    iq = (iq + 0.005 * (rng.standard_normal(iq.size) + 1j * rng.standard_normal(iq.size))).astype(np.complex64)
+    n, start, err, nsym, sym, end = oracle.stream_demod(iq, sf, thresh=-8.0, mtu=64, max_frames=4)
+    assert n == 1 and abs(int(start[0]) - (lead + 10 * N)) <= 1 and err[0] == 0
+    assert np.array_equal(sym[0, :24], syms)
