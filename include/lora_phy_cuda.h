@@ -246,6 +246,27 @@ int lora_phy_cuda_decode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda
                                      const int32_t* d_symbol_counts, size_t n_symbols, size_t n_packets,
                                      uint8_t* d_payload, size_t payload_stride, int32_t* d_len, uint8_t* d_flags);
 
+/* ---- AWGN Monte-Carlo driver (BASELINE.json configs[4]) ---------------------------------------- */
+/* For packets first_packet .. first_packet + n_packets - 1 of sweep cell cell_id, entirely on the device:
+ * draw payload_len payload bytes (Philox4x32-10 keyed by seed; counter = byte group, packet, cell) ->
+ * upstream coding chain (cc) -> lora_modulate (LoRaMod.cpp:8-43; SF cc->sf, BW125, osr 1, amplitude 1,
+ * sync 0x12) -> add complex Gaussian noise of standard deviation noise_std per I/Q component (Box-Muller
+ * on the same Philox stream; SNR = -10 log10(2 noise_std^2)) and dechirp -> lora_demodulate
+ * (LoRaDemod.cpp:50-197) -> decode chain -> compare with what was sent.  The reference ships no AWGN
+ * code; the channel is defined in csrc/montecarlo.cu and restated in oracle/lora_mc_oracle.c so that
+ * any packet can be regenerated and replayed on the host.  Packet ranges are independent: shard a
+ * sweep over GPUs by giving each its own [first_packet, n_packets).
+ *   d_counts[8] uint64, ACCUMULATED (zero it first): packets, packet errors, packets the decoder dropped
+ *               or mis-sized, bit errors, bits compared, symbol errors, symbols compared, sync-word errors
+ *   d_packet_ok [n_packets] (may be NULL); d_rx_symbols / d_rx_payload / d_rx_len (may be NULL):
+ *               demodulated symbols, decoded bytes (payload_len per packet) and decoder length per packet
+ * Work is chunked so that the IQ scratch stays below 4 GiB (LORA_PHY_MC_SCRATCH_MB).                */
+int lora_phy_cuda_awgn_roundtrip(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_chain_cfg* cc, float noise_std,
+                                 uint64_t seed, uint32_t cell_id, uint64_t first_packet, size_t n_packets,
+                                 size_t payload_len, uint64_t* d_counts, uint8_t* d_packet_ok,
+                                 uint16_t* d_rx_symbols, size_t rx_symbol_stride, uint8_t* d_rx_payload,
+                                 size_t rx_payload_stride, int32_t* d_rx_len);
+
 /* ---- tables (parity tests read these back) -------------------------------------------------- */
 /* which: 0 = kissfft twiddles (kissfft.hh:24-29), 1 = Hann window (LoRaDemod.cpp:18-24),
  * 2 = downchirp for cfg bw (phy.cpp:205-208).  Copies N entries to host memory.                */

@@ -78,6 +78,8 @@ SIGNATURES = {
     "lora_phy_cuda_detect_batch": (C.c_int, [_vp, _u32, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_modulate_batch": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_modulate_batch_host": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
+    "lora_phy_cuda_awgn_roundtrip": (C.c_int, [_vp, C.POINTER(ChainCfg), C.c_float, C.c_uint64, C.c_uint32, C.c_uint64, _sz,
+                                               _sz, _vp, _vp, _vp, _sz, _vp, _sz, _vp]),
     "lora_phy_cuda_frame_samples": (C.c_long, [C.c_uint32, C.c_uint32, _sz, C.c_uint32]),
     "lora_phy_cuda_modulate_frames_batch": (C.c_long, [_vp, _cfgp, C.c_uint32, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_dechirp_batch": (C.c_int, [_vp, _cfgp, _vp, _sz, _sz, _sz]),
@@ -323,6 +325,30 @@ class LoraPhyCuda:
         self._check(self.lib.lora_phy_cuda_decode_chain_batch(self.h, C.byref(cc), _ptr(symbols), symbols.stride(0),
                                                               _ptr(counts), S, P, _ptr(pay), payload_stride, _ptr(ln), _ptr(fl)))
         return pay, ln, fl
+
+    def awgn_roundtrip(self, cc, snr_db, n_packets, payload_len, seed=0xA76E, cell_id=0, first_packet=0, counts=None,
+                       details=False, noise_std=None):
+        """One cell of the Monte-Carlo sweep.  Returns (counts tensor[8] uint64-as-int64, details dict or None)."""
+        import math
+        t = self.torch
+        if noise_std is None:
+            noise_std = math.sqrt(10.0 ** (-snr_db / 10.0) / 2.0)
+        if counts is None:
+            counts = t.zeros(8, dtype=t.int64, device=self.device)
+        det = None
+        args = [None, 0, None, 0, None]
+        ok = None
+        if details:
+            nsym = self.chain_symbols(cc, payload_len)
+            det = dict(ok=t.zeros(n_packets, dtype=t.uint8, device=self.device),
+                       rx_symbols=t.zeros((n_packets, nsym), dtype=t.uint16, device=self.device),
+                       rx_payload=t.zeros((n_packets, max(payload_len, 1)), dtype=t.uint8, device=self.device),
+                       rx_len=t.zeros(n_packets, dtype=t.int32, device=self.device))
+            ok = det["ok"]
+            args = [_ptr(det["rx_symbols"]), nsym, _ptr(det["rx_payload"]), max(payload_len, 1), _ptr(det["rx_len"])]
+        self._check(self.lib.lora_phy_cuda_awgn_roundtrip(self.h, C.byref(cc), noise_std, seed, cell_id, first_packet,
+                                                          n_packets, payload_len, _ptr(counts), _ptr(ok), *args))
+        return counts, det
 
     def copy_table(self, sf, which, bw_hz=125000):
         import numpy as np

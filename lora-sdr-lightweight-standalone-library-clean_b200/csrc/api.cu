@@ -4,6 +4,7 @@
 #include "demod_device.cuh"
 #include "internal.h"
 
+#include <algorithm>
 #include <cerrno>
 #include <cmath>
 #include <complex>
@@ -67,6 +68,9 @@ struct lora_phy_cuda_ctx {
     DevBuf state, phases, tmp, sched;                   // PacketState[], modulator phases, compensate scratch, fused-kernel counters
     uint32_t lookahead_bytes = 64u << 20;               // fused schedule look-ahead (LORA_PHY_LOOKAHEAD_MB)
     cf* sync_tab[13] = { nullptr };                      // stream detector tables per sf: up | down | fine (stream_sync.cu)
+    DevBuf mc[8];                                        // Monte-Carlo driver: payload, tx symbols, IQ, rx symbols, status+sync, decoded, len, flags
+    std::mutex mc_mu;
+    size_t mc_scratch_bytes = (size_t)4 << 30;           // IQ bytes per Monte-Carlo chunk (LORA_PHY_MC_SCRATCH_MB)
     DevBuf lfsr;                                         // dewhitening byte table of the coding chain (chain.cu)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
@@ -176,6 +180,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
     for (auto& kv : ctx->chirps) cudaFree(kv.second);
     for (int sf = 0; sf <= 12; ++sf) if (ctx->sync_tab[sf]) cudaFree(ctx->sync_tab[sf]);
     ctx->lfsr.release();
+    for (auto& b : ctx->mc) b.release();
     ctx->state.release(); ctx->phases.release(); ctx->tmp.release(); ctx->sched.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
     ctx->h_in.release(); ctx->h_out.release();
@@ -797,6 +802,95 @@ int lora_phy_cuda_decode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda
                                static_cast<const uint8_t*>(ctx->lfsr.p), d_payload, payload_stride, d_len, d_flags,
                                ctx->sm_count, ctx->stream));
     ++ctx->launches;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// AWGN Monte-Carlo driver (BASELINE.json configs[4]): per chunk of packets, all on the device,
+//   payload draw -> coding chain -> lora_modulate -> channel + dechirp -> demodulate -> decode chain -> score.
+int lora_phy_cuda_awgn_roundtrip(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_chain_cfg* cc, float noise_std,
+                                 uint64_t seed, uint32_t cell_id, uint64_t first_packet, size_t n_packets,
+                                 size_t payload_len, uint64_t* d_counts, uint8_t* d_packet_ok,
+                                 uint16_t* d_rx_symbols, size_t rx_symbol_stride, uint8_t* d_rx_payload,
+                                 size_t rx_payload_stride, int32_t* d_rx_len)
+{
+    if (!ctx) return -EINVAL;
+    if (!cc || !d_counts) return fail(ctx, -EINVAL, "NULL argument");
+    if (payload_len > 255) return fail(ctx, -EINVAL, "payload_len exceeds 255");
+    if (!(noise_std >= 0.0f)) return fail(ctx, -EINVAL, "noise_std must be >= 0");
+    const long nsym_l = lora_phy_cuda_chain_symbols(cc, payload_len);
+    if (nsym_l <= 0) return fail(ctx, -EINVAL, "bad chain configuration");
+    const size_t nsym = (size_t)nsym_l, N = (size_t)1 << cc->sf, spp = (nsym + 2) * N;
+    if ((d_rx_symbols && rx_symbol_stride < nsym) || (d_rx_payload && rx_payload_stride < payload_len))
+        return fail(ctx, -ERANGE, "output stride too small");
+    if (!n_packets) return 0;
+    std::lock_guard<std::mutex> mc_lock(ctx->mc_mu);
+    Guard g(ctx->device);
+    if (const char* e = getenv("LORA_PHY_MC_SCRATCH_MB")) {
+        const long mb = atol(e);
+        if (mb > 0) ctx->mc_scratch_bytes = (size_t)mb << 20;
+    }
+    size_t chunk = ctx->mc_scratch_bytes / (spp * sizeof(cf));
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_packets) chunk = n_packets;
+    const size_t dec_stride = 260;
+    CK(ctx->mc[0].reserve(chunk * 256));
+    CK(ctx->mc[1].reserve(chunk * nsym * 2));
+    CK(ctx->mc[2].reserve(chunk * spp * sizeof(cf)));
+    CK(ctx->mc[3].reserve(chunk * nsym * 2));
+    CK(ctx->mc[4].reserve(chunk * 8));
+    CK(ctx->mc[5].reserve(chunk * dec_stride));
+    CK(ctx->mc[6].reserve(chunk * 4));
+    CK(ctx->mc[7].reserve(chunk));
+    lora_phy_cuda_cfg cfg = { cc->sf, 125000u, 1u, 0u, 0u, 0x12u, 1.0f, 0u };
+    cf* table = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        int rc = get_chirp(ctx, (int)cc->sf, 125000, 1, &table);
+        if (rc) return rc;
+    }
+    uint8_t* pay = static_cast<uint8_t*>(ctx->mc[0].p);
+    uint16_t* txs = static_cast<uint16_t*>(ctx->mc[1].p);
+    cf* iq = static_cast<cf*>(ctx->mc[2].p);
+    uint16_t* rxs = static_cast<uint16_t*>(ctx->mc[3].p);
+    int32_t* status = static_cast<int32_t*>(ctx->mc[4].p);
+    uint8_t* sync = reinterpret_cast<uint8_t*>(status + chunk);
+    uint8_t* dec = static_cast<uint8_t*>(ctx->mc[5].p);
+    int32_t* len = static_cast<int32_t*>(ctx->mc[6].p);
+    uint8_t* flags = static_cast<uint8_t*>(ctx->mc[7].p);
+    for (size_t done = 0; done < n_packets; done += chunk) {
+        const size_t n = std::min(chunk, n_packets - done);
+        lk::McArgs a;
+        a.seed = seed; a.first_packet = first_packet + done; a.cell = cell_id; a.n_packets = (uint32_t)n;
+        a.payload = pay; a.payload_stride = 256; a.payload_len = (uint32_t)payload_len;
+        a.iq = iq; a.packet_stride = spp; a.spp = (uint32_t)spp; a.chirp = table; a.chirp_len = (uint32_t)N;
+        a.noise_std = noise_std;
+        a.tx_sym = txs; a.rx_sym = rxs; a.sym_stride = nsym; a.n_sym = (uint32_t)nsym;
+        a.rx_payload = dec; a.rx_stride = dec_stride; a.rx_len = len; a.status = status; a.sync = sync;
+        a.sync_word = 0x12; a.counts = reinterpret_cast<unsigned long long*>(d_counts);
+        a.packet_ok = d_packet_ok ? d_packet_ok + done : nullptr;
+        CK(lk::launch_mc_payload(a, ctx->sm_count, ctx->stream));
+        ++ctx->launches;
+        long r = lora_phy_cuda_encode_chain_batch(ctx, cc, pay, 256, payload_len, n, txs, nsym);
+        if (r < 0) return (int)r;
+        r = lora_phy_cuda_modulate_batch(ctx, &cfg, txs, nsym, nsym, n, iq, spp);
+        if (r < 0) return (int)r;
+        CK(lk::launch_awgn_dechirp(a, ctx->sm_count, ctx->stream));
+        ++ctx->launches;
+        int rc = lora_phy_cuda_demodulate_batch(ctx, &cfg, iq, spp, nullptr, spp, n, rxs, nsym, sync, nullptr, nullptr, status);
+        if (rc < 0) return rc;
+        rc = lora_phy_cuda_decode_chain_batch(ctx, cc, rxs, nsym, status, nsym, n, dec, dec_stride, len, flags);
+        if (rc < 0) return rc;
+        CK(lk::launch_mc_score(a, ctx->stream));
+        ++ctx->launches;
+        if (d_rx_symbols)
+            CK(cudaMemcpy2DAsync(d_rx_symbols + done * rx_symbol_stride, rx_symbol_stride * 2, rxs, nsym * 2, nsym * 2, n,
+                                 cudaMemcpyDeviceToDevice, ctx->stream));
+        if (d_rx_payload && payload_len)
+            CK(cudaMemcpy2DAsync(d_rx_payload + done * rx_payload_stride, rx_payload_stride, dec, dec_stride, payload_len, n,
+                                 cudaMemcpyDeviceToDevice, ctx->stream));
+        if (d_rx_len) CK(cudaMemcpyAsync(d_rx_len + done, len, n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
     return 0;
 }
 

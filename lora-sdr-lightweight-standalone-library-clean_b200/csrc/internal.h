@@ -67,6 +67,19 @@ cudaError_t launch_compensate(const cf* in, cf* out, size_t packet_stride, uint3
                               uint32_t n_packets, int sf, uint32_t osr, const float* cfo,
                               const float* time_offset, cudaStream_t stream);
 
+// montecarlo.cu: AWGN Monte-Carlo driver kernels (payload draw, channel + dechirp, scoring)
+struct McArgs {
+    unsigned long long seed, first_packet; uint32_t cell; uint32_t n_packets;
+    uint8_t* payload; size_t payload_stride; uint32_t payload_len;
+    cf* iq; size_t packet_stride; uint32_t spp; const cf* chirp; uint32_t chirp_len; float noise_std;
+    const uint16_t* tx_sym; const uint16_t* rx_sym; size_t sym_stride; uint32_t n_sym;
+    const uint8_t* rx_payload; size_t rx_stride; const int32_t* rx_len; const int32_t* status; const uint8_t* sync;
+    uint32_t sync_word; unsigned long long* counts; uint8_t* packet_ok;
+};
+cudaError_t launch_mc_payload(const McArgs& a, int sm_count, cudaStream_t stream);
+cudaError_t launch_awgn_dechirp(const McArgs& a, int sm_count, cudaStream_t stream);
+cudaError_t launch_mc_score(const McArgs& a, cudaStream_t stream);
+
 // stream_sync.cu: sliding-window preamble / sync-word detector on continuous IQ, one thread group per stream
 struct StreamSyncArgs {
     const cf* iq; size_t stream_stride; const uint32_t* counts; uint32_t n_samples; uint32_t n_streams;

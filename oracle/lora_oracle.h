@@ -105,6 +105,14 @@ size_t oracle_frame_samples(unsigned sf, unsigned ovs, size_t n_symbols, unsigne
 size_t oracle_frame_modulate(const uint16_t* symbols, size_t n, ocplx* out, unsigned sf, unsigned ovs, unsigned sync,
                              float ampl, unsigned padding);
 
+/* AWGN Monte-Carlo spot check (lora_mc_oracle.c): Philox4x32-10, payload / noise draws, one packet round trip. */
+void oracle_philox4x32(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
+void oracle_mc_payload(uint64_t seed, uint32_t cell, uint64_t packet, size_t len, uint8_t* out);
+void oracle_mc_noise_sample(uint64_t seed, uint32_t cell, uint64_t packet, uint32_t i, float std, float* re, float* im);
+long oracle_awgn_roundtrip(const oracle_chain_cfg* cc, float noise_std, uint64_t seed, uint32_t cell, uint64_t packet,
+                           size_t payload_len, uint8_t* tx_payload, uint16_t* tx_sym, uint16_t* rx_sym,
+                           uint8_t* rx_payload, size_t rx_cap, int* flags);
+
 /* Timed CPU arm when oracle/_ref is unavailable: one packet per thread. Returns seconds. */
 double oracle_demod_batch_mt(unsigned sf, int window, unsigned osr, const ocplx* iq,
                              size_t n_packets, size_t samples_per_packet,

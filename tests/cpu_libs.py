@@ -235,6 +235,41 @@ class CpuPhy:
             C.addressof(cfg), symbols.ctypes.data, symbols.size, out.ctypes.data, cap, C.byref(fl))
         return int(r), out[:max(int(r), 0)].copy(), fl.value
 
+    # ---- AWGN Monte-Carlo spot check ------------------------------------------------------------
+    def philox(self, ctr, key):
+        c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()
+        self.fn("philox4x32", None, [C.c_void_p, C.c_void_p, C.c_void_p])(c, k, o)
+        return list(o)
+
+    def mc_payload(self, seed, cell, packet, n):
+        out = np.zeros(n, np.uint8)
+        self.fn("mc_payload", None, [C.c_uint64, C.c_uint32, C.c_uint64, C.c_size_t, C.c_void_p])(seed, cell, packet, n,
+                                                                                                 out.ctypes.data)
+        return out
+
+    def mc_noise(self, seed, cell, packet, n, std):
+        f = self.fn("mc_noise_sample", None, [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.c_float,
+                                              C.POINTER(C.c_float), C.POINTER(C.c_float)])
+        out = np.zeros(n, np.complex64)
+        re, im = C.c_float(0), C.c_float(0)
+        for i in range(n):
+            f(seed, cell, packet, i, std, C.byref(re), C.byref(im))
+            out[i] = re.value + 1j * im.value
+        return out
+
+    def awgn_roundtrip(self, cfg, noise_std, seed, cell, packet, payload_len):
+        """-> dict(tx_payload, tx_sym, rx_sym, rx_payload, length, flags) for one packet of the sweep"""
+        nsym = self.fn("chain_num_symbols", C.c_size_t, [C.c_void_p, C.c_size_t])(C.addressof(cfg), payload_len)
+        txp, rxp = np.zeros(max(payload_len, 1), np.uint8), np.zeros(600, np.uint8)
+        txs, rxs = np.zeros(nsym, np.uint16), np.zeros(nsym, np.uint16)
+        fl = C.c_int(0)
+        f = self.fn("awgn_roundtrip", C.c_long, [C.c_void_p, C.c_float, C.c_uint64, C.c_uint32, C.c_uint64, C.c_size_t,
+                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, i32p])
+        r = f(C.addressof(cfg), noise_std, seed, cell, packet, payload_len, txp.ctypes.data, txs.ctypes.data,
+              rxs.ctypes.data, rxp.ctypes.data, rxp.size, C.byref(fl))
+        return dict(tx_payload=txp[:payload_len], tx_sym=txs, rx_sym=rxs, rx_payload=rxp[:max(int(r), 0)].copy(),
+                    length=int(r), flags=fl.value)
+
     # ---- upstream streaming receiver (oracle restatement only) ----------------------------------
     def stream_demod(self, iq, sf, sync=0x12, thresh=-30.0, mtu=256, max_frames=16):
         assert not self.is_ref

@@ -606,3 +606,50 @@ def test_stream_end_to_end_payload(phy, lp, oracle, sf):
         nf, start, err, ns, osym, end = oracle.stream_demod(buf[s], sf, thresh=-8.0, mtu=nsym, max_frames=F + 1)
         assert nf == F and np.array_equal(out["frame_start"][s, :F].cpu().numpy().astype(np.uint32), start[:F])
         assert np.array_equal(out["symbols"][s, :F].cpu().numpy(), osym[:F])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf,cr,snr_db", [(7, 4, -6.0), (7, 1, -12.0), (8, 2, -9.0), (9, 4, -12.0), (10, 3, -15.0),
+                                          (11, 4, -17.0), (12, 4, -20.0), (7, 4, 3.0)])
+def test_awgn_roundtrip_spot_check(phy, lp, oracle, sf, cr, snr_db):
+    """BASELINE configs[4] spot check: every packet of a Monte-Carlo cell regenerated on the host from the same
+    Philox stream and run through the oracle gives the same demodulated symbols, decoded bytes, decoder length and
+    verdict; the accumulated counters are the sums of those per-packet results."""
+    import math
+    P = 48 if sf <= 9 else (12 if sf <= 11 else 6)
+    L = 13
+    first = (1 << 33) + 5                                     # exercises the high counter word
+    cell = sf << 8 | 3
+    cc = lp.make_chain_cfg(sf, cr=cr)
+    oc = oracle.chain_cfg(sf, cr=cr)
+    std = np.float32(math.sqrt(10.0 ** (-snr_db / 10.0) / 2.0))
+    counts, det = phy.awgn_roundtrip(cc, snr_db, P, L, seed=0xA76E, cell_id=cell, first_packet=first, details=True,
+                                     noise_std=float(std))
+    phy.synchronize()
+    counts = counts.cpu().numpy()
+    det = {k: v.cpu().numpy() for k, v in det.items()}
+    exp = np.zeros(8, np.int64)
+    for p in range(P):
+        r = oracle.awgn_roundtrip(oc, float(std), 0xA76E, cell, first + p, L)
+        assert np.array_equal(det["rx_symbols"][p], r["rx_sym"]), (sf, p)
+        assert det["rx_len"][p] == r["length"], (sf, p)
+        n = max(min(r["length"], L), 0)
+        assert np.array_equal(det["rx_payload"][p, :n], r["rx_payload"][:n]), (sf, p)
+        ok = r["length"] == L and np.array_equal(r["rx_payload"], r["tx_payload"])
+        assert bool(det["ok"][p]) == ok
+        be = int(np.unpackbits(r["rx_payload"][:n] ^ r["tx_payload"][:n]).sum())
+        exp += np.array([1, not ok, r["length"] != L, be, 8 * n, int(np.sum(r["rx_sym"] != r["tx_sym"])), r["tx_sym"].size, 0])
+    assert np.array_equal(counts[:7], exp[:7]), (counts, exp)
+    if snr_db > 0:
+        assert counts[1] == 0 and counts[7] == 0
+    # chunking and packet-range sharding do not change anything: two halves with a tiny scratch == one call
+    import os
+    os.environ["LORA_PHY_MC_SCRATCH_MB"] = "1"
+    try:
+        c2, _ = phy.awgn_roundtrip(cc, snr_db, P // 2, L, cell_id=cell, first_packet=first, noise_std=float(std))
+        c2, _ = phy.awgn_roundtrip(cc, snr_db, P - P // 2, L, cell_id=cell, first_packet=first + P // 2, counts=c2,
+                                   noise_std=float(std))
+        phy.synchronize()
+    finally:
+        os.environ["LORA_PHY_MC_SCRATCH_MB"] = "4096"
+    assert np.array_equal(c2.cpu().numpy(), counts)
