@@ -16,7 +16,10 @@
 #include <cstddef>
 #include <cstdint>
 #include <mutex>
+#include <stdexcept>
+#include <string>
 #include <sys/types.h>
+#include <vector>
 
 #include "../lora_phy_cuda.h"
 
@@ -314,4 +317,104 @@ inline ssize_t lora_decode(const uint16_t* symbols, std::size_t symbol_count, ui
                                            symbol_count / 2 ? symbol_count / 2 : 1, nullptr);
 }
 
+// ---- README facade (README.md:40-59 of the reference): LoRaParams / LoRaPHY ----------------------------------
+// The reference's README advertises this class but its sources never define it; here it is real, over the
+// whole-modem pipelines of the C ABI: modulate = upstream coding chain (CRC, explicit header, FEC at `cr`,
+// whitening, interleaver, Gray: external/LoRa-SDR/LoRaEncoder.cpp:161-233) + lora_modulate (LoRaMod.cpp:8-43);
+// demodulate = dechirp + lora_demodulate (LoRaDemod.cpp:50-197) + decode chain (LoRaDecoder.cpp:196-397).
+// The *_batch members are the many-packet entry points (equal-length payloads / packets, row-major).
+struct LoRaParams {
+    unsigned sf = 7;
+    unsigned bw = 125000;
+    unsigned cr = 1;                 // coding rate 4/(4+cr), 1..4 (0 = uncoded)
+    bool explicit_header = true;
+    bool crc_enabled = true;
+    unsigned osr = 1;
+    uint8_t sync_word = 0x12;
+    unsigned implicit_length = 0;    // payload bytes when explicit_header is false
+};
+
+class LoRaPHY {
+public:
+    explicit LoRaPHY(const LoRaParams& p) : p_(p)
+    {
+        int rc = 0;
+        ctx_ = detail::shared_ctx(&rc);
+        if (!ctx_) throw std::runtime_error("lora_phy_cuda_create failed (" + std::to_string(rc) + "): no sm_100 device");
+        cfg_ = lora_phy_cuda_cfg{};
+        cfg_.sf = p.sf; cfg_.bw_hz = p.bw; cfg_.osr = p.osr ? p.osr : 1u; cfg_.sync_word = p.sync_word; cfg_.amplitude = 1.0f;
+        cc_ = lora_phy_cuda_chain_cfg{};
+        cc_.sf = p.sf; cc_.cr = p.cr; cc_.explicit_header = p.explicit_header; cc_.crc = p.crc_enabled; cc_.whitening = 1;
+        cc_.crc_check = 1; cc_.data_length = p.implicit_length;
+        if (lora_phy_cuda_chain_symbols(&cc_, 1) < 0 || (p.bw != 125000 && p.bw != 250000 && p.bw != 500000))
+            throw std::invalid_argument("LoRaParams: sf 7..12, bw 125/250/500 kHz, cr 0..4");
+    }
+
+    std::size_t samples_for(std::size_t payload_len) const
+    {
+        return (static_cast<std::size_t>(lora_phy_cuda_chain_symbols(&cc_, payload_len)) + 2) * (std::size_t(1) << p_.sf) * cfg_.osr;
+    }
+
+    std::vector<std::complex<float>> modulate(const std::vector<uint8_t>& payload) { return modulate_batch(payload, 1); }
+
+    // n_packets payloads of payload.size() / n_packets bytes each -> n_packets * samples_for(len) samples
+    std::vector<std::complex<float>> modulate_batch(const std::vector<uint8_t>& payload, std::size_t n_packets)
+    {
+        if (!n_packets || payload.size() % n_packets) throw std::invalid_argument("payload size not a multiple of n_packets");
+        const std::size_t len = payload.size() / n_packets, spp = samples_for(len);
+        std::vector<std::complex<float>> iq(n_packets * spp);
+        const long r = lora_phy_cuda_tx_batch_host(ctx_, &cfg_, &cc_, payload.data(), len, len, n_packets, iq.data(), spp);
+        if (r < 0) throw std::runtime_error(std::string("modulate: ") + lora_phy_cuda_last_error(ctx_));
+        return iq;
+    }
+
+    // One packet of whole symbols -> payload bytes; empty when the decoder dropped it (bad header / CRC).
+    std::vector<uint8_t> demodulate(const std::vector<std::complex<float>>& iq)
+    {
+        auto rows = demodulate_batch(iq, 1);
+        return rows.empty() ? std::vector<uint8_t>{} : rows[0];
+    }
+
+    std::vector<std::vector<uint8_t>> demodulate_batch(const std::vector<std::complex<float>>& iq, std::size_t n_packets)
+    {
+        if (!n_packets || iq.size() % n_packets) throw std::invalid_argument("sample count not a multiple of n_packets");
+        const std::size_t spp = iq.size() / n_packets;
+        std::vector<uint8_t> pay(n_packets * 260);
+        len_.assign(n_packets, 0); flags_.assign(n_packets, 0); sync_.assign(n_packets, 0);
+        cfo_.assign(n_packets, 0.0f); to_.assign(n_packets, 0.0f);
+        const int rc = lora_phy_cuda_rx_batch_host(ctx_, &cfg_, &cc_, iq.data(), spp, spp, n_packets, pay.data(), 260,
+                                                   len_.data(), flags_.data(), sync_.data(), cfo_.data(), to_.data());
+        if (rc < 0) throw std::runtime_error(std::string("demodulate: ") + lora_phy_cuda_last_error(ctx_));
+        std::vector<std::vector<uint8_t>> out(n_packets);
+        for (std::size_t p = 0; p < n_packets; ++p)
+            if (len_[p] > 0) out[p].assign(pay.begin() + p * 260, pay.begin() + p * 260 + len_[p]);
+        return out;
+    }
+
+    // results of the last demodulate call, per packet
+    bool crc_ok(std::size_t p = 0) const { return p < flags_.size() && (flags_[p] & 0x0c) == 0x0c; }
+    bool dropped(std::size_t p = 0) const { return p < len_.size() && len_[p] < 0; }
+    uint8_t sync_word(std::size_t p = 0) const { return p < sync_.size() ? sync_[p] : 0; }
+    lora_metrics metrics(std::size_t p = 0) const
+    {
+        lora_metrics m{};
+        if (p < cfo_.size()) { m.cfo = cfo_[p]; m.time_offset = to_[p]; m.crc_ok = crc_ok(p); }
+        return m;
+    }
+    const LoRaParams& params() const { return p_; }
+
+private:
+    LoRaParams p_;
+    lora_phy_cuda_ctx* ctx_ = nullptr;
+    lora_phy_cuda_cfg cfg_{};
+    lora_phy_cuda_chain_cfg cc_{};
+    std::vector<int32_t> len_;
+    std::vector<uint8_t> flags_, sync_;
+    std::vector<float> cfo_, to_;
+};
+
 } // namespace lora_phy
+
+// The README uses the facade unqualified.
+using lora_phy::LoRaParams;
+using lora_phy::LoRaPHY;

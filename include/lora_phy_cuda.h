@@ -246,6 +246,29 @@ int lora_phy_cuda_decode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda
                                      const int32_t* d_symbol_counts, size_t n_symbols, size_t n_packets,
                                      uint8_t* d_payload, size_t payload_stride, int32_t* d_len, uint8_t* d_flags);
 
+/* ---- whole-modem pipelines (the README's LoRaPHY::modulate / LoRaPHY::demodulate, batched) ------ */
+/* tx: payload bytes -> coding chain (cc) -> lora_modulate (cfg: sf, bw, osr, amplitude, sync_word), i.e.
+ * encode_chain_batch + modulate_batch without leaving the device.  Returns samples per packet
+ * (= (lora_phy_cuda_chain_symbols(cc, payload_len) + 2) * N * osr) or a negative errno.
+ * rx: raw IQ -> caller-side dechirp + lora_demodulate (the receive flow of tests/e2e_chain_test.cpp:83-101;
+ * the reference's high-level demodulate() does not round-trip its own modulator) -> decode
+ * chain.  The device variant dechirps d_iq IN PLACE.  d_len / d_flags as in decode_chain_batch; d_flags,
+ * d_sync, d_cfo, d_time_offset may be NULL.                                                              */
+long lora_phy_cuda_tx_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                            const uint8_t* d_payload, size_t payload_stride, size_t payload_len, size_t n_packets,
+                            void* d_iq, size_t packet_stride);
+int lora_phy_cuda_rx_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                           void* d_iq, size_t packet_stride, size_t samples_per_packet, size_t n_packets,
+                           uint8_t* d_payload, size_t payload_stride, int32_t* d_len, uint8_t* d_flags,
+                           uint8_t* d_sync, float* d_cfo, float* d_time_offset);
+long lora_phy_cuda_tx_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                                 const uint8_t* h_payload, size_t payload_stride, size_t payload_len, size_t n_packets,
+                                 void* h_iq, size_t packet_stride);
+int lora_phy_cuda_rx_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                                const void* h_iq, size_t packet_stride, size_t samples_per_packet, size_t n_packets,
+                                uint8_t* h_payload, size_t payload_stride, int32_t* h_len, uint8_t* h_flags,
+                                uint8_t* h_sync, float* h_cfo, float* h_time_offset);
+
 /* ---- AWGN Monte-Carlo driver (BASELINE.json configs[4]) ---------------------------------------- */
 /* For packets first_packet .. first_packet + n_packets - 1 of sweep cell cell_id, entirely on the device:
  * draw payload_len payload bytes (Philox4x32-10 keyed by seed; counter = byte group, packet, cell) ->

@@ -78,6 +78,11 @@ SIGNATURES = {
     "lora_phy_cuda_detect_batch": (C.c_int, [_vp, _u32, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_modulate_batch": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_modulate_batch_host": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
+    "lora_phy_cuda_tx_batch": (C.c_long, [_vp, _cfgp, C.POINTER(ChainCfg), _vp, _sz, _sz, _sz, _vp, _sz]),
+    "lora_phy_cuda_tx_batch_host": (C.c_long, [_vp, _cfgp, C.POINTER(ChainCfg), _vp, _sz, _sz, _sz, _vp, _sz]),
+    "lora_phy_cuda_rx_batch": (C.c_int, [_vp, _cfgp, C.POINTER(ChainCfg), _vp, _sz, _sz, _sz, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
+    "lora_phy_cuda_rx_batch_host": (C.c_int, [_vp, _cfgp, C.POINTER(ChainCfg), _vp, _sz, _sz, _sz, _vp, _sz, _vp, _vp, _vp, _vp,
+                                              _vp]),
     "lora_phy_cuda_awgn_roundtrip": (C.c_int, [_vp, C.POINTER(ChainCfg), C.c_float, C.c_uint64, C.c_uint32, C.c_uint64, _sz,
                                                _sz, _vp, _vp, _vp, _sz, _vp, _sz, _vp]),
     "lora_phy_cuda_frame_samples": (C.c_long, [C.c_uint32, C.c_uint32, _sz, C.c_uint32]),
@@ -325,6 +330,29 @@ class LoraPhyCuda:
         self._check(self.lib.lora_phy_cuda_decode_chain_batch(self.h, C.byref(cc), _ptr(symbols), symbols.stride(0),
                                                               _ptr(counts), S, P, _ptr(pay), payload_stride, _ptr(ln), _ptr(fl)))
         return pay, ln, fl
+
+    # ---- whole-modem pipelines ---------------------------------------------------------------
+    def tx_batch(self, cfg, cc, payload):
+        t = self.torch
+        P, L = payload.shape
+        n = (self.chain_symbols(cc, L) + 2) * (1 << cfg.sf) * cfg.osr
+        iq = t.empty((P, n), dtype=t.complex64, device=self.device)
+        self._check(self.lib.lora_phy_cuda_tx_batch(self.h, C.byref(cfg), C.byref(cc), _ptr(payload), payload.stride(0), L, P,
+                                                    _ptr(iq), iq.stride(0)))
+        return iq
+
+    def rx_batch(self, cfg, cc, iq, payload_stride=260):
+        """iq is dechirped in place.  -> dict(payload, len, flags, sync, cfo, time_offset)"""
+        t = self.torch
+        P, n = iq.shape
+        out = dict(payload=t.zeros((P, payload_stride), dtype=t.uint8, device=self.device),
+                   len=t.zeros(P, dtype=t.int32, device=self.device), flags=t.zeros(P, dtype=t.uint8, device=self.device),
+                   sync=t.zeros(P, dtype=t.uint8, device=self.device), cfo=t.zeros(P, dtype=t.float32, device=self.device),
+                   time_offset=t.zeros(P, dtype=t.float32, device=self.device))
+        self._check(self.lib.lora_phy_cuda_rx_batch(self.h, C.byref(cfg), C.byref(cc), _ptr(iq), iq.stride(0), n, P,
+                                                    _ptr(out["payload"]), payload_stride, _ptr(out["len"]), _ptr(out["flags"]),
+                                                    _ptr(out["sync"]), _ptr(out["cfo"]), _ptr(out["time_offset"])))
+        return out
 
     def awgn_roundtrip(self, cc, snr_db, n_packets, payload_len, seed=0xA76E, cell_id=0, first_packet=0, counts=None,
                        details=False, noise_std=None):

@@ -68,6 +68,7 @@ struct lora_phy_cuda_ctx {
     DevBuf state, phases, tmp, sched;                   // PacketState[], modulator phases, compensate scratch, fused-kernel counters
     uint32_t lookahead_bytes = 64u << 20;               // fused schedule look-ahead (LORA_PHY_LOOKAHEAD_MB)
     cf* sync_tab[13] = { nullptr };                      // stream detector tables per sf: up | down | fine (stream_sync.cu)
+    DevBuf txrx[3];                                      // tx/rx pipelines: symbols, status, host-variant results
     DevBuf mc[8];                                        // Monte-Carlo driver: payload, tx symbols, IQ, rx symbols, status+sync, decoded, len, flags
     std::mutex mc_mu;
     size_t mc_scratch_bytes = (size_t)4 << 30;           // IQ bytes per Monte-Carlo chunk (LORA_PHY_MC_SCRATCH_MB)
@@ -181,6 +182,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
     for (int sf = 0; sf <= 12; ++sf) if (ctx->sync_tab[sf]) cudaFree(ctx->sync_tab[sf]);
     ctx->lfsr.release();
     for (auto& b : ctx->mc) b.release();
+    for (auto& b : ctx->txrx) b.release();
     ctx->state.release(); ctx->phases.release(); ctx->tmp.release(); ctx->sched.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
     ctx->h_in.release(); ctx->h_out.release();
@@ -802,6 +804,125 @@ int lora_phy_cuda_decode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda
                                static_cast<const uint8_t*>(ctx->lfsr.p), d_payload, payload_stride, d_len, d_flags,
                                ctx->sm_count, ctx->stream));
     ++ctx->launches;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// README facade pipelines: LoRaPHY::modulate (payload -> IQ) and LoRaPHY::demodulate (IQ -> payload), batched.
+long lora_phy_cuda_tx_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                            const uint8_t* d_payload, size_t payload_stride, size_t payload_len, size_t n_packets,
+                            void* d_iq, size_t packet_stride)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if (!cc || cc->sf != cfg->sf) return fail(ctx, -EINVAL, "chain configuration missing or for another sf");
+    const long nsym = lora_phy_cuda_chain_symbols(cc, payload_len);
+    if (nsym < 0) return fail(ctx, -EINVAL, "bad chain configuration");
+    const size_t produced = ((size_t)nsym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
+    if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
+    if (!n_packets) return (long)produced;
+    {
+        Guard g(ctx->device);
+        CK(ctx->txrx[0].reserve(n_packets * (size_t)nsym * 2));
+    }
+    uint16_t* sym = static_cast<uint16_t*>(ctx->txrx[0].p);
+    long r = lora_phy_cuda_encode_chain_batch(ctx, cc, d_payload, payload_stride, payload_len, n_packets, sym, (size_t)nsym);
+    if (r < 0) return r;
+    return lora_phy_cuda_modulate_batch(ctx, cfg, sym, (size_t)nsym, (size_t)nsym, n_packets, d_iq, packet_stride);
+}
+
+int lora_phy_cuda_rx_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                           void* d_iq, size_t packet_stride, size_t spp, size_t n_packets, uint8_t* d_payload,
+                           size_t payload_stride, int32_t* d_len, uint8_t* d_flags, uint8_t* d_sync, float* d_cfo,
+                           float* d_time_offset)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if (!cc || cc->sf != cfg->sf) return fail(ctx, -EINVAL, "chain configuration missing or for another sf");
+    if ((!d_iq || !d_payload || !d_len) && n_packets) return fail(ctx, -EINVAL, "NULL buffer");
+    const size_t step = ((size_t)1 << cfg->sf) * cfg->osr, total = spp / step;
+    if (total < 2) return fail(ctx, -ERANGE, "fewer than two symbols per packet");
+    if (!n_packets) return 0;
+    const size_t nsym = total - 2;
+    {
+        Guard g(ctx->device);
+        CK(ctx->txrx[0].reserve(n_packets * (nsym + 1) * 2));
+        CK(ctx->txrx[1].reserve(n_packets * 4));
+    }
+    uint16_t* sym = static_cast<uint16_t*>(ctx->txrx[0].p);
+    int32_t* status = static_cast<int32_t*>(ctx->txrx[1].p);
+    lora_phy_cuda_cfg c = *cfg;
+    c.flags &= ~(uint32_t)LORA_PHY_CUDA_F_DECHIRP;                 // caller-side dechirp + lora_demodulate (e2e_chain_test.cpp:83-101)
+    rc = lora_phy_cuda_dechirp_batch(ctx, &c, d_iq, packet_stride, spp, n_packets);
+    if (rc < 0) return rc;
+    rc = lora_phy_cuda_demodulate_batch(ctx, &c, d_iq, packet_stride, nullptr, spp, n_packets, sym, nsym ? nsym : 1, d_sync,
+                                        d_cfo, d_time_offset, status);
+    if (rc < 0) return rc;
+    return lora_phy_cuda_decode_chain_batch(ctx, cc, sym, nsym ? nsym : 1, status, nsym, n_packets, d_payload, payload_stride,
+                                            d_len, d_flags);
+}
+
+long lora_phy_cuda_tx_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                                 const uint8_t* h_payload, size_t payload_stride, size_t payload_len, size_t n_packets,
+                                 void* h_iq, size_t packet_stride)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if ((!h_payload && payload_len && n_packets) || (!h_iq && n_packets)) return fail(ctx, -EINVAL, "NULL buffer");
+    if (!cc) return fail(ctx, -EINVAL, "chain configuration missing");
+    const long nsym = lora_phy_cuda_chain_symbols(cc, payload_len);
+    if (nsym < 0) return fail(ctx, -EINVAL, "bad chain configuration");
+    const size_t produced = ((size_t)nsym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
+    if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
+    if (!n_packets) return (long)produced;
+    Guard g(ctx->device);
+    const size_t in_bytes = (n_packets - 1) * payload_stride + payload_len, iq_bytes = n_packets * packet_stride * sizeof(cf);
+    CK(ctx->d_in.reserve(in_bytes + 16));
+    CK(ctx->d_out.reserve(iq_bytes));
+    if (in_bytes) CK(cudaMemcpyAsync(ctx->d_in.p, h_payload, in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    long r = lora_phy_cuda_tx_batch(ctx, cfg, cc, static_cast<const uint8_t*>(ctx->d_in.p), payload_stride, payload_len,
+                                    n_packets, ctx->d_out.p, packet_stride);
+    if (r < 0) return r;
+    CK(cudaMemcpy2DAsync(h_iq, packet_stride * sizeof(cf), ctx->d_out.p, packet_stride * sizeof(cf), produced * sizeof(cf),
+                         n_packets, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return r;
+}
+
+int lora_phy_cuda_rx_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const lora_phy_cuda_chain_cfg* cc,
+                                const void* h_iq, size_t packet_stride, size_t spp, size_t n_packets, uint8_t* h_payload,
+                                size_t payload_stride, int32_t* h_len, uint8_t* h_flags, uint8_t* h_sync, float* h_cfo,
+                                float* h_time_offset)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if ((!h_iq || !h_payload || !h_len) && n_packets) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
+    if (!n_packets) return 0;
+    Guard g(ctx->device);
+    const size_t iq_bytes = ((n_packets - 1) * packet_stride + spp) * sizeof(cf), pay_bytes = n_packets * payload_stride;
+    // results: payload | len (int32) | cfo | time_offset | flags | sync
+    const size_t o_len = (pay_bytes + 15) & ~(size_t)15, o_cfo = o_len + n_packets * 4, o_to = o_cfo + n_packets * 4,
+                 o_fl = o_to + n_packets * 4, o_sy = o_fl + n_packets, res_bytes = o_sy + n_packets;
+    CK(ctx->d_in.reserve(iq_bytes));
+    CK(ctx->txrx[2].reserve(res_bytes));
+    CK(cudaMemcpyAsync(ctx->d_in.p, h_iq, iq_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    uint8_t* res = static_cast<uint8_t*>(ctx->txrx[2].p);
+    CK(cudaMemsetAsync(res, 0, res_bytes, ctx->stream));
+    rc = lora_phy_cuda_rx_batch(ctx, cfg, cc, ctx->d_in.p, packet_stride, spp, n_packets, res, payload_stride,
+                                reinterpret_cast<int32_t*>(res + o_len), res + o_fl, res + o_sy,
+                                reinterpret_cast<float*>(res + o_cfo), reinterpret_cast<float*>(res + o_to));
+    if (rc < 0) return rc;
+    CK(ctx->h_out.reserve(res_bytes));
+    CK(cudaMemcpyAsync(ctx->h_out.p, res, res_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const uint8_t* h = static_cast<const uint8_t*>(ctx->h_out.p);
+    memcpy(h_payload, h, pay_bytes);
+    memcpy(h_len, h + o_len, n_packets * 4);
+    if (h_cfo) memcpy(h_cfo, h + o_cfo, n_packets * 4);
+    if (h_time_offset) memcpy(h_time_offset, h + o_to, n_packets * 4);
+    if (h_flags) memcpy(h_flags, h + o_fl, n_packets);
+    if (h_sync) memcpy(h_sync, h + o_sy, n_packets);
     return 0;
 }
 

@@ -113,6 +113,36 @@ int main(int argc, char** argv)
     // un-dechirped input); parity means reproducing that, which tests/test_gpu_parity.py checks against the oracle
     EXPECT(out[0] == 0x0c && out[1] == 0xa9 && out[2] == 0xa0 && out[3] == 0xa0 && out[4] == 0xa3);
 
+    // ---- README facade, verbatim (reference README.md:42-59): LoRaParams / LoRaPHY ----
+    {
+        LoRaParams params;
+        params.sf = 7; params.bw = 125000; params.cr = 1; params.explicit_header = true; params.crc_enabled = true;
+        LoRaPHY phy(params);
+        std::vector<uint8_t> payload = {0x48, 0x65, 0x6C, 0x6C, 0x6F};
+        auto iq_samples = phy.modulate(payload);
+        EXPECT(iq_samples.size() == (18 + 2) * 128);                     // CR4/5 explicit header CRC: 18 data symbols
+        auto decoded_payload = phy.demodulate(iq_samples);
+        EXPECT(decoded_payload == payload);
+        EXPECT(phy.crc_ok() && !phy.dropped() && phy.sync_word() == 0x12);
+        iq_samples[700] = -iq_samples[700];                              // a glitch the FEC / FFT gain absorbs
+        EXPECT(phy.demodulate(iq_samples) == payload);
+        for (std::size_t i = 5 * 128; i < 9 * 128; ++i) iq_samples[i] = 0;   // four symbols wiped: CRC / header must catch it
+        EXPECT(phy.demodulate(iq_samples) != payload);
+        // many-packet entry point: 6 packets x 9 bytes at SF9 CR4/8
+        LoRaParams p9; p9.sf = 9; p9.cr = 4;
+        LoRaPHY phy9(p9);
+        std::vector<uint8_t> batch(6 * 9);
+        for (std::size_t i = 0; i < batch.size(); ++i) batch[i] = (uint8_t)(i * 37 + 11);
+        auto iq9 = phy9.modulate_batch(batch, 6);
+        EXPECT(iq9.size() == 6 * phy9.samples_for(9));
+        auto rows = phy9.demodulate_batch(iq9, 6);
+        for (std::size_t p = 0; p < 6; ++p)
+            EXPECT(rows[p] == std::vector<uint8_t>(batch.begin() + 9 * p, batch.begin() + 9 * p + 9) && phy9.crc_ok(p));
+        bool threw = false;
+        try { LoRaParams bad; bad.sf = 13; LoRaPHY x(bad); } catch (const std::invalid_argument&) { threw = true; }
+        EXPECT(threw);
+    }
+
     std::printf(fails ? "phy_dropin_test gpu: %d failure(s)\n" : "phy_dropin_test gpu: ok\n", fails);
     return fails ? 1 : 0;
 }

@@ -653,3 +653,39 @@ def test_awgn_roundtrip_spot_check(phy, lp, oracle, sf, cr, snr_db):
     finally:
         os.environ["LORA_PHY_MC_SCRATCH_MB"] = "4096"
     assert np.array_equal(c2.cpu().numpy(), counts)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf,cr,bw", [(7, 1, 125000), (8, 3, 250000), (10, 4, 125000), (12, 2, 500000)])
+def test_whole_modem_pipelines(phy, lp, oracle, sf, cr, bw):
+    """lora_phy_cuda_tx_batch / rx_batch (the README's LoRaPHY::modulate / demodulate, batched) == the oracle's
+    encode chain + lora_modulate and dechirp + lora_demodulate + decode chain, stage outputs bit for bit."""
+    rng = np.random.default_rng(sf + cr)
+    N = 1 << sf
+    P, L = 7, 10
+    pay = rng.integers(0, 256, (P, L), dtype=np.uint8)
+    cfg = lp.make_cfg(sf, bw_hz=bw, amplitude=0.8)
+    cc, oc = lp.make_chain_cfg(sf, cr=cr), oracle.chain_cfg(sf, cr=cr)
+    iq = phy.tx_batch(cfg, cc, to_dev(phy, pay))
+    phy.synchronize()
+    iq_h = iq.cpu().numpy()
+    down = oracle.gen_chirp(N, 1, N, 0.0, True, 1.0, 0.0, bw / 125000.0)[0]
+    noisy = iq_h + (0.3 * (rng.standard_normal(iq_h.shape) + 1j * rng.standard_normal(iq_h.shape))).astype(np.complex64)
+    noisy = noisy.astype(np.complex64)
+    noisy[P - 1, 3 * N: 9 * N] = 0                                   # a packet the decoder has to reject or flag
+    out = phy.rx_batch(cfg, cc, to_dev(phy, noisy))
+    phy.synchronize()
+    out = {k: v.cpu().numpy() for k, v in out.items()}
+    for p in range(P):
+        o_sym = oracle.encode_chain(oc, pay[p])
+        o_iq = oracle.lora_modulate(o_sym, sf, 1, bw, 0.8, 0x12)
+        assert np.array_equal(bits(iq_h[p].view(np.float32)), bits(o_iq.view(np.float32))), (sf, p)
+        d = (noisy[p].reshape(-1, N) * down[None, :]).astype(np.complex64).ravel()
+        r, o_rx, o_sync, o_cfo, o_to = oracle.lora_demodulate(d, sf)
+        ln, o_bytes, o_fl = oracle.decode_chain(oc, o_rx[:r], cap=260)
+        assert out["len"][p] == ln and out["flags"][p] == o_fl and out["sync"][p] == o_sync, (sf, p)
+        assert bits(np.float32(out["cfo"][p])) == bits(np.float32(o_cfo))
+        if ln > 0:
+            assert np.array_equal(out["payload"][p, :ln], o_bytes)
+        if p < P - 1 and bw == 125000:
+            assert ln == L and np.array_equal(o_bytes, pay[p])
