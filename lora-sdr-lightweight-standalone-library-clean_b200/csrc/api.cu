@@ -726,6 +726,7 @@ int lora_phy_cuda_detect_stream(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t sy
     a.up = tab; a.down = tab + N; a.fine = tab + 2 * N;
     a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
     a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
+    { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
     a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
     a.n_frames = d_n_frames; a.end_pos = d_end_pos;
     CK(lk::launch_stream_sync((int)sf, a, ctx->stream));

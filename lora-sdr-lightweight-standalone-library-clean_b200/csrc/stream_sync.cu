@@ -29,7 +29,7 @@ struct GroupCtl {            // written by the group's thread 0, read by the who
     uint32_t pos;
     int live, down, need2, ft;
     float fine_err;
-    int pad[2];
+    int ok, ft2;
 };
 
 template <int SF>
@@ -38,38 +38,100 @@ struct SyncSmem {
     static constexpr int G = CTA_THREADS / P::T;
     static constexpr size_t buf_bytes = 2 * (size_t)G * P::N * sizeof(cf);
     static constexpr size_t ft_bytes = (size_t)G * P::N * sizeof(int);
-    static constexpr size_t bytes = buf_bytes + ft_bytes + 8 * sizeof(Peak) + (size_t)G * sizeof(GroupCtl);
+    static constexpr size_t red_off = buf_bytes + ft_bytes;                       // 8 Peaks, then 8 doubles
+    static constexpr size_t ctl_off = red_off + 8 * sizeof(Peak) + 8 * sizeof(double);
+    static constexpr size_t bytes = ctl_off + (size_t)G * sizeof(GroupCtl);
 };
 
 struct DetectOut { int value; float snr, findex; };
 
+// one step of the fine-tune index recurrence (:160-163): int -= float * size_t, truncated, wrapped once
+__device__ __forceinline__ int ft_step(int idx, float d, int wrap)
+{
+    int r = (int)fx::fsub((float)idx, d);
+    if (r < 0) r += wrap;
+    else if (r >= wrap) r -= wrap;
+    return r;
+}
+
+// sum of the group's doubles (any order: the caller proves the order does not matter)
+template <int T>
+__device__ __forceinline__ double group_dsum(double x, double* redd)
+{
+    constexpr int W = T < 32 ? T : 32;
+#pragma unroll
+    for (int off = W / 2; off > 0; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
+    if (T > 32) {
+        const int warp = threadIdx.x >> 5;
+        if ((threadIdx.x & 31) == 0) redd[warp] = x;
+        __syncthreads();
+        const int w0 = (threadIdx.x / T) * (T / 32);
+        x = redd[w0];
+#pragma unroll
+        for (int k = 1; k < T / 32; ++k) x += redd[w0 + k];
+    }
+    return x;
+}
+
 // one window at `src`: dechirp + fine tune (:157-166), FFT, detect (LoRaDetector.hpp:39-74).
-// thread 0 of the group returns the detector outputs; *ft is advanced past the window.
+// thread 0 of the group returns the detector outputs and the fine-tune index advanced past the window.
+//
+// The two pieces of the reference that are serial by construction are run in parallel with a proof
+// obligation and fall back to the literal serial loop when the proof fails:
+//  * fine-tune index: inside one float binade the recurrence is a constant integer step k, so the
+//    sequence is idx0 - i*k (mod N*128).  Every thread checks ft_step(c_i) == c_{i+1} for its own
+//    samples; if all agree the arithmetic progression IS the recurrence (induction from idx0).
+//  * detector total: the ascending double sum differs from any other summation order by at most
+//    2(N-1)u * total.  If float(total - max) is the same at both ends of that interval (the map is
+//    monotone) the order cannot matter and the tree sum is used.
 template <int SF>
 __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const cf* __restrict__ src, bool live,
-                                                 const cf* __restrict__ chirp, int* ft, float fine_err, int tid,
-                                                 cf* buf0, cf* buf1, int& flip, int* ftidx, Peak* red)
+                                                 const cf* __restrict__ chirp, int idx0, int* ft_out, float fine_err,
+                                                 int tid, cf* buf0, cf* buf1, int& flip, int* ftidx, Peak* red,
+                                                 double* redd, volatile int* ok_flag)
 {
     using P = fx::Plan<SF>;
     constexpr int T = P::T, N = P::N;
-    const int wrap = N * FINE_STEPS;
-    if (tid == 0) {
-        int idx = *ft;
-        if (fine_err == 0.0f || !live) {
-            ftidx[0] = idx;                                  // constant index: lanes read entry 0 (flag below)
-        } else {
-            const float d = fx::fmul(fine_err, (float)FINE_STEPS);
-            for (int i = 0; i < N; ++i) {
-                ftidx[i] = idx;
-                idx = (int)fx::fsub((float)idx, d);          // int -= float * size_t, truncated (:160)
-                if (idx < 0) idx += wrap;
-                else if (idx >= wrap) idx -= wrap;
-            }
-            *ft = idx;
+    constexpr int wrap = N * FINE_STEPS;
+    const bool constant = fine_err == 0.0f;
+    const float d = fx::fmul(fine_err, (float)FINE_STEPS);
+    // k: the integer step of the first sample, before wrapping
+    const int k = idx0 - (int)fx::fsub((float)idx0, d);
+    bool mine_ok = !a.force_serial;
+    int ci[P::R];
+#pragma unroll
+    for (int c = 0; c < P::R; ++c) {
+        const int i = tid + T * c;
+        ci[c] = constant ? idx0 : (int)(((unsigned)idx0 - (unsigned)i * (unsigned)k) & (unsigned)(wrap - 1));
+        if (!constant && live && !a.force_serial) {
+            const int nxt = (int)(((unsigned)idx0 - (unsigned)(i + 1) * (unsigned)k) & (unsigned)(wrap - 1));
+            mine_ok = mine_ok && ft_step(ci[c], d, wrap) == nxt;
         }
     }
+    if (tid == 0) *ok_flag = 1;
     group_sync<T>();
-    const bool constant = fine_err == 0.0f;
+    if (!mine_ok) *ok_flag = 0;
+    group_sync<T>();
+    const bool progression = *ok_flag != 0;
+    int ft_end = constant ? idx0 : (int)(((unsigned)idx0 - (unsigned)N * (unsigned)k) & (unsigned)(wrap - 1));
+    // the barrier domain (warp or CTA) may hold several groups: enter the fallback together
+    const bool any_serial = T > 32 ? (__syncthreads_or(!progression) != 0) : (__any_sync(0xffffffffu, !progression) != 0);
+    if (any_serial) {                                        // literal recurrence on thread 0
+        if (!progression && tid == 0) {
+            int idx = idx0;
+            for (int i = 0; i < N; ++i) {
+                ftidx[i] = idx;
+                idx = ft_step(idx, d, wrap);
+            }
+            ft_end = idx;
+        }
+        group_sync<T>();
+        if (!progression) {
+#pragma unroll
+            for (int c = 0; c < P::R; ++c) ci[c] = ftidx[tid + T * c];
+        }
+    }
+    if (tid == 0 && live) *ft_out = ft_end;
     cf v[P::R];
 #pragma unroll
     for (int c = 0; c < P::R; ++c) {
@@ -77,12 +139,16 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
         cf x = fx::mk(0.0f, 0.0f);
         if (live) {
             x = fx::cmul(ldg_cf(src + i), ldg_cf(chirp + i));
-            x = fx::cmul(x, ldg_cf(a.fine + (constant ? ftidx[0] : ftidx[i])));
+            x = fx::cmul(x, ldg_cf(a.fine + ci[c]));
         }
         v[c] = x;
     }
     fft_group<SF, true>(v, tid, a.tw, a.ct, buf0, buf1, flip);
     const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+    double part = 0.0;
+#pragma unroll
+    for (int r = 0; r < P::R; ++r) part += (double)fx::cnorm(v[r]);
+    const double tree = group_dsum<T>(part, redd);
     cf* spec = flip ? buf1 : buf0;
     flip ^= 1;
 #pragma unroll
@@ -90,10 +156,14 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     group_sync<T>();
     DetectOut o; o.value = 0; o.snr = 0.0f; o.findex = 0.0f;
     if (tid == 0 && live) {
-        double total = 0.0;                                  // LoRaDetector.hpp:45-52, ascending
-        for (int i = 0; i < N; ++i)
-            total += (double)fx::fadd(fx::fmul(spec[i].x, spec[i].x), fx::fmul(spec[i].y, spec[i].y));
-        const float noise = __fsqrt_rn((float)(total - (double)pk.val));
+        const double eps = tree * (4.0 * (double)N * 0x1p-53);
+        float rest = (float)((tree - eps) - (double)pk.val);
+        if (a.force_serial || !(rest == (float)((tree + eps) - (double)pk.val))) {
+            double total = 0.0;                              // LoRaDetector.hpp:45-52, ascending
+            for (int i = 0; i < N; ++i) total += (double)fx::cnorm(spec[i]);
+            rest = (float)(total - (double)pk.val);
+        }
+        const float noise = __fsqrt_rn(rest);
         const float fundamental = __fsqrt_rn(pk.val);
         const cf l = spec[pk.idx > 0 ? pk.idx - 1 : N - 1];
         const cf r = spec[pk.idx < N - 1 ? pk.idx + 1 : 0];
@@ -121,8 +191,9 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
     cf* buf0 = base + (size_t)g * N;
     cf* buf1 = base + (size_t)G * N + (size_t)g * N;
     int* ftidx = reinterpret_cast<int*>(smem_raw + S::buf_bytes) + (size_t)g * N;
-    Peak* red = reinterpret_cast<Peak*>(smem_raw + S::buf_bytes + S::ft_bytes);
-    GroupCtl& ctl = reinterpret_cast<GroupCtl*>(smem_raw + S::buf_bytes + S::ft_bytes + 8 * sizeof(Peak))[g];
+    Peak* red = reinterpret_cast<Peak*>(smem_raw + S::red_off);
+    double* redd = reinterpret_cast<double*>(smem_raw + S::red_off + 8 * sizeof(Peak));
+    GroupCtl& ctl = reinterpret_cast<GroupCtl*>(smem_raw + S::ctl_off)[g];
     int flip = 0;
 
     const uint32_t sid = blockIdx.x * G + g;
@@ -151,7 +222,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
         const float ferr = ctl.fine_err;
         const cf* chirp = ctl.down ? a.down : a.up;
         int ft = ctl.ft;
-        DetectOut d = sync_window<SF>(a, iq + wpos, live, chirp, &ft, ferr, tid, buf0, buf1, flip, ftidx, red);
+        DetectOut d = sync_window<SF>(a, iq + wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, ftidx, red, redd,
+                                      &ctl.ok);
         bool squelched = false, syncd = false, match0 = false;
         if (tid == 0 && live) {
             fine_idx = ft;
@@ -159,16 +231,16 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
             if (state == ST_FRAMESYNC) {                                       // :179-185
                 syncd = !squelched && (prev_value + 4) / 8 == 0;
                 match0 = (unsigned)(d.value + 4) / 8 == (a.sync >> 4);
-                if (syncd && match0) ctl.need2 = 1;
+                if (syncd && match0) { ctl.need2 = 1; ctl.ft2 = ft; }
             }
         }
         __syncthreads();
         const bool need2 = ctl.need2 != 0;
         int value1 = 0;
         if (__syncthreads_or(need2)) {                                         // look ahead one window for sync word1 (:188-205)
-            int ft2 = fine_idx;                                                // (a copy: _fineTuneIndex itself is not advanced)
-            if (tid != 0) ft2 = 0;
-            DetectOut d1 = sync_window<SF>(a, iq + wpos + N, live && need2, chirp, &ft2, ferr, tid, buf0, buf1, flip, ftidx, red);
+            int ft2 = 0;                                                       // (a copy: _fineTuneIndex itself is not advanced)
+            DetectOut d1 = sync_window<SF>(a, iq + wpos + N, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
+                                           ftidx, red, redd, &ctl.ok);
             if (tid == 0 && need2) { value1 = d1.value; d.findex = d1.findex; }
         }
         if (tid == 0 && live) {

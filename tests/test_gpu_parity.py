@@ -539,6 +539,13 @@ def test_stream_detector_parity(phy, lp, oracle, sf):
     check_stream(phy, oracle, rows[:3], sf, thresh=-30.0, mtu=8, max_frames=2)
     # a different sync word: nothing matches 0x34 in these streams, alignment logic still replays
     check_stream(phy, oracle, rows[:2], sf, thresh=-8.0, mtu=16, max_frames=4, sync=0x34)
+    # the literal serial loops (fallback of the verified-parallel fine-tune index and detector total)
+    import os
+    os.environ["LORA_PHY_STREAM_SERIAL"] = "1"
+    try:
+        check_stream(phy, oracle, rows[:4], sf, thresh=-8.0, mtu=32, max_frames=6)
+    finally:
+        os.environ["LORA_PHY_STREAM_SERIAL"] = "0"
 
 
 @pytest.mark.gpu
