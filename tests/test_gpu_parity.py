@@ -696,3 +696,115 @@ def test_whole_modem_pipelines(phy, lp, oracle, sf, cr, bw):
             assert np.array_equal(out["payload"][p, :ln], o_bytes)
         if p < P - 1 and bw == 125000:
             assert ln == L and np.array_equal(o_bytes, pay[p])
+
+
+@pytest.mark.gpu
+def test_compiled_reference_fixture(phy, lp):
+    """tests/golden/ref_outputs.npz holds outputs of the reference's own sources compiled unchanged
+    (tests/golden/make_golden.py): the CUDA path against the reference itself, no oracle in between."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_outputs.npz"))
+    for sf in (2, 5, 7, 8, 9, 12):
+        out = phy.detect_batch(sf, to_dev(phy, z[f"detect_sf{sf}_in"][None, :]))
+        phy.synchronize()
+        sc = z[f"detect_sf{sf}_scalars"]
+        assert np.array_equal(bits(out["spectrum"][0].cpu().numpy().view(np.float32)), bits(z[f"detect_sf{sf}_spec"].view(np.float32)))
+        assert int(out["index"][0]) == int(sc[0])
+        got = np.array([float(out["power"][0]), float(out["power_avg"][0]), float(out["findex"][0])], np.float32)
+        assert np.array_equal(bits(got), bits(sc[1:].astype(np.float32))), sf
+        for osr in (1, 2):
+            k = f"demod_sf{sf}_osr{osr}"
+            cfg = lp.make_cfg(sf, osr=osr)
+            mod = phy.modulate_batch(cfg, to_dev(phy, z[k + "_syms_in"][None, :]))
+            r = phy.demodulate_batch(cfg, to_dev(phy, z[k + "_in"][None, :]))
+            phy.synchronize()
+            assert np.array_equal(bits(mod[0].cpu().numpy().view(np.float32)), bits(z[k + "_mod"].view(np.float32))), k
+            n, sync = [int(v) for v in z[k + "_scalars"]]
+            assert int(r["status"][0]) == n and int(r["sync"][0]) == sync, k
+            assert np.array_equal(r["symbols"][0, :n].cpu().numpy(), z[k + "_out"]), k
+            m = np.array([float(r["cfo"][0]), float(r["time_offset"][0])], np.float32)
+            assert np.array_equal(bits(m), bits(z[k + "_metrics"])), k
+
+
+@pytest.mark.gpu
+def test_regenerated_golden_set(phy, lp):
+    """CUDA == tests/golden/regenerated.npz for the chain, modulation, frame, stream and awgn classes."""
+    import os
+    import torch
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "regenerated.npz"))
+    for i in range(int(z["n_chain"][0])):
+        sf, cr, expl, crc, ppm = [int(v) for v in z[f"chain_{i}_cfg"]]
+        pay, sym = z[f"chain_{i}_payload"], z[f"chain_{i}_symbols"]
+        cc = lp.make_chain_cfg(sf, cr=cr, explicit_header=expl, crc=crc, ppm=ppm, data_length=pay.size)
+        got = phy.encode_chain_batch(cc, to_dev(phy, pay[None, :]))
+        dec, ln, fl = phy.decode_chain_batch(cc, to_dev(phy, sym[None, :]))
+        phy.synchronize()
+        assert np.array_equal(got[0].cpu().numpy(), sym), i
+        # implicit header: upstream posts the CRC bytes too (LoRaDecoder.cpp:381-395), XORed to zero when they match
+        # and an explicit-header packet without CRC loses its last two bytes (:299 adds 3, :374 subtracts 5): upstream quirks
+        want_len = pay.size + (2 if (not expl and crc) else 0) - (2 if (expl and not crc) else 0)
+        n = min(want_len, pay.size)
+        assert int(ln[0]) == want_len and np.array_equal(dec[0, :n].cpu().numpy(), pay[:n]), i
+    for i in range(int(z["n_modulation"][0])):
+        sf, osr, bw, sync = [int(v) for v in z[f"modulation_{i}_cfg"]]
+        cfg = lp.make_cfg(sf, bw_hz=bw, osr=osr, sync_word=sync, amplitude=0.9)
+        iq = phy.modulate_batch(cfg, to_dev(phy, z[f"modulation_{i}_symbols"][None, :]))
+        phy.synchronize()
+        assert np.array_equal(bits(iq[0].cpu().numpy().view(np.float32)), bits(z[f"modulation_{i}_iq"].view(np.float32))), i
+    for sf in (7, 10):
+        cfg = lp.make_cfg(sf, amplitude=0.3)
+        iq = phy.modulate_frames_batch(cfg, to_dev(phy, z[f"frame_{sf}_symbols"][None, :]), padding=1)
+        x = z[f"stream_{sf}_iq"]
+        out = phy.detect_stream(sf, to_dev(phy, x[None, :]), thresh_db=-8.0, mtu=24, max_frames=4)
+        phy.synchronize()
+        assert np.array_equal(bits(iq[0].cpu().numpy().view(np.float32)), bits(z[f"frame_{sf}_iq"].view(np.float32))), sf
+        assert int(out["n_frames"][0]) == 2 and int(out["end_pos"][0]) == int(z[f"stream_{sf}_end"][0])
+        assert np.array_equal(out["frame_start"][0, :2].cpu().numpy().astype(np.uint32), z[f"stream_{sf}_start"])
+        assert np.array_equal(out["frame_err"][0, :2].cpu().numpy(), z[f"stream_{sf}_err"])
+        assert np.array_equal(out["frame_nsym"][0, :2].cpu().numpy(), z[f"stream_{sf}_nsym"])
+        assert np.array_equal(out["symbols"][0, :2].cpu().numpy(), z[f"stream_{sf}_symbols"])
+    for i in range(int(z["n_awgn"][0])):
+        sf, cr, cell, pkt, L = [int(v) for v in z[f"awgn_{i}_cfg"]]
+        cc = lp.make_chain_cfg(sf, cr=cr)
+        counts, det = phy.awgn_roundtrip(cc, 0.0, 1, L, cell_id=cell, first_packet=pkt, details=True,
+                                         noise_std=float(z[f"awgn_{i}_std"][0]))
+        phy.synchronize()
+        ln = int(z[f"awgn_{i}_length"][0])
+        assert np.array_equal(det["rx_symbols"][0].cpu().numpy(), z[f"awgn_{i}_rx_sym"]), i
+        assert int(det["rx_len"][0]) == ln, i
+        if ln > 0:
+            n = min(ln, L)
+            assert np.array_equal(det["rx_payload"][0, :n].cpu().numpy(), z[f"awgn_{i}_rx_payload"][:n]), i
+
+
+@pytest.mark.gpu
+def test_error_codes_of_the_wider_entry_points(phy, lp):
+    """Negative errno by return value, nothing written, for the chain / frame / stream / pipeline / Monte-Carlo entries."""
+    import errno
+    import torch
+
+    def code(fn):
+        with pytest.raises(lp.LoraPhyError) as e:
+            fn()
+        return e.value.code
+
+    sym = torch.zeros((2, 4), dtype=torch.uint16, device=phy.device)
+    pay = torch.zeros((2, 4), dtype=torch.uint8, device=phy.device)
+    iq = torch.zeros((2, 4096), dtype=torch.complex64, device=phy.device)
+    assert code(lambda: phy.modulate_frames_batch(lp.make_cfg(7, osr=3), sym)) == -errno.EINVAL      # osr not a power of two
+    assert code(lambda: phy.modulate_frames_batch(lp.make_cfg(7), sym, iq=torch.zeros((2, 100), dtype=torch.complex64, device=phy.device))) == -errno.ERANGE
+    assert code(lambda: phy.detect_stream(6, iq)) == -errno.EINVAL
+    assert code(lambda: phy.detect_stream(7, iq, mtu=0)) == -errno.EINVAL
+    assert code(lambda: phy.encode_chain_batch(lp.make_chain_cfg(13), pay)) == -errno.EINVAL
+    assert code(lambda: phy.encode_chain_batch(lp.make_chain_cfg(7, cr=5), pay)) == -errno.EINVAL
+    assert code(lambda: phy.tx_batch(lp.make_cfg(8), lp.make_chain_cfg(7), pay)) == -errno.EINVAL     # sf mismatch
+    assert code(lambda: phy.rx_batch(lp.make_cfg(7), lp.make_chain_cfg(7), iq[:, :128])) == -errno.ERANGE   # < 2 symbols
+    assert code(lambda: phy.awgn_roundtrip(lp.make_chain_cfg(7), 0.0, 4, 256)) == -errno.EINVAL       # payload > 255
+    assert code(lambda: phy.awgn_roundtrip(lp.make_chain_cfg(7), 0.0, 4, 8, noise_std=-1.0)) == -errno.EINVAL
+    assert code(lambda: phy.awgn_roundtrip(lp.make_chain_cfg(7), 0.0, 4, 8, noise_std=float("nan"))) == -errno.EINVAL
+    # zero-sized batches are fine and launch nothing
+    n0 = phy.launch_count()
+    counts, _ = phy.awgn_roundtrip(lp.make_chain_cfg(7), 0.0, 0, 8)
+    out = phy.detect_stream(7, iq[:0])
+    phy.synchronize()
+    assert phy.launch_count() == n0 and int(counts.sum()) == 0 and out["n_frames"].numel() == 0
