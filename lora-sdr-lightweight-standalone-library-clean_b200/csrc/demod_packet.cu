@@ -45,6 +45,14 @@ struct PacketCfg : StreamCfg<SF> {
     static constexpr size_t bytes = sh_off + sizeof(PktShared);
 };
 
+// max(m, |a|, |b|) that returns NaN when any input is NaN (sm_100 three-input max; the abs fold into the operands)
+__device__ __forceinline__ float max3_nan_abs(float m, float a, float b)
+{
+    float d;
+    asm("{\n\t.reg .f32 aa, bb;\n\tabs.f32 aa, %2;\n\tabs.f32 bb, %3;\n\tmax.NaN.f32 %0, %1, aa, bb;\n\t}" : "=f"(d) : "f"(m), "f"(a), "f"(b));
+    return d;
+}
+
 __device__ __forceinline__ float amp_of(float re, float im)      // LoRaDemod.cpp:63-66
 {
     const float r = fabsf(re), i = fabsf(im);
@@ -91,17 +99,29 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_packet_
         if (a.mode == MODE_LEGACY) {
             float m = 0.0f;
             if ((reinterpret_cast<uintptr_t>(pkt) & 15) == 0) {
+                // Fast scan: one NaN-propagating 3-input max per sample (|re|, |im| are operand modifiers).  The
+                // reference ignores a sample whose real part is NaN and takes |re| when only the imaginary part is
+                // (std::max / '>' semantics, LoRaDemod.cpp:63-66); a NaN anywhere poisons m here, and the CTA then
+                // rescans with the literal comparison chain below.
                 const float4* p4 = reinterpret_cast<const float4*>(pkt);
                 const uint32_t pairs = count >> 1;
-#pragma unroll 4
+#pragma unroll 8
                 for (uint32_t j = threadIdx.x; j < pairs; j += CTA_THREADS) {
                     const float4 q = __ldg(p4 + j);
-                    m = fmaxf(m, amp_of(q.x, q.y));
-                    m = fmaxf(m, amp_of(q.z, q.w));
+                    m = max3_nan_abs(m, q.x, q.y);
+                    m = max3_nan_abs(m, q.z, q.w);
                 }
                 if ((count & 1) && threadIdx.x == 0) {
                     const cf x = ldg_cf(pkt + count - 1);
-                    m = fmaxf(m, amp_of(x.x, x.y));
+                    m = max3_nan_abs(m, x.x, x.y);
+                }
+                if (__syncthreads_or(m != m)) {
+                    m = 0.0f;
+#pragma unroll 4
+                    for (uint32_t j = threadIdx.x; j < count; j += CTA_THREADS) {
+                        const cf x = ldg_cf(pkt + j);
+                        m = fmaxf(m, amp_of(x.x, x.y));
+                    }
                 }
             } else {
 #pragma unroll 4
