@@ -212,6 +212,17 @@ int lora_phy_cuda_detect_stream(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t sy
                                 int32_t* d_frame_nsym, int16_t* d_symbols, uint32_t* d_n_frames,
                                 uint32_t* d_end_pos);
 
+/* Mixed batch (BASELINE.json configs[3]): stream s runs at spreading factor h_sf[s] (HOST array, 7..12); rows of
+ * one SF are walked by one launch each, results land in the rows of the same output arrays.  Bandwidth does not
+ * enter the receiver's arithmetic at one sample per chip (it only names the sample rate); oversampled captures
+ * are decimated by the caller, as upstream's LoRaDemod expects.  Everything else as lora_phy_cuda_detect_stream. */
+int lora_phy_cuda_detect_streams_mixed(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, uint32_t sync_word, float thresh_db,
+                                       uint32_t mtu, const void* d_iq, size_t stream_stride,
+                                       const uint32_t* d_sample_counts, size_t n_samples, size_t n_streams,
+                                       size_t max_frames, uint32_t* d_frame_start, int32_t* d_frame_err,
+                                       int32_t* d_frame_nsym, int16_t* d_symbols, uint32_t* d_n_frames,
+                                       uint32_t* d_end_pos);
+
 /* ---- bit pipeline: K4 (full upstream coding chain) -------------------------------------------- */
 /* The chain the reference vendors under external/LoRa-SDR and its README's LoRaParams{cr, explicit_header,
  * crc_enabled} refer to (LoRaEncoder.cpp:161-233, LoRaDecoder.cpp:196-397): CRC-16, 3-byte explicit

@@ -728,9 +728,62 @@ int lora_phy_cuda_detect_stream(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t sy
     a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
     { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
     a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
-    a.n_frames = d_n_frames; a.end_pos = d_end_pos;
+    a.n_frames = d_n_frames; a.end_pos = d_end_pos; a.ids = nullptr;
     CK(lk::launch_stream_sync((int)sf, a, ctx->stream));
     ++ctx->launches;
+    return 0;
+}
+
+int lora_phy_cuda_detect_streams_mixed(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, uint32_t sync_word, float thresh_db,
+                                       uint32_t mtu, const void* d_iq, size_t stream_stride, const uint32_t* d_counts,
+                                       size_t n_samples, size_t n_streams, size_t max_frames, uint32_t* d_frame_start,
+                                       int32_t* d_frame_err, int32_t* d_frame_nsym, int16_t* d_symbols,
+                                       uint32_t* d_n_frames, uint32_t* d_end_pos)
+{
+    if (!ctx) return -EINVAL;
+    if (!h_sf && n_streams) return fail(ctx, -EINVAL, "h_sf is NULL");
+    if (!mtu || mtu > 32767) return fail(ctx, -EINVAL, "mtu out of range 1..32767");
+    if (n_samples > stream_stride && n_streams > 1) return fail(ctx, -EINVAL, "n_samples exceeds stream_stride");
+    if (n_samples > 0xf0000000ull || n_streams > 0xffffffffull || max_frames > 0xffffffffull) return fail(ctx, -EINVAL, "too large");
+    if (n_streams && (!d_iq || !d_n_frames || (max_frames && (!d_frame_start || !d_frame_err || !d_frame_nsym || !d_symbols))))
+        return fail(ctx, -EINVAL, "NULL buffer");
+    std::vector<uint32_t> ids[13];
+    for (size_t s = 0; s < n_streams; ++s) {
+        if (h_sf[s] < 7 || h_sf[s] > 12) return fail(ctx, -EINVAL, "per-stream sf out of range 7..12");
+        ids[h_sf[s]].push_back((uint32_t)s);
+    }
+    if (!n_streams) return 0;
+    Guard g(ctx->device);
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CK(ctx->tmp.reserve(n_streams * sizeof(uint32_t)));
+    uint32_t* d_ids = static_cast<uint32_t*>(ctx->tmp.p);
+    size_t off = 0;
+    for (uint32_t sf = 7; sf <= 12; ++sf) {                     // rows of one SF are contiguous in the id list
+        if (ids[sf].empty()) continue;
+        CK(cudaMemcpyAsync(d_ids + off, ids[sf].data(), ids[sf].size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        off += ids[sf].size();
+    }
+    CK(cudaStreamSynchronize(ctx->stream));                      // the host vectors go out of scope below
+    off = 0;
+    for (uint32_t sf = 7; sf <= 12; ++sf) {
+        if (ids[sf].empty()) continue;
+        cf* tab = nullptr;
+        int rc = sync_tables(ctx, sf, &tab);
+        if (rc) return rc;
+        const size_t N = (size_t)1 << sf;
+        lk::StreamSyncArgs a;
+        a.iq = static_cast<const cf*>(d_iq); a.stream_stride = stream_stride; a.counts = d_counts;
+        a.n_samples = (uint32_t)n_samples; a.n_streams = (uint32_t)ids[sf].size();
+        a.up = tab; a.down = tab + N; a.fine = tab + 2 * N;
+        a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
+        a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
+        { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
+        a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
+        a.n_frames = d_n_frames; a.end_pos = d_end_pos; a.ids = d_ids + off;
+        CK(lk::launch_stream_sync((int)sf, a, ctx->stream));
+        ++ctx->launches;
+        off += ids[sf].size();
+    }
     return 0;
 }
 

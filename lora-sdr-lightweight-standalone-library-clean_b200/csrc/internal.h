@@ -86,6 +86,7 @@ struct StreamSyncArgs {
     const cf* up; const cf* down; const cf* fine;          // LoRaDemod.cpp:96-117 tables (N, N, N*128 entries)
     const cf* tw; const cf* ct; float power_scale;
     uint32_t sync; float thresh; uint32_t mtu; uint32_t max_frames;
+    const uint32_t* ids;                                    // NULL, or [n_streams] rows this launch walks (mixed-SF batches)
     int force_serial;                                       // tests: take the literal serial loops (LORA_PHY_STREAM_SERIAL=1)
     uint32_t* frame_start; int32_t* frame_err; int32_t* frame_nsym; int16_t* symbols;   // [n_streams][max_frames]([mtu])
     uint32_t* n_frames; uint32_t* end_pos;                 // [n_streams]

@@ -196,8 +196,9 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
     GroupCtl& ctl = reinterpret_cast<GroupCtl*>(smem_raw + S::ctl_off)[g];
     int flip = 0;
 
-    const uint32_t sid = blockIdx.x * G + g;
-    const bool have = sid < a.n_streams;
+    const uint32_t slot = blockIdx.x * G + g;
+    const bool have = slot < a.n_streams;
+    const uint32_t sid = have ? (a.ids ? a.ids[slot] : slot) : 0;
     const cf* iq = a.iq + (size_t)(have ? sid : 0) * a.stream_stride;
     const uint32_t n = have ? (a.counts ? a.counts[sid] : a.n_samples) : 0;
 

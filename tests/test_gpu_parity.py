@@ -808,3 +808,33 @@ def test_error_codes_of_the_wider_entry_points(phy, lp):
     out = phy.detect_stream(7, iq[:0])
     phy.synchronize()
     assert phy.launch_count() == n0 and int(counts.sum()) == 0 and out["n_frames"].numel() == 0
+
+
+@pytest.mark.gpu
+def test_mixed_sf_stream_batch(phy, lp, oracle):
+    """BASELINE configs[3]: one batch of continuous streams at mixed spreading factors (ragged lengths) ==
+    the restated upstream receiver run per stream at that stream's SF."""
+    from test_stream_oracle import make_stream
+    rng = np.random.default_rng(2024)
+    sfs = [7, 12, 9, 7, 10, 8, 11, 9, 7, 12, 8]
+    rows = []
+    for sf in sfs:
+        N = 1 << sf
+        frames = [(rng.integers(0, N, int(rng.integers(3, 12))), float(rng.uniform(-0.3, 0.3))) for _ in range(2)]
+        rows.append(make_stream(oracle, rng, sf, frames, noise=0.1)[0])
+    n = max(r.size for r in rows)
+    buf = np.zeros((len(rows), n), np.complex64)
+    for s, r in enumerate(rows):
+        buf[s, :r.size] = r
+    cnt = np.array([r.size for r in rows], np.uint32)
+    out = phy.detect_stream(sfs, to_dev(phy, buf), thresh_db=-8.0, mtu=16, max_frames=4, sample_counts=to_dev(phy, cnt))
+    phy.synchronize()
+    out = {k: v.cpu().numpy() for k, v in out.items()}
+    for s, sf in enumerate(sfs):
+        nf, start, err, nsym, sym, end = oracle.stream_demod(buf[s, :cnt[s]], sf, thresh=-8.0, mtu=16, max_frames=4)
+        assert nf == 2 and out["n_frames"][s] == nf and out["end_pos"][s] == end, (s, sf)
+        assert np.array_equal(out["frame_start"][s, :nf].astype(np.uint32), start[:nf])
+        assert np.array_equal(out["frame_err"][s, :nf], err[:nf]) and np.array_equal(out["frame_nsym"][s, :nf], nsym[:nf])
+        assert np.array_equal(out["symbols"][s, :nf], sym[:nf])
+    with pytest.raises(lp.LoraPhyError):
+        phy.detect_stream([7, 6] + sfs[2:], to_dev(phy, buf))
