@@ -54,3 +54,52 @@ def test_reference_own_tests_pass_on_b200(name, tmp_path):
     os.symlink(os.path.join(HERE, "golden"), tmp_path / "vectors" / "golden")
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300, cwd=tmp_path)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+REFBIN = os.path.join(ROOT, "oracle", "_ref", "refbin")
+
+
+def _run(exe, args, cwd):
+    r = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300, cwd=cwd)
+    return r.returncode, r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf,bw,payload", [(7, 125000, "48656c6c6f"), (9, 250000, "00ff10ef5aa5c33c"), (12, 125000, "deadbeef"),
+                                           (8, 500000, "0102030405060708090a0b0c0d0e0f10")])
+def test_reference_cli_runners_on_b200(sf, bw, payload, tmp_path):
+    """The reference's own tx_runner / rx_runner (raw interleaved float32 IQ on disk, payload / CRC / CFO / time-offset
+    report), compiled unchanged against the drop-in header, against the same sources linked with the reference's own
+    library: identical IQ files and identical reports."""
+    for d in (REFBIN, REFTESTS):
+        if not os.path.exists(os.path.join(d, "tx_runner")):
+            pytest.skip("oracle/_ref runners not built (needs /root/reference at build time)")
+    args = [f"--payload={payload}", f"--sf={sf}", f"--bw={bw}"]
+    assert _run(os.path.join(REFBIN, "tx_runner"), args + ["--out=cpu.bin"], tmp_path)[0] == 0
+    assert _run(os.path.join(REFTESTS, "tx_runner"), args + ["--out=gpu.bin"], tmp_path)[0] == 0
+    cpu, gpu = (tmp_path / "cpu.bin").read_bytes(), (tmp_path / "gpu.bin").read_bytes()
+    assert len(cpu) == (len(payload) + 2) * (1 << sf) * 8 and cpu == gpu
+    rargs = ["--in=cpu.bin", f"--sf={sf}", f"--bw={bw}", "--report-offsets"]
+    want = _run(os.path.join(REFBIN, "rx_runner"), rargs, tmp_path)
+    got = _run(os.path.join(REFTESTS, "rx_runner"), rargs, tmp_path)
+    assert want[0] == 0 and got == want, (want, got)
+    assert _run(os.path.join(REFTESTS, "rx_runner"), ["--in=missing.bin"], tmp_path)[0] == 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("extra", [[], ["--osr=2"], ["--sf=9", "--bytes=12", "--window=hann"], ["--sf=8", "--bw=250000"]])
+def test_reference_vector_dump_on_b200(extra, tmp_path):
+    """lora_phy_vector_dump (per-stage CSV / bin dumps, runners/lora_phy_vector_dump.cpp:164-203): the directory the
+    drop-in build writes equals the reference build's, file by file."""
+    for d in (REFBIN, REFTESTS):
+        if not os.path.exists(os.path.join(d, "lora_phy_vector_dump")):
+            pytest.skip("oracle/_ref runners not built (needs /root/reference at build time)")
+    (tmp_path / "cpu").mkdir()
+    (tmp_path / "gpu").mkdir()
+    a = _run(os.path.join(REFBIN, "lora_phy_vector_dump"), ["--out=cpu", "--seed=11"] + extra, tmp_path)
+    b = _run(os.path.join(REFTESTS, "lora_phy_vector_dump"), ["--out=gpu", "--seed=11"] + extra, tmp_path)
+    assert a[0] == b[0] == 0, (a, b)
+    names = sorted(os.listdir(tmp_path / "cpu"))
+    assert names and names == sorted(os.listdir(tmp_path / "gpu"))
+    for n in names:
+        assert (tmp_path / "cpu" / n).read_bytes() == (tmp_path / "gpu" / n).read_bytes(), n
