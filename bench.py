@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- demodulated symbols/s of the batched LoRa PHY hot path on B200 (driver contract).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload sf7|sf12] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload sf7..sf12] [--impl reference]
 
 A "step" is one pass of the demodulator (lora_phy_cuda_demodulate_batch: one launch of
 demod_packet_kernel, one CTA per packet: scan -> estimator -> symbols) over one batch of synthetic, clean, pre-dechirped IQ already resident in HBM.
@@ -27,6 +27,11 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 WORKLOADS = {
     "sf7": dict(sf=7, payload=32, packets=1 << 20, name="SF7 BW125k, 1Mi packets x 32-byte payload, clean pre-dechirped IQ, demodulate-only"),
     "sf12": dict(sf=12, payload=64, packets=1 << 14, name="SF12 BW125k, 16Ki-packet resident chunk x 64-byte payload (of the 64Ki batch), clean pre-dechirped IQ, demodulate-only"),
+    # not BASELINE configs: the spreading factors in between, same 32-byte framing, ~70 GB resident each (north_star: SF7-SF12)
+    "sf8": dict(sf=8, payload=32, packets=1 << 19, name="SF8 BW125k, 512Ki packets x 32-byte payload, clean pre-dechirped IQ, demodulate-only"),
+    "sf9": dict(sf=9, payload=32, packets=1 << 18, name="SF9 BW125k, 256Ki packets x 32-byte payload, clean pre-dechirped IQ, demodulate-only"),
+    "sf10": dict(sf=10, payload=32, packets=1 << 17, name="SF10 BW125k, 128Ki packets x 32-byte payload, clean pre-dechirped IQ, demodulate-only"),
+    "sf11": dict(sf=11, payload=32, packets=1 << 16, name="SF11 BW125k, 64Ki packets x 32-byte payload, clean pre-dechirped IQ, demodulate-only"),
 }
 
 

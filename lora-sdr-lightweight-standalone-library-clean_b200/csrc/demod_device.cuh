@@ -81,7 +81,12 @@ __device__ __forceinline__ cf ldg_cf(const cf* p)
 template <int T>
 __device__ __forceinline__ void group_sync()
 {
-    if (T <= 32) __syncwarp(); else __syncthreads();
+    // a group's windows, exchange slots and reduction cells are its own: only its T threads meet.
+    // Sub-warp groups share a warp barrier; a group of several warps gets its own named barrier
+    // (ids 1..CTA_THREADS/T; id 0 stays __syncthreads), so the groups of a CTA do not wait on each other.
+    if (T <= 32) __syncwarp();
+    else if (T >= CTA_THREADS) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" :: "r"(1 + (int)threadIdx.x / T), "n"(T) : "memory");
 }
 
 // ---- per-sample chain + load into pass-0 register order ---------------------------------------
@@ -181,7 +186,7 @@ __device__ __forceinline__ Peak group_peak(Peak pk, Peak* red)
     if (T > 32) {
         const int warp = threadIdx.x >> 5;
         if ((threadIdx.x & 31) == 0) red[warp] = pk;
-        __syncthreads();
+        group_sync<T>();
         const int w0 = (threadIdx.x / T) * (T / 32);
         pk = red[w0];
 #pragma unroll
@@ -199,7 +204,7 @@ __device__ __forceinline__ float group_max(float m, float* redf)
     if (T > 32) {
         const int warp = threadIdx.x >> 5;
         if ((threadIdx.x & 31) == 0) redf[warp] = m;
-        __syncthreads();
+        group_sync<T>();
         const int w0 = (threadIdx.x / T) * (T / 32);
         m = redf[w0];
 #pragma unroll

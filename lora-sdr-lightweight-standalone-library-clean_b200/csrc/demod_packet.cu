@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_packet_
                     else a.symbols[(size_t)pid * a.symbol_stride + (have_sync ? s - 2 : s)] = (uint16_t)pk.idx;
                 }
                 ptx::fence_proxy_async();     // our generic-proxy stores to the slot precede the next bulk copy into it
-                domain_sync<SF>();
+                group_sync<T>();              // the slot is this group's own: groups stay coupled only through the stage mbarrier
                 u = u_next;
                 stage ^= 1;
             }

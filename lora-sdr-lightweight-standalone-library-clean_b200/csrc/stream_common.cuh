@@ -50,13 +50,14 @@ __device__ __forceinline__ void fft_inplace(cf (&v)[fx::Plan<SF>::R], int tid, c
     P::template pass0<FULL>(v, tw);
 #pragma unroll
     for (int p = 1; p < P::NP; ++p) {
-        domain_sync<SF>();            // raw samples (p == 1) / previous exchange (p > 1) fully consumed
+        group_sync<P::T>();           // raw samples (p == 1) / previous exchange (p > 1) fully consumed; the slot is
+                                      // the window's own, so only its thread group meets (named barrier per group)
 #pragma unroll
         for (int r = 0; r < P::R; ++r) {
             const int o = (p == 1) ? P::pos_after_pass0(tid, r) : P::pos_in_pass(p - 1, tid, r);
             ex[P::phys(o)] = v[r];
         }
-        domain_sync<SF>();
+        group_sync<P::T>();
 #pragma unroll
         for (int r = 0; r < P::R; ++r) v[r] = ex[P::phys(P::pos_in_pass(p, tid, r))];
         P::pass(p, v, tid, ct);

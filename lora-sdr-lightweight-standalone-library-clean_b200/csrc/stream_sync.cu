@@ -64,7 +64,7 @@ __device__ __forceinline__ double group_dsum(double x, double* redd)
     if (T > 32) {
         const int warp = threadIdx.x >> 5;
         if ((threadIdx.x & 31) == 0) redd[warp] = x;
-        __syncthreads();
+        group_sync<T>();
         const int w0 = (threadIdx.x / T) * (T / 32);
         x = redd[w0];
 #pragma unroll
