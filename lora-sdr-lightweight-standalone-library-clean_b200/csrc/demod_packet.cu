@@ -558,8 +558,10 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
                 // an inactive window (past the packet's last symbol) runs the same code on whatever its slot
                 // holds: the result is discarded, and no register zeroing / branch sits in the hot path
                 float mw = 0.0f;
-                if (!known) chain_window<SF, EXTRA, true>(v, raw, tid, scale, rate, start, slow, a.down, a.window, &mw);
-                else chain_window<SF, EXTRA, false>(v, raw, tid, scale, rate, start, slow, a.down, a.window);
+                // one copy of the chain in the loop (the running max costs one FMNMX3 per sample and is simply unused when
+                // the max is already known): a second, untracked copy made the loop body 10 KB longer, and the SM
+                // instruction cache -- 24 warps walk this loop out of phase -- is what the issue rate is short of
+                chain_window<SF, EXTRA, true>(v, raw, tid, scale, rate, start, slow, a.down, a.window, &mw);
                 if (active) m = fmaxf(m, mw);
                 fft_inplace<SF, false>(v, tid, a.tw, a.ct, win);
                 const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
