@@ -213,7 +213,13 @@ struct Plan {
     // that 64-bit stores/loads of all passes are bank-conflict free.
     FX_MHD static int phys(int o)
     {
-        if constexpr (SF >= 8) return o ^ ((o >> (SF - 4)) & 15);
+        // SF10: the pass-1 exchange varies position bits {0,1} and {6,7} across a half-warp, and the single fold left
+        // it 4-way conflicted (3.8 G conflict cycles per cfg-sized step); a second field makes every exchange
+        // conflict-free (exhaustive search over two-field XOR swizzles: tools/fft_swizzle_search.py).  SF9 / SF11 have
+        // conflict-free two-field swizzles too, but their 2-way conflicts cost less than the extra address
+        // arithmetic in these issue-bound kernels (measured: SF9 33.7 -> 36.8 ms with it), so they keep one field.
+        if constexpr (SF == 10) return o ^ ((o >> 4) & 15) ^ ((o >> 6) & 15);
+        else if constexpr (SF >= 8) return o ^ ((o >> (SF - 4)) & 15);
         else if constexpr (SF == 7) return o ^ ((o >> 4) & 7);
         else return o;
     }
