@@ -16,7 +16,11 @@
  *     reference (phy.hpp:100-141): -EINVAL bad argument, -ERANGE capacity / <2 symbols /
  *     missing scratch, -ENOMEM missing buffer, plus -EIO for a CUDA failure
  *     (text via lora_phy_cuda_last_error);
- *   - there is NO CPU fallback: without a CUDA device create() fails with -ENODEV.
+ *   - there is NO CPU fallback: without a CUDA device create() fails with -ENODEV;
+ *   - threading: like the reference (one workspace per thread, phy.hpp:74-78) a context serves ONE caller at
+ *     a time -- it owns the staging buffers, scratch and stream its calls use.  Use one context per host
+ *     thread (contexts on the same device are independent); device work of one context is ordered on its
+ *     stream, and the device-pointer entry points return without waiting for it.
  */
 #ifndef LORA_PHY_CUDA_H
 #define LORA_PHY_CUDA_H
