@@ -214,7 +214,8 @@ def run_ours(args, wl):
     sym_kernel_ms = sum(a.elapsed_time(b) for a, b in evs) / args.steps
 
     # ---- end-to-end through the host-buffer C-ABI call (pinned host IQ in, host symbols out) ----
-    Pe = min(P, args.e2e_packets)
+    # host staging is pinned memory on every rank: bound it to ~2.2 GB of IQ per rank whatever the packet size
+    Pe = max(1, min(P, args.e2e_packets, int(2.3e9 // (spp * 8))))
     h_iq = torch.empty((Pe, spp), dtype=torch.complex64).pin_memory()
     h_iq.copy_(iq[:Pe])
     h_iq_np = h_iq.numpy()
