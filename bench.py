@@ -249,7 +249,7 @@ def run_ours(args, wl):
         sym_bytes = P * (nsym - 2) * b_sym              # symbols kernel: data symbols of every packet, once
     else:
         kname = ("demod_fused_kernel<SF%d>" if args.fused else
-                 "demod_warp_kernel<SF%d>" if sf <= 9 else "demod_packet_kernel<SF%d>") % sf   # demod_packet.cu: warp per packet SF7-9
+                 "demod_warp_kernel<SF%d>" if sf <= 11 else "demod_packet_kernel<SF%d>") % sf   # demod_packet.cu: pipeline per packet SF7-11
         sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")

@@ -209,7 +209,7 @@ __device__ __forceinline__ float group_max(float m, float* redf)
         m = redf[w0];
 #pragma unroll
         for (int k = 1; k < T / 32; ++k) m = fmaxf(m, redf[w0 + k]);
-        __syncthreads();
+        group_sync<T>();             // the group's own redf cells may be rewritten
     }
     return m;
 }

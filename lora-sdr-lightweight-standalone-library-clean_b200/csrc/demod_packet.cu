@@ -23,6 +23,7 @@
 // byte once; packets too long for that (SF12: 4.3 MB each) read HBM twice, which the issue-bound
 // phase C still hides.
 #include "stream_common.cuh"
+#include <cstdlib>
 #include "internal.h"
 
 namespace lk {
@@ -306,7 +307,8 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_packet_
 }
 
 // ---------------------------------------------------------------------------------------------
-// SF 7..9: one WARP per packet, single pass, speculative scale.
+// SF 7..11: one PIPELINE per packet (a warp for SF7-9, the window's 2 / 4 warps for SF10 / 11), single pass,
+// speculative scale.
 //
 // A window needs T = N/16 <= 32 threads, so a warp is a complete pipeline (demod_stream.cu) and can
 // own a packet without any CTA-level barrier.  The reference's first walk (max-abs, LoRaDemod.cpp
@@ -320,15 +322,46 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_packet_
 //            phase -> cfo, time_offset, rate, t_off (LoRaDemod.cpp:80-136 / phy.cpp:93-147)
 //   C units  every symbol of the packet, sync symbols included (LoRaDemod.cpp:142-176)
 // ---------------------------------------------------------------------------------------------
-struct WarpShared { EstSym est[2]; int sw[2]; };
+struct WarpShared { EstSym est[2]; int sw[2]; float bc_rate; int bc_toff; };
 
+// A pipeline (the threads that own one packet at a time) is a warp for SF7-9 (T <= 32: GD = 32/T windows per
+// step) and the T = 64 / 128 threads of one window for SF10 / 11 (GD = 1, 4 / 2 pipelines per CTA, each with its
+// own named barrier, ring and mbarriers), so packets never wait on each other at CTA level.
 template <int SF>
-struct WarpCfg : StreamCfg<SF> {
-    using B = StreamCfg<SF>;
-    static_assert(B::T <= 32, "warp-owned packets need a window per warp");
-    static constexpr size_t ws_off = (B::bytes + 15) & ~(size_t)15;
-    static constexpr size_t bytes = ws_off + (size_t)B::DOMS * sizeof(WarpShared);
+struct WarpCfg {
+    using P = fx::Plan<SF>;
+    static constexpr int T = P::T, N = P::N;
+    static constexpr int DOM_THREADS = T <= 32 ? 32 : T;
+    static constexpr int DOMS = CTA_THREADS / DOM_THREADS;
+    static constexpr int GD = DOM_THREADS / T;
+    static constexpr int PITCH = N + 8;
+    static constexpr int SLOT = GD * PITCH;
+    static constexpr int STAGES = 2;
+    static constexpr size_t slot_bytes = (size_t)DOMS * STAGES * SLOT * sizeof(cf);
+    static constexpr size_t desc_bytes = (size_t)DOMS * STAGES * GD * sizeof(WinDesc);
+    static constexpr size_t bar_bytes = (size_t)DOMS * STAGES * sizeof(uint64_t);
+    static constexpr size_t red_bytes = 8 * sizeof(Peak) + 8 * sizeof(float);
+    static constexpr size_t ws_off = (slot_bytes + desc_bytes + bar_bytes + red_bytes + 15) & ~(size_t)15;
+    static constexpr size_t bytes = ws_off + (size_t)DOMS * sizeof(WarpShared);
 };
+
+// ---- pipeline-wide primitives: warp intrinsics for DT == 32, the pipeline's named barrier otherwise ----------
+template <int DT>
+__device__ __forceinline__ void pipe_sync()
+{
+    if (DT <= 32) pipe_sync<DT>(); else group_sync<DT>();
+}
+
+template <int DT>
+__device__ __forceinline__ bool pipe_any(bool p)
+{
+    if (DT <= 32) return __any_sync(0xffffffffu, p) != 0;
+    if (DT >= CTA_THREADS) return __syncthreads_or(p) != 0;
+    int r;
+    asm volatile("{\n\t.reg .pred q, r;\n\tsetp.ne.b32 q, %1, 0;\n\tbarrier.cta.red.or.pred r, %2, %3, q;\n\tselp.b32 %0, 1, 0, r;\n\t}"
+                 : "=r"(r) : "r"((int)p), "r"(1 + (int)threadIdx.x / DT), "n"(DT) : "memory");
+    return r != 0;
+}
 
 __device__ __forceinline__ float warp_max(float m)
 {
@@ -337,8 +370,16 @@ __device__ __forceinline__ float warp_max(float m)
     return m;
 }
 
-// max over [0, count) of max(|re|,|im|) with one warp: 128-bit loads, eight in flight per lane
-__device__ __forceinline__ float warp_scan_max(const cf* __restrict__ pkt, uint32_t count, int lane)
+template <int DT>
+__device__ __forceinline__ float pipe_max(float m, float* redf)
+{
+    if (DT <= 32) return warp_max(m);
+    return group_max<DT>(m, redf);
+}
+
+// max over [0, count) of max(|re|,|im|) with one pipeline: 128-bit loads, eight in flight per thread
+template <int DT>
+__device__ __forceinline__ float pipe_scan_max(const cf* __restrict__ pkt, uint32_t count, int lane, float* redf)
 {
     float m = 0.0f;
     uint32_t head = 0;
@@ -349,13 +390,13 @@ __device__ __forceinline__ float warp_scan_max(const cf* __restrict__ pkt, uint3
     const float4* p4 = reinterpret_cast<const float4*>(pkt + head);
     const uint32_t pairs = (count - head) >> 1;
 #pragma unroll 8
-    for (uint32_t j = lane; j < pairs; j += 32) {
+    for (uint32_t j = lane; j < pairs; j += DT) {
         const float4 q = __ldg(p4 + j);
         m = fmaxf(m, amp_of(q.x, q.y));
         m = fmaxf(m, amp_of(q.z, q.w));
     }
     if (((count - head) & 1) && lane == 0) { const cf x = ldg_cf(pkt + count - 1); m = fmaxf(m, amp_of(x.x, x.y)); }
-    return warp_max(m);
+    return pipe_max<DT>(m, redf);
 }
 
 template <int SF, bool EXTRA>
@@ -365,14 +406,16 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
     using P = fx::Plan<SF>;
     constexpr int T = C::T, N = C::N, GD = C::GD;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int dom = threadIdx.x >> 5;              // DOM_THREADS == 32: a pipeline is a warp
-    const int lane = threadIdx.x & 31;
+    constexpr int DT = C::DOM_THREADS;
+    const int dom = threadIdx.x / DT;              // pipeline index inside the CTA
+    const int lane = threadIdx.x % DT;             // thread index inside the pipeline
     const int gq = lane / T, tid = lane % T;
 
     cf* slots = reinterpret_cast<cf*>(smem_raw) + (size_t)dom * C::STAGES * C::SLOT;
     WinDesc* descs = reinterpret_cast<WinDesc*>(smem_raw + C::slot_bytes) + (size_t)dom * C::STAGES * GD;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::slot_bytes + C::desc_bytes) + dom * C::STAGES;
     Peak* red = reinterpret_cast<Peak*>(smem_raw + C::slot_bytes + C::desc_bytes + C::bar_bytes);   // unused for T <= 32
+    float* redf = reinterpret_cast<float*>(red + 8);
     WarpShared& ws = reinterpret_cast<WarpShared*>(smem_raw + C::ws_off)[dom];
 
     if (lane == 0) {
@@ -380,7 +423,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
         for (int s = 0; s < C::STAGES; ++s) ptx::mbar_init(&full[s], GD);
         ptx::fence_mbar_init();
     }
-    __syncwarp();
+    pipe_sync<DT>();
 
     int stage = 0;
     unsigned phase_bits = 0;
@@ -411,7 +454,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
         float use_max = pred_max;
         bool known = !legacy;
         if (legacy && (distrust > 0 || a.no_scratch)) {
-            use_max = warp_scan_max(pkt, count, lane);
+            use_max = pipe_scan_max<DT>(pkt, count, lane, redf);
             known = true;
             if (distrust > 0) distrust = (use_max == pred_max) ? distrust - 1 : DISTRUST_PACKETS;
             pred_max = use_max;
@@ -463,10 +506,10 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
                 }
                 fft_inplace<SF, true>(v, tid, a.tw, a.ct, win);
                 const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
-                __syncwarp();                              // last exchange fully read: the slot becomes the spectrum
+                pipe_sync<DT>();                              // last exchange fully read: the slot becomes the spectrum
 #pragma unroll
                 for (int r = 0; r < P::R; ++r) win[P::bin_of_reg(tid, r)] = v[r];
-                __syncwarp();
+                pipe_sync<DT>();
                 if (tid == 0 && live) {
                     EstSym e; e.idx = 0; e.fi = 0.0f; e.phase = 0.0f; e.t = 0;
                     cf best_bin = fx::mk(0.0f, 0.0f);
@@ -486,7 +529,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
                     ws.est[s] = e;
                 }
                 ptx::fence_proxy_async();
-                __syncwarp();
+                pipe_sync<DT>();
                 stage ^= 1;
             }
 
@@ -520,8 +563,14 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
                 rate = __fdiv_rn(fx::fmul(-2.0f * PI_F, cfo), (float)N);
                 ws.sw[0] = 0; ws.sw[1] = 0;
             }
-            rate = __shfl_sync(0xffffffffu, rate, 0);
-            t_off = __shfl_sync(0xffffffffu, t_off, 0);
+            if (DT <= 32) {
+                rate = __shfl_sync(0xffffffffu, rate, 0);
+                t_off = __shfl_sync(0xffffffffu, t_off, 0);
+            } else {
+                if (lane == 0) { ws.bc_rate = rate; ws.bc_toff = t_off; }
+                pipe_sync<DT>();
+                rate = ws.bc_rate; t_off = ws.bc_toff;
+            }
             have_metrics = true;
 
             // ---- C units --------------------------------------------------------------------------
@@ -571,18 +620,18 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
                     else a.symbols[(size_t)pid * a.symbol_stride + (have_sync ? s - 2 : s)] = (uint16_t)pk.idx;
                 }
                 ptx::fence_proxy_async();
-                __syncwarp();
+                pipe_sync<DT>();
                 stage ^= 1;
             }
 
             // ---- verify the trusted max against the samples actually walked ------------------------------
             if (known) break;
-            if (t_off != 0 || count != total * (uint32_t)N || __any_sync(0xffffffffu, suspicious)) {
+            if (t_off != 0 || count != total * (uint32_t)N || pipe_any<DT>(suspicious)) {
                 // shifted windows / a trailing partial symbol leave samples the units did not stream, and NaN samples
                 // are invisible to the tracked max: scan the packet with the reference's own comparison
-                m = warp_scan_max(pkt, count, lane);
+                m = pipe_scan_max<DT>(pkt, count, lane, redf);
             } else {
-                m = warp_max(m);
+                m = pipe_max<DT>(m, redf);
             }
             const bool ok = (m > 1.0f) ? (m == use_max) : !(use_max > 1.0f);
             pred_max = m;
@@ -593,7 +642,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
         }
 
         // ---- bookkeeping: LoRaDemod.cpp:166-196 ----------------------------------------------------------
-        __syncwarp();
+        pipe_sync<DT>();
         if (lane == 0) {
             const bool run = !(flags & PS_SKIP);
             if (run) status = have_sync ? (int)(total - 2) : (int)total;
@@ -607,9 +656,13 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
             }
             if (a.status) a.status[pid] = status;
         }
-        __syncwarp();
+        pipe_sync<DT>();
     }
 }
+
+// measured (A/B in one run, 1.965 GHz): SF10 44.4 -> 39.7 ms, SF11 42.0 -> 40.8 ms with a pipeline per packet; SF12's
+// pipeline is the whole CTA and cfg 3's packets alternate between two max-abs classes, so it keeps the scan-first kernel
+constexpr int PIPE_MAX_SF_DEFAULT = 11;
 
 template <int SF>
 static cudaError_t launch_warp_sf(const DemodArgs& a, int sm_count, cudaStream_t stream)
@@ -660,13 +713,17 @@ bool packet_supported(int sf, const DemodArgs& a)
 
 cudaError_t launch_demod_packet(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream)
 {
+    // pipeline-per-packet kernel (a warp for SF7-9, the window's 2 / 4 warps for SF10 / 11) up to PIPE_MAX_SF,
+    // CTA-per-packet kernel above; LORA_PHY_PIPE_MAX_SF (9..12) overrides the split for A/B measurements
+    static int pipe_max_sf = [] { const char* e = getenv("LORA_PHY_PIPE_MAX_SF"); const int v = e ? atoi(e) : 0;
+                                  return (v >= 9 && v <= 12) ? v : PIPE_MAX_SF_DEFAULT; }();
     switch (sf) {
     case 7: return launch_warp_sf<7>(a, sm_count, stream);
     case 8: return launch_warp_sf<8>(a, sm_count, stream);
     case 9: return launch_warp_sf<9>(a, sm_count, stream);
-    case 10: return launch_packet_sf<10>(a, sm_count, stream);
-    case 11: return launch_packet_sf<11>(a, sm_count, stream);
-    case 12: return launch_packet_sf<12>(a, sm_count, stream);
+    case 10: return pipe_max_sf >= 10 ? launch_warp_sf<10>(a, sm_count, stream) : launch_packet_sf<10>(a, sm_count, stream);
+    case 11: return pipe_max_sf >= 11 ? launch_warp_sf<11>(a, sm_count, stream) : launch_packet_sf<11>(a, sm_count, stream);
+    case 12: return pipe_max_sf >= 12 ? launch_warp_sf<12>(a, sm_count, stream) : launch_packet_sf<12>(a, sm_count, stream);
     default: return cudaErrorInvalidValue;
     }
 }
