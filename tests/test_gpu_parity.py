@@ -877,3 +877,46 @@ def test_full_size_batches(phy, lp, oracle, sf, L, P, n_check):
         assert np.float32(o_to).tobytes() == out["time_offset"][p].cpu().numpy().tobytes()
     del iq, out, pay, payload, sym
     torch.cuda.empty_cache()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf,n_pkt", [(7, 9000), (8, 8000), (9, 8000), (10, 4500), (11, 2600), (12, 1000)])
+def test_pipeline_packet_sequences(phy, lp, oracle, sf, n_pkt):
+    """More packets than resident pipelines (444 CTAs x 8 / 4 / 2 / 1), so every pipeline walks a SEQUENCE of packets and
+    the max-abs prediction goes through hit, miss + second walk, distrust (scan first) and recovery: amplitude classes
+    change in runs (clean, x1.7, x0.4, noisy, all-zero, NaN / inf samples), some packets are ragged.  Every packet ==
+    the oracle."""
+    rng = np.random.default_rng(4000 + sf)
+    N = 1 << sf
+    S = 3
+    base = make_packets(oracle, rng, sf, 1, 8, S - 2, kind="clean")
+    noisy = make_packets(oracle, rng, sf, 1, 8, S - 2, kind="noisy")
+    iq = np.empty((n_pkt, S * N), np.complex64)
+    cls = 0
+    for p in range(n_pkt):
+        if rng.random() > 0.8:
+            cls = int(rng.integers(0, 9))
+        d = base[p % 8].copy()
+        if cls == 1:
+            d = (d * np.float32(1.7)).astype(np.complex64)
+        elif cls == 2:
+            d = (d * np.float32(0.4)).astype(np.complex64)
+        elif cls == 3:
+            d = noisy[p % 8].copy()
+        elif cls == 4:
+            d[:] = 0
+        elif cls == 5:
+            d[int(rng.integers(0, d.size))] = np.complex64(complex(np.nan, 5.0))
+        elif cls == 6:
+            d[int(rng.integers(0, d.size))] = np.complex64(complex(0.5, np.nan))
+        elif cls == 7:
+            d[int(rng.integers(0, d.size))] = np.complex64(complex(np.inf, 0.0))
+        elif cls == 8:
+            d = (d * np.float32(1.0 + 2.0 ** -20)).astype(np.complex64)
+        iq[p] = d
+    counts = np.full(n_pkt, S * N, np.uint32)
+    ragged = rng.random(n_pkt) < 0.1
+    counts[ragged] = rng.integers(0, S * N + 1, int(ragged.sum()))
+    with np.errstate(all="ignore"):
+        check_legacy(phy, lp, oracle, iq, sf, 1, 0, counts=counts)
+        check_legacy(phy, lp, oracle, iq[: n_pkt // 2], sf, 1, 0, flags=lp.F_NO_SCRATCH)
