@@ -104,7 +104,13 @@ __device__ __forceinline__ void chain_window(cf (&v)[fx::Plan<SF>::R], const cf*
             if (EXTRA && down) x = fx::cmul(x, ldg_cf(down + tid + T * c));          // phy.cpp:224
             const float ph = fx::fadd(start, fx::fmul(rate, fx::fadd(fi0, (float)(T * c))));
             float sn, cs;
+#if defined(LORA_ABLATE_SINCOS)
+            // measurement-only build (tools/ablate.sh, never the product): a 3-instruction stand-in for the exact
+            // sincosf, to time the chain without it
+            sn = ph; cs = fx::fsub(1.0f, fx::fmul(ph, ph));
+#else
             gm::sincosf_core(ph, &sn, &cs);                                          // LoRaDemod.cpp:155-159
+#endif
             x = fx::cmul(x, fx::mk(cs, sn));
             if (EXTRA && w) x = fx::cscale(x, __ldg(w + tid + T * c));               // LoRaDemod.cpp:160-161
             v[c] = x;

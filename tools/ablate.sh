@@ -1,0 +1,17 @@
+#!/bin/bash
+# Measurement-only build variants of the demodulator (never the product; outputs are git-ignored .so files
+# under tools/ubench/ablate/).  Each variant swaps ONE part of the per-sample chain for a cheap, inexact
+# stand-in so that `LORA_PHY_LIB=<variant> python bench.py --no-cpu` times the chain without it.
+#   nosincos : the glibc-exact double-precision sincosf of the CFO rotation -> 3 float instructions
+# Usage: tools/ablate.sh   (after `make -C <pkg>/csrc`, which provides the other objects)
+set -euo pipefail
+ROOT=$(cd "$(dirname "$0")/.." && pwd)
+C=$ROOT/lora-sdr-lightweight-standalone-library-clean_b200/csrc
+OUT=$ROOT/tools/ubench/ablate
+mkdir -p "$OUT"
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+FLAGS="-std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false -Xcompiler -fPIC"
+$NVCC $FLAGS -DLORA_ABLATE_SINCOS -c "$C/demod_packet.cu" -o "$OUT/demod_packet_nosincos.o"
+$NVCC -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o "$OUT/liblora_nosincos.so" \
+    "$OUT/demod_packet_nosincos.o" $(ls "$C"/build/*.o | grep -v '/demod_packet.o$')
+echo "built $OUT/liblora_nosincos.so"
