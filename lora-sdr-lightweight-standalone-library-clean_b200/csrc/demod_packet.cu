@@ -612,7 +612,9 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
                 // instruction cache -- 24 warps walk this loop out of phase -- is what the issue rate is short of
                 chain_window<SF, EXTRA, true>(v, raw, tid, scale, rate, start, slow, a.down, a.window, &mw);
                 if (active) m = fmaxf(m, mw);
+#if !defined(LORA_ABLATE_FFT)                      // measurement-only variant (tools/ablate.sh): the chain without the FFT
                 fft_inplace<SF, false>(v, tid, a.tw, a.ct, win);
+#endif
                 const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
                 if (tid == 0 && active) {
                     if (!(pk.val > 0.0f)) suspicious = true;
