@@ -301,6 +301,12 @@ def main():
     ap.add_argument("--fused", action="store_true", help="A/B: time the experimental ticket-scheduled fused launch (demod_fused.cu)")
     ap.add_argument("--two-kernel", action="store_true", help="A/B: time the older prepass + symbols kernel pair")
     args = ap.parse_args()
+    # stdout carries the ONE JSON line and nothing else: libraries that write to fd 1 (NCCL prints its version
+    # banner there under some NCCL_DEBUG settings) are sent to stderr for the rest of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(json_fd, "w", buffering=1)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
