@@ -162,7 +162,7 @@ def run_ours(args, wl):
     two = args.two_kernel
     cfg_pre = lp.make_cfg(sf, flags=lp.F_ONLY_PREPASS)
     cfg_sym = lp.make_cfg(sf, flags=lp.F_ONLY_SYMBOLS)
-    cfg_one = lp.make_cfg(sf, flags=lp.F_FUSED) if args.fused else cfg
+    cfg_one = cfg
 
     def step(ev=None):
         if not two:                            # default: ONE launch per batch (demod_packet_kernel, one CTA per packet)
@@ -248,12 +248,11 @@ def run_ours(args, wl):
         kname = "symbols_stream_kernel<SF%d>" % sf
         sym_bytes = P * (nsym - 2) * b_sym              # symbols kernel: data symbols of every packet, once
     else:
-        kname = ("demod_fused_kernel<SF%d>" if args.fused else
-                 "demod_warp_kernel<SF%d>" if sf <= 11 else "demod_packet_kernel<SF%d>") % sf   # demod_packet.cu: pipeline per packet SF7-11
+        kname = ("demod_warp_kernel<SF%d>" if sf <= 11 else "demod_packet_kernel<SF%d>") % sf   # demod_packet.cu: pipeline per packet SF7-11
         sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if not two and not args.fused and os.path.exists(tpath):
+    if not two and os.path.exists(tpath):
         traffic = (json.load(open(tpath)).get("%s:%d" % (args.workload, P)) or {}).get("bytes")
     achieved = sym_bytes / (sym_kernel_ms * 1e-3) / 1e9
     step_bytes = P * nsym * b_sym
@@ -298,7 +297,6 @@ def main():
     ap.add_argument("--packets", type=int, default=0, help="packets per GPU (default: the workload's)")
     ap.add_argument("--e2e-packets", type=int, default=1 << 15)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--fused", action="store_true", help="A/B: time the experimental ticket-scheduled fused launch (demod_fused.cu)")
     ap.add_argument("--two-kernel", action="store_true", help="A/B: time the older prepass + symbols kernel pair")
     args = ap.parse_args()
     # stdout carries the ONE JSON line and nothing else: libraries that write to fd 1 (NCCL prints its version

@@ -17,10 +17,12 @@
  *     missing scratch, -ENOMEM missing buffer, plus -EIO for a CUDA failure
  *     (text via lora_phy_cuda_last_error);
  *   - there is NO CPU fallback: without a CUDA device create() fails with -ENODEV;
- *   - threading: like the reference (one workspace per thread, phy.hpp:74-78) a context serves ONE caller at
- *     a time -- it owns the staging buffers, scratch and stream its calls use.  Use one context per host
- *     thread (contexts on the same device are independent); device work of one context is ordered on its
- *     stream, and the device-pointer entry points return without waiting for it.
+ *   - threading: a context owns the staging buffers, scratch and stream its calls use; every entry point holds
+ *     the context's mutex from its first use of them to its last (the *_host variants: through the copy-out), so
+ *     calls from several threads on ONE context are safe and serialise.  For parallelism use one context per
+ *     host thread, like one workspace per thread in the reference (phy.hpp:74-78); contexts on the same device
+ *     are independent.  Device work of one context is ordered on its stream, and the device-pointer entry
+ *     points return without waiting for it.
  */
 #ifndef LORA_PHY_CUDA_H
 #define LORA_PHY_CUDA_H
@@ -58,12 +60,14 @@ typedef struct lora_phy_cuda_cfg {
 /* Split one demodulate_batch call into its two launches (bench.py times the kernels separately
  * with CUDA events; a normal call sets neither):                                            */
 #define LORA_PHY_CUDA_F_ONLY_PREPASS 0x10u /* run only the per-packet prepass (max-abs, estimator, sync) */
-#define LORA_PHY_CUDA_F_FUSED        0x40u /* experimental: scan + estimator + data symbols in ONE persistent cooperative
-                                              launch (demod_fused.cu) instead of the prepass + symbols kernel pair;
-                                              results are identical, see DESIGN.md for when it pays */
 #define LORA_PHY_CUDA_F_ONLY_SYMBOLS 0x20u /* run only the data-symbol kernel, reusing the packet state
                                               the previous prepass of the same batch left in the context */
 
+#define LORA_PHY_CUDA_F_EXACT         0x100u /* A/B: demodulate every window with the operation-for-operation replay of the
+                                               reference's float arithmetic (bit-exact spectra), instead of the default
+                                               margin-certified fast path that falls back to that replay per window only
+                                               when the argmax is not provably the reference's.
+                                               Symbols, sync word, status, cfo and time_offset are identical either way. */
 #define LORA_PHY_CUDA_F_TWO_KERNEL   0x80u /* A/B: force the older prepass + symbols kernel pair instead of the default
                                               single launch with one CTA per packet (demod_packet.cu) */
 
@@ -85,8 +89,11 @@ int  lora_phy_cuda_synchronize(lora_phy_cuda_ctx* ctx);
 /* replaces lora_demodulate (LoRaDemod.cpp:50-197) -- and, with F_DECHIRP, demodulate
  * (phy.cpp:182-243) -- for n_packets independent packets.
  *   d_iq            [n_packets][packet_stride] complex64
- *   d_sample_counts NULL (every packet has samples_per_packet samples) or [n_packets] ragged lengths
- *                   (<= samples_per_packet); a trailing partial symbol is ignored (LoRaDemod.cpp:57)
+ *   d_iq            must be 8-byte aligned (complex64); it need NOT be 16-byte aligned and nothing outside
+ *                   [d_iq, d_iq + n_packets*packet_stride) is ever read
+ *   d_sample_counts NULL (every packet has samples_per_packet samples) or [n_packets] ragged lengths; a count above
+ *                   samples_per_packet is clamped to it on the device (the *_host variant returns -EINVAL instead);
+ *                   a trailing partial symbol is ignored (LoRaDemod.cpp:57)
  *   d_symbols       [n_packets][symbol_stride] uint16: the data symbols (sync symbols stripped when
  *                   the packet has >= 2 symbols, LoRaDemod.cpp:166-175)
  *   d_sync          [n_packets] recovered sync word (LoRaDemod.cpp:178-193), may be NULL

@@ -19,8 +19,8 @@ F_DECHIRP = 0x1
 F_NO_SCRATCH = 0x2
 F_ONLY_PREPASS = 0x10
 F_ONLY_SYMBOLS = 0x20
-F_FUSED = 0x40
 F_TWO_KERNEL = 0x80
+F_EXACT = 0x100
 
 
 class Cfg(C.Structure):

@@ -65,8 +65,7 @@ struct lora_phy_cuda_ctx {
     uint64_t launches = 0;
     SfTables tab[13];
     std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
-    DevBuf state, phases, tmp, sched;                   // PacketState[], modulator phases, compensate scratch, fused-kernel counters
-    uint32_t lookahead_bytes = 64u << 20;               // fused schedule look-ahead (LORA_PHY_LOOKAHEAD_MB)
+    DevBuf state, phases, tmp;                          // PacketState[], modulator phases, compensate scratch
     cf* sync_tab[13] = { nullptr };                      // stream detector tables per sf: up | down | fine (stream_sync.cu)
     DevBuf txrx[3];                                      // tx/rx pipelines: symbols, status, host-variant results
     DevBuf mc[8];                                        // Monte-Carlo driver: payload, tx symbols, IQ, rx symbols, status+sync, decoded, len, flags
@@ -75,7 +74,7 @@ struct lora_phy_cuda_ctx {
     DevBuf lfsr;                                         // dewhitening byte table of the coding chain (chain.cu)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
-    std::mutex mu;
+    std::recursive_mutex mu;                            // held for a whole entry point (staging buffers, scratch, err)
 };
 
 namespace {
@@ -125,6 +124,16 @@ struct Guard {
     ~Guard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// Every entry point that touches a context holds its (recursive) mutex from the first use of the staging buffers /
+// scratch / error string to the last copy-out, so two threads sharing one context (the C++ drop-in wrapper routes
+// every workspace through one) serialise instead of racing on d_in / d_out / h_out; the entry points nest
+// (a *_host call runs the device call under the same lock).
+struct CtxGuard {
+    std::lock_guard<std::recursive_mutex> lock;
+    Guard dev;
+    explicit CtxGuard(lora_phy_cuda_ctx* c) : lock(c->mu), dev(c->device) {}
+};
+
 } // namespace
 
 extern "C" {
@@ -147,10 +156,6 @@ int lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device)
     ctx->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return -EIO; }
     ctx->own_stream = true;
-    if (const char* mb = getenv("LORA_PHY_LOOKAHEAD_MB")) {
-        const long v = strtol(mb, nullptr, 10);
-        if (v > 0 && v < 4096) ctx->lookahead_bytes = (uint32_t)v << 20;
-    }
     for (int sf = 2; sf <= 12; ++sf) {
         const size_t N = (size_t)1 << sf;
         SfTables& t = ctx->tab[sf];
@@ -171,7 +176,7 @@ int lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device)
 void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
 {
     if (!ctx) return;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (int sf = 2; sf <= 12; ++sf) {
         if (ctx->tab[sf].tw) cudaFree(ctx->tab[sf].tw);
@@ -183,7 +188,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
     ctx->lfsr.release();
     for (auto& b : ctx->mc) b.release();
     for (auto& b : ctx->txrx) b.release();
-    ctx->state.release(); ctx->phases.release(); ctx->tmp.release(); ctx->sched.release();
+    ctx->state.release(); ctx->phases.release(); ctx->tmp.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
     ctx->h_in.release(); ctx->h_out.release();
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -197,7 +202,7 @@ uint64_t lora_phy_cuda_launch_count(const lora_phy_cuda_ctx* ctx) { return ctx ?
 int lora_phy_cuda_set_stream(lora_phy_cuda_ctx* ctx, void* stream)
 {
     if (!ctx) return -EINVAL;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     ctx->stream = static_cast<cudaStream_t>(stream);
@@ -208,7 +213,7 @@ int lora_phy_cuda_set_stream(lora_phy_cuda_ctx* ctx, void* stream)
 int lora_phy_cuda_synchronize(lora_phy_cuda_ctx* ctx)
 {
     if (!ctx) return -EINVAL;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     CK(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
@@ -222,6 +227,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     int rc = check_cfg(ctx, cfg);
     if (rc) return rc;
     if (!d_iq && n_packets && spp) return fail(ctx, -EINVAL, "d_iq is NULL");
+    if (reinterpret_cast<uintptr_t>(d_iq) & 7u) return fail(ctx, -EINVAL, "d_iq is not 8-byte aligned");
     if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
     if (spp > 0xffffffffull || n_packets > 0xffffffffull) return fail(ctx, -EINVAL, "batch too large");
     const size_t N = (size_t)1 << cfg->sf, step = N * cfg->osr;
@@ -240,8 +246,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
         if (dsm > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than the data symbols per packet");
     }
     if (n_packets == 0) return 0;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     CK(ctx->state.reserve(n_packets * sizeof(lk::PacketState)));
 
     lk::DemodArgs a;
@@ -275,23 +280,8 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.time_offset = d_to;
     a.status = d_status;
     unsigned launches = 0;
-    // experimental: one persistent cooperative launch for the whole demodulator ("fused schedule")
-    if ((cfg->flags & LORA_PHY_CUDA_F_FUSED) && !(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS))) {
-        lk::FusedArgs f;
-        if (lk::fused_plan((int)cfg->sf, a, ctx->lookahead_bytes, &f)) {
-            const size_t words = 4 + 3 * n_packets;
-            CK(ctx->sched.reserve(words * sizeof(uint32_t)));
-            CK(cudaMemsetAsync(ctx->sched.p, 0, words * sizeof(uint32_t), ctx->stream));
-            uint32_t* w = static_cast<uint32_t*>(ctx->sched.p);
-            f.pmax = w + 4; f.acount = w + 4 + n_packets; f.eready = w + 4 + 2 * n_packets;
-            cudaError_t e = lk::launch_demod_fused((int)cfg->sf, f, ctx->sm_count, ctx->stream);
-            ++ctx->launches;
-            if (e != cudaSuccess) return fail(ctx, -EIO, "fused demodulator launch", e);
-            return 0;
-        }
-    }
     // default: one launch, one CTA per packet (demod_packet.cu)
-    if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_FUSED)) &&
+    if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL)) &&
         lk::packet_supported((int)cfg->sf, a)) {
         cudaError_t e = lk::launch_demod_packet((int)cfg->sf, a, ctx->sm_count, ctx->stream);
         ++ctx->launches;
@@ -337,7 +327,7 @@ int lora_phy_cuda_demodulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_c
     if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
     if (n_packets == 0) return demod_common(ctx, cfg, (cfg->flags & LORA_PHY_CUDA_F_DECHIRP) ? lk::MODE_HIGHLEVEL : lk::MODE_LEGACY,
                                             h_iq, packet_stride, nullptr, spp, 0, h_symbols, symbol_stride, nullptr, nullptr, nullptr, nullptr);
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t iq_bytes = n_packets * packet_stride * sizeof(cf);
     const size_t sym_bytes = n_packets * symbol_stride * sizeof(uint16_t);
     // device scratch layout (d_out): symbols | cfo | time_offset | status | sync
@@ -349,6 +339,8 @@ int lora_phy_cuda_demodulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_c
     CK(ctx->h_out.reserve(out_bytes));
     uint32_t* d_counts = nullptr;
     if (h_counts) {
+        for (size_t p = 0; p < n_packets; ++p)
+            if (h_counts[p] > spp) return fail(ctx, -EINVAL, "a sample count exceeds samples_per_packet");
         CK(ctx->d_aux.reserve(n_packets * 4));
         d_counts = static_cast<uint32_t*>(ctx->d_aux.p);
         CK(cudaMemcpyAsync(d_counts, h_counts, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -385,8 +377,7 @@ int lora_phy_cuda_compensate_offsets_batch(lora_phy_cuda_ctx* ctx, const lora_ph
     if (!d_iq || !d_cfo || !d_to) return fail(ctx, -EINVAL, "NULL buffer");
     if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
     if (!n_packets || !spp) return 0;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     const size_t bytes = n_packets * packet_stride * sizeof(cf);
     CK(ctx->tmp.reserve(bytes));
     CK(lk::launch_compensate(static_cast<const cf*>(d_iq), static_cast<cf*>(ctx->tmp.p), packet_stride, (uint32_t)spp,
@@ -406,7 +397,7 @@ int lora_phy_cuda_estimate_offsets_batch_host(lora_phy_cuda_ctx* ctx, const lora
     if (!h_iq || !h_cfo || !h_to) return fail(ctx, -EINVAL, "NULL buffer");
     if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
     if (!n_packets) return 0;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t iq_bytes = n_packets * packet_stride * sizeof(cf);
     CK(ctx->d_in.reserve(iq_bytes + 16));
     CK(ctx->d_out.reserve(n_packets * 8));
@@ -433,7 +424,7 @@ int lora_phy_cuda_compensate_offsets_batch_host(lora_phy_cuda_ctx* ctx, const lo
     if (!h_iq || !h_cfo || !h_to) return fail(ctx, -EINVAL, "NULL buffer");
     if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
     if (!n_packets || !spp) return 0;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t iq_bytes = n_packets * packet_stride * sizeof(cf);
     CK(ctx->d_in.reserve(iq_bytes + 16));
     CK(ctx->d_aux.reserve(n_packets * 8));
@@ -457,7 +448,7 @@ int lora_phy_cuda_detect_batch(lora_phy_cuda_ctx* ctx, uint32_t sf, const void* 
     if (sf < 2 || sf > 12) return fail(ctx, -EINVAL, "sf out of range 2..12");
     if (!d_windows && n_windows) return fail(ctx, -EINVAL, "d_windows is NULL");
     if (!n_windows) return 0;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     lk::DetectArgs a;
     a.windows = static_cast<const cf*>(d_windows);
     a.n_windows = (uint32_t)n_windows;
@@ -481,8 +472,7 @@ long lora_phy_cuda_modulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cf
     const size_t produced = (spp_sym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
     if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
     if (!n_packets) return (long)produced;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     CK(ctx->phases.reserve(n_packets * (spp_sym + 2) * sizeof(float)));
     lk::ModArgs a;
     a.symbols = d_symbols; a.symbol_stride = symbol_stride; a.symbols_per_packet = (uint32_t)spp_sym;
@@ -518,8 +508,7 @@ long lora_phy_cuda_modulate_frames_batch(lora_phy_cuda_ctx* ctx, const lora_phy_
     if (produced < 0) return fail(ctx, (int)produced, "bad frame geometry");
     if ((size_t)produced > frame_stride) return fail(ctx, -ERANGE, "frame_stride smaller than the frame");
     if (!n_frames) return produced;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     CK(ctx->phases.reserve(n_frames * (spf + 15) * sizeof(float)));
     lk::ModArgs a;
     a.symbols = d_symbols; a.symbol_stride = symbol_stride; a.symbols_per_packet = (uint32_t)spf;
@@ -545,7 +534,7 @@ long lora_phy_cuda_modulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cu
     const size_t produced = (spp_sym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
     if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
     if (!n_packets) return (long)produced;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t sym_bytes = (n_packets * symbol_stride + 1) * 2, iq_bytes = n_packets * packet_stride * sizeof(cf);
     CK(ctx->d_in.reserve(sym_bytes));
     CK(ctx->d_out.reserve(iq_bytes));
@@ -565,10 +554,10 @@ int lora_phy_cuda_dechirp_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg*
     int rc = check_cfg(ctx, cfg);
     if (rc) return rc;
     if (!d_iq && n_packets && spp) return fail(ctx, -EINVAL, "d_iq is NULL");
+    if (reinterpret_cast<uintptr_t>(d_iq) & 7u) return fail(ctx, -EINVAL, "d_iq is not 8-byte aligned");
     if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
     if (!n_packets || !spp) return 0;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     cf* table = nullptr;
     rc = get_chirp(ctx, (int)cfg->sf, (int)cfg->bw_hz, (int)cfg->osr, &table);
     if (rc) return rc;
@@ -586,7 +575,7 @@ long lora_phy_cuda_encode_batch(lora_phy_cuda_ctx* ctx, const uint8_t* d_payload
     if ((!d_payload || !d_symbols) && n_packets && payload_len) return fail(ctx, -EINVAL, "NULL buffer");
     if (payload_len > payload_stride && n_packets > 1) return fail(ctx, -EINVAL, "payload_len exceeds payload_stride");
     if (2 * payload_len > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than 2*payload_len");
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     CK(lk::launch_encode(d_payload, payload_stride, (uint32_t)payload_len, (uint32_t)n_packets, d_symbols, symbol_stride, ctx->stream));
     if (n_packets && payload_len) ++ctx->launches;
     return (long)(2 * payload_len);
@@ -600,7 +589,7 @@ long lora_phy_cuda_decode_batch(lora_phy_cuda_ctx* ctx, const uint16_t* d_symbol
     if ((!d_symbols || !d_payload) && n_packets && spp) return fail(ctx, -EINVAL, "NULL buffer");
     if (!d_counts && (spp & 1)) return fail(ctx, -EINVAL, "odd symbol count");      // LoRaDecoder.cpp:10
     if (spp / 2 > payload_stride) return fail(ctx, -ERANGE, "payload_stride smaller than symbols/2");
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     CK(lk::launch_decode(d_symbols, symbol_stride, d_counts, (uint32_t)spp, (uint32_t)n_packets, d_payload, payload_stride, d_crc_ok, ctx->stream));
     if (n_packets) ctx->launches += (spp / 2 ? 1 : 0) + (d_crc_ok ? 1 : 0);
     return (long)(spp / 2);
@@ -613,7 +602,7 @@ long lora_phy_cuda_encode_batch_host(lora_phy_cuda_ctx* ctx, const uint8_t* h_pa
     if ((!h_payload || !h_symbols) && n_packets && payload_len) return fail(ctx, -EINVAL, "NULL buffer");
     if (2 * payload_len > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than 2*payload_len");
     if (!n_packets || !payload_len) return (long)(2 * payload_len);
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t in_bytes = (n_packets - 1) * payload_stride + payload_len, out_bytes = n_packets * symbol_stride * 2;
     CK(ctx->d_in.reserve(in_bytes));
     CK(ctx->d_out.reserve(out_bytes));
@@ -636,7 +625,7 @@ long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_s
     if (!h_counts && (spp & 1)) return fail(ctx, -EINVAL, "odd symbol count");
     if (spp / 2 > payload_stride) return fail(ctx, -ERANGE, "payload_stride smaller than symbols/2");
     if (!n_packets) return (long)(spp / 2);
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t in_bytes = ((n_packets - 1) * symbol_stride + spp) * 2;
     const size_t pay_bytes = n_packets * payload_stride;
     CK(ctx->d_in.reserve(in_bytes + 16));
@@ -683,7 +672,7 @@ static int sync_tables(lora_phy_cuda_ctx* ctx, uint32_t sf, cf** out)
         const std::complex<double> e = std::polar(1.0, acc);
         host[i] = fx::mk((float)e.real(), (float)-e.imag());          // _upChirpTable = conj(entry)
         host[N + i] = fx::mk((float)e.real(), (float)e.imag());       // _downChirpTable
-        phase += (float)((2 * M_PI) / (double)N);
+        phase = (float)((double)phase + (2 * M_PI) / (double)N);      // float += double: summed in double, rounded once
     }
     acc = 0.0;
     phase = (float)(2.0 * M_PI / (double)fine_n);
@@ -714,8 +703,7 @@ int lora_phy_cuda_detect_stream(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t sy
     if (n_streams && (!d_iq || !d_n_frames || (max_frames && (!d_frame_start || !d_frame_err || !d_frame_nsym || !d_symbols))))
         return fail(ctx, -EINVAL, "NULL buffer");
     if (!n_streams) return 0;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     cf* tab = nullptr;
     int rc = sync_tables(ctx, sf, &tab);
     if (rc) return rc;
@@ -753,8 +741,7 @@ int lora_phy_cuda_detect_streams_mixed(lora_phy_cuda_ctx* ctx, const uint8_t* h_
         ids[h_sf[s]].push_back((uint32_t)s);
     }
     if (!n_streams) return 0;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     CK(ctx->tmp.reserve(n_streams * sizeof(uint32_t)));
     uint32_t* d_ids = static_cast<uint32_t*>(ctx->tmp.p);
     size_t off = 0;
@@ -822,7 +809,7 @@ long lora_phy_cuda_encode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cud
     const long nsym = lora_phy_cuda_chain_symbols(cc, payload_len);
     if ((size_t)nsym > symbol_stride) return fail(ctx, -ERANGE, "symbol_stride smaller than the symbols per packet");
     if (n_packets > 0xffffffffull) return fail(ctx, -EINVAL, "batch too large");
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     CK(lk::launch_chain_encode(a, d_payload, payload_stride, (uint32_t)payload_len, (uint32_t)n_packets, d_symbols,
                                symbol_stride, ctx->sm_count, ctx->stream));
     if (n_packets) ++ctx->launches;
@@ -844,8 +831,7 @@ int lora_phy_cuda_decode_chain_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda
         return fail(ctx, -EINVAL, "too many symbols per packet for the coding chain (a 255-byte packet needs < 700)");
     if (n_packets > 0xffffffffull) return fail(ctx, -EINVAL, "batch too large");
     if (!n_packets) return 0;
-    Guard g(ctx->device);
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    CtxGuard g(ctx);
     if (!ctx->lfsr.p) {
         const size_t n = (size_t)lk::chain_lfsr_table_size();
         std::string host(n, '\0');
@@ -876,7 +862,7 @@ long lora_phy_cuda_tx_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg
     if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
     if (!n_packets) return (long)produced;
     {
-        Guard g(ctx->device);
+        CtxGuard g(ctx);
         CK(ctx->txrx[0].reserve(n_packets * (size_t)nsym * 2));
     }
     uint16_t* sym = static_cast<uint16_t*>(ctx->txrx[0].p);
@@ -899,7 +885,7 @@ int lora_phy_cuda_rx_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
     if (!n_packets) return 0;
     const size_t nsym = total - 2;
     {
-        Guard g(ctx->device);
+        CtxGuard g(ctx);
         CK(ctx->txrx[0].reserve(n_packets * (nsym + 1) * 2));
         CK(ctx->txrx[1].reserve(n_packets * 4));
     }
@@ -929,7 +915,7 @@ long lora_phy_cuda_tx_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg
     const size_t produced = ((size_t)nsym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
     if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
     if (!n_packets) return (long)produced;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t in_bytes = (n_packets - 1) * payload_stride + payload_len, iq_bytes = n_packets * packet_stride * sizeof(cf);
     CK(ctx->d_in.reserve(in_bytes + 16));
     CK(ctx->d_out.reserve(iq_bytes));
@@ -953,7 +939,7 @@ int lora_phy_cuda_rx_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg*
     if ((!h_iq || !h_payload || !h_len) && n_packets) return fail(ctx, -EINVAL, "NULL buffer");
     if (spp > packet_stride) return fail(ctx, -EINVAL, "samples_per_packet exceeds packet_stride");
     if (!n_packets) return 0;
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t iq_bytes = ((n_packets - 1) * packet_stride + spp) * sizeof(cf), pay_bytes = n_packets * payload_stride;
     // results: payload | len (int32) | cfo | time_offset | flags | sync
     const size_t o_len = (pay_bytes + 15) & ~(size_t)15, o_cfo = o_len + n_packets * 4, o_to = o_cfo + n_packets * 4,
@@ -1000,7 +986,7 @@ int lora_phy_cuda_awgn_roundtrip(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cha
         return fail(ctx, -ERANGE, "output stride too small");
     if (!n_packets) return 0;
     std::lock_guard<std::mutex> mc_lock(ctx->mc_mu);
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     if (const char* e = getenv("LORA_PHY_MC_SCRATCH_MB")) {
         const long mb = atol(e);
         if (mb > 0) ctx->mc_scratch_bytes = (size_t)mb << 20;
@@ -1020,7 +1006,6 @@ int lora_phy_cuda_awgn_roundtrip(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cha
     lora_phy_cuda_cfg cfg = { cc->sf, 125000u, 1u, 0u, 0u, 0x12u, 1.0f, 0u };
     cf* table = nullptr;
     {
-        std::lock_guard<std::mutex> lock(ctx->mu);
         int rc = get_chirp(ctx, (int)cc->sf, 125000, 1, &table);
         if (rc) return rc;
     }
@@ -1073,7 +1058,7 @@ int lora_phy_cuda_copy_table(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t bw_hz
 {
     if (!ctx || !h_out) return -EINVAL;
     if (sf < 2 || sf > 12) return fail(ctx, -EINVAL, "sf out of range 2..12");
-    Guard g(ctx->device);
+    CtxGuard g(ctx);
     const size_t N = (size_t)1 << sf;
     if (which == 0) { CK(cudaMemcpyAsync(h_out, ctx->tab[sf].tw, N * sizeof(cf), cudaMemcpyDeviceToHost, ctx->stream)); }
     else if (which == 1) { CK(cudaMemcpyAsync(h_out, ctx->tab[sf].hann, N * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream)); }

@@ -8,6 +8,7 @@
 //   detect_kernel   LoRaDetector::detect on caller-supplied windows (parity tests).
 //
 // Compiled with -fmad=false: every float operation rounds once, like the reference binary.
+#include <atomic>
 #include "demod_device.cuh"
 #include "internal.h"
 
@@ -54,7 +55,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) prepass_kernel(const DemodArgs
         const uint32_t pid = pid0 + g;
         const bool active = pid < a.n_packets;
         const cf* pkt = a.iq + (size_t)(active ? pid : 0) * a.packet_stride;
-        const uint32_t count = active ? (a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet) : 0;
+        const uint32_t count = active ? (a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet) : 0;
         const uint32_t total = count / step;
 
         // -- 1. max-abs scan (legacy path only) : LoRaDemod.cpp:61-68 --
@@ -218,7 +219,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) symbols_kernel(const DemodArgs
         bool active = item < n_items;
         const uint32_t pid = active ? (uint32_t)(item / a.data_symbols_max) : 0;
         const uint32_t k = active ? (uint32_t)(item % a.data_symbols_max) : 0;   // output slot
-        const uint32_t count = a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet;
+        const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
         const uint32_t total = count / step;
         const bool have_sync = total >= 2;
         const uint32_t s = have_sync ? k + 2 : k;
@@ -286,13 +287,13 @@ static cudaError_t launch_demod_sf(const DemodArgs& a, int sm_count, cudaStream_
                                    bool symbols, unsigned* launches)
 {
     using S = Smem<SF>;
-    static bool attr_done[64] = { false };      // per device: function attributes live in the context
+    static std::atomic<bool> attr_done[64];           // per device; the attribute set is idempotent, so a racing first launch is harmless
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!attr_done[dev & 63]) {
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
         cudaFuncSetAttribute(prepass_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
         cudaFuncSetAttribute(symbols_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
-        attr_done[dev & 63] = true;
+        attr_done[dev & 63].store(true, std::memory_order_release);
     }
     const unsigned max_ctas = (unsigned)sm_count * 64u;
     if (prepass && a.n_packets) {

@@ -55,23 +55,6 @@ struct DemodArgs {
     int32_t* status;
 };
 
-struct FusedArgs {                // demod_fused.cu
-    DemodArgs d;
-    uint32_t n_groups;            // packet groups (EP packets each)
-    uint32_t awin;                // scan windows per packet (ceil(samples_per_packet / N)); 0 = no scan (high-level mode)
-    uint32_t ua, ub;              // SCAN / DATA units per group
-    uint32_t scan_units;          // n_groups * ua, dealt to the scan pipelines
-    uint32_t block_units;         // 1 + ub: compute block b = [EST of group b][DATA units of group b - data_lag]
-    uint32_t total_units;         // (n_groups + data_lag) * block_units, dealt to the compute pipelines
-    uint32_t data_lag;            // groups between a group's EST unit and its DATA units
-    uint32_t scan_lead;           // scans of group g wait until EST of group g - scan_lead is published
-    uint32_t scan_ctas;           // the LAST scan_ctas CTAs of the grid are scan pipelines (0 in high-level mode)
-    unsigned long long block_magic, awin_magic, ua_magic;   // floor(2^64 / x) + 1 dividers
-    uint32_t* pmax;               // [n_packets] max(|re|,|im|) as float bits, zeroed before launch
-    uint32_t* acount;             // [n_packets] scanned windows, zeroed
-    uint32_t* eready;             // [n_packets] 1 once PacketState is published, zeroed
-};
-
 __device__ __forceinline__ cf ldg_cf(const cf* p)
 {
     const float2 t = __ldg(reinterpret_cast<const float2*>(p));

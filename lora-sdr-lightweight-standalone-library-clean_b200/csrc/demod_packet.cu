@@ -22,6 +22,7 @@
 // 66 symbols, far below the 126 MB L2), so phases B and C are served by L2 and HBM sees every IQ
 // byte once; packets too long for that (SF12: 4.3 MB each) read HBM twice, which the issue-bound
 // phase C still hides.
+#include <atomic>
 #include "stream_common.cuh"
 #include <cstdlib>
 #include "internal.h"
@@ -90,7 +91,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_packet_
 
     for (uint32_t pid = blockIdx.x; pid < a.n_packets; pid += gridDim.x) {
         const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
-        const uint32_t count = a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet;
+        const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
         const uint32_t total = count / (uint32_t)N;
         const bool have_sync = total >= 2;
 
@@ -349,7 +350,7 @@ struct WarpCfg {
 template <int DT>
 __device__ __forceinline__ void pipe_sync()
 {
-    if (DT <= 32) pipe_sync<DT>(); else group_sync<DT>();
+    if (DT <= 32) __syncwarp(); else group_sync<DT>();
 }
 
 template <int DT>
@@ -434,7 +435,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) demod_warp_ke
 
     for (uint32_t pid = blockIdx.x * C::DOMS + dom; pid < a.n_packets; pid += n_warps) {
         const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
-        const uint32_t count = a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet;
+        const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
         const uint32_t total = count / (uint32_t)N;
         const bool have_sync = total >= 2;
         const bool legacy = a.mode == MODE_LEGACY;
@@ -671,13 +672,13 @@ static cudaError_t launch_warp_sf(const DemodArgs& a, int sm_count, cudaStream_t
 {
     using C = WarpCfg<SF>;
     const bool extra = a.down != nullptr || a.window != nullptr;
-    static bool attr_done[64] = { false };
+    static std::atomic<bool> attr_done[64];           // per device; the attribute set is idempotent, so a racing first launch is harmless
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!attr_done[dev & 63]) {
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
         cudaFuncSetAttribute(demod_warp_kernel<SF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
         cudaFuncSetAttribute(demod_warp_kernel<SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
-        attr_done[dev & 63] = true;
+        attr_done[dev & 63].store(true, std::memory_order_release);
     }
     const unsigned max_ctas = (unsigned)sm_count * STREAM_CTAS_PER_SM;    // persistent grid: every CTA resident
     const unsigned need = (a.n_packets + C::DOMS - 1) / C::DOMS;
@@ -692,13 +693,13 @@ static cudaError_t launch_packet_sf(const DemodArgs& a, int sm_count, cudaStream
 {
     using C = PacketCfg<SF>;
     const bool extra = a.down != nullptr || a.window != nullptr;
-    static bool attr_done[64] = { false };
+    static std::atomic<bool> attr_done[64];           // per device; the attribute set is idempotent, so a racing first launch is harmless
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!attr_done[dev & 63]) {
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
         cudaFuncSetAttribute(demod_packet_kernel<SF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
         cudaFuncSetAttribute(demod_packet_kernel<SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
-        attr_done[dev & 63] = true;
+        attr_done[dev & 63].store(true, std::memory_order_release);
     }
     const unsigned max_ctas = (unsigned)sm_count * STREAM_CTAS_PER_SM;    // persistent grid: every CTA resident
     const unsigned grid = a.n_packets < max_ctas ? a.n_packets : max_ctas;

@@ -17,6 +17,7 @@
 //     |X|^2 to the first-max bin and store one uint16;
 //   * IQ is read from HBM exactly once by this kernel (the packet prepass reads it once more;
 //     see DESIGN.md for the fused schedule).
+#include <atomic>
 #include "stream_common.cuh"
 #include "internal.h"
 
@@ -60,7 +61,7 @@ __global__ void __launch_bounds__(CTA_THREADS, STREAM_CTAS_PER_SM) symbols_strea
         if (item < n_items) {
             const uint32_t pid = (uint32_t)__umul64hi((unsigned long long)item, a.dsm_magic);   // item / dsm
             const uint32_t k = item - pid * a.data_symbols_max;
-            const uint32_t count = a.sample_counts ? a.sample_counts[pid] : a.samples_per_packet;
+            const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
             const uint32_t total = count / (uint32_t)N;
             const uint32_t s = total >= 2 ? k + 2 : k;
             const int4 sraw = __ldg(reinterpret_cast<const int4*>(a.state + pid));
@@ -128,13 +129,13 @@ static cudaError_t launch_stream_sf(const DemodArgs& a, int sm_count, cudaStream
 {
     using C = StreamCfg<SF>;
     const bool extra = a.down != nullptr || a.window != nullptr;
-    static bool attr_done[64] = { false };
+    static std::atomic<bool> attr_done[64];           // per device; the attribute set is idempotent, so a racing first launch is harmless
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!attr_done[dev & 63]) {
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
         cudaFuncSetAttribute(symbols_stream_kernel<SF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
         cudaFuncSetAttribute(symbols_stream_kernel<SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
-        attr_done[dev & 63] = true;
+        attr_done[dev & 63].store(true, std::memory_order_release);
     }
     const unsigned long long items = (unsigned long long)a.n_packets * a.data_symbols_max;
     const unsigned long long units = (items + C::GD - 1) / C::GD;

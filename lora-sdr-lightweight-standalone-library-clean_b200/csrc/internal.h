@@ -9,7 +9,6 @@ namespace lk {
 
 using fx::cf;
 struct DemodArgs;
-struct FusedArgs;
 
 struct DetectArgs {
     const cf* windows; uint32_t n_windows;
@@ -36,10 +35,6 @@ cudaError_t launch_symbols_stream(int sf, const DemodArgs& a, int sm_count, cuda
 // demod_packet.cu: one CTA per packet, scan -> estimator -> symbols in one launch (SF 7..12, osr == 1)
 bool packet_supported(int sf, const DemodArgs& a);
 cudaError_t launch_demod_packet(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
-// demod_fused.cu: scan + estimator + sync + data symbols in one persistent launch (SF 7..12, osr == 1)
-bool fused_plan(int sf, const DemodArgs& a, uint32_t lookahead_bytes, FusedArgs* f);
-cudaError_t launch_demod_fused(int sf, const FusedArgs& f, int sm_count, cudaStream_t stream);
-
 // tables.cu
 cudaError_t launch_build_tables(int sf, cf* tw, cf* ct, int ct_size, float* hann, cudaStream_t stream);
 cudaError_t launch_build_chirp(int sf, int osr, float bw_scale, cf* out /* N*osr */, cudaStream_t stream);

@@ -1,5 +1,5 @@
-// stream_common.cuh -- pieces shared by the streaming kernels (demod_stream.cu: data symbols
-// only; demod_fused.cu: max-abs scan + estimator + sync + data symbols in one launch).
+// stream_common.cuh -- pieces shared by the streaming kernels (demod_stream.cu: data symbols only;
+// demod_packet.cu / demod_cert.cu: max-abs + estimator + sync + data symbols in one launch).
 #pragma once
 #include "demod_device.cuh"
 #include "stream_ptx.cuh"
@@ -158,17 +158,25 @@ __device__ __forceinline__ bool window_is_odd(const cf* src)      // starts 8 by
     return ((reinterpret_cast<uintptr_t>(src) >> 3) & 1u) != 0;
 }
 
-// Leader-side fetch of one full window into its stage slot: aligned bulk copy plus, for an odd
-// window, the one sample the aligned copy misses (readers then start at win + 1).  The caller
+// Leader-side fetch of one full window into its stage slot.  An even window (16-byte aligned) is one bulk copy
+// to win[0..N).  An odd window (8 bytes past a 16-byte boundary) lands one entry later -- sample i at win[i + 1],
+// readers start at win + 1: its aligned interior (samples 1..N-2) is the bulk copy, the two end samples are plain
+// loads, so nothing outside the window is ever read (a batch may start 8 bytes into an allocation).  The caller
 // publishes its descriptor BEFORE calling: the mbarrier arrive releases it to the waiters.
 template <int N>
 __device__ __forceinline__ void fetch_window(cf* win, const cf* src, uint64_t* bar)
 {
     const uintptr_t addr = reinterpret_cast<uintptr_t>(src);
     const unsigned odd = (unsigned)(addr >> 3) & 1u;
-    if (odd) win[N] = ldg_cf(src + (N - 1));
-    ptx::mbar_arrive_expect_tx(bar, (unsigned)(N * sizeof(cf)));
-    ptx::bulk_g2s(win, reinterpret_cast<const void*>(addr - 8u * odd), (unsigned)(N * sizeof(cf)), bar);
+    if (odd) {
+        win[1] = ldg_cf(src);
+        win[N] = ldg_cf(src + (N - 1));
+        ptx::mbar_arrive_expect_tx(bar, (unsigned)((N - 2) * sizeof(cf)));
+        ptx::bulk_g2s(win + 2, src + 1, (unsigned)((N - 2) * sizeof(cf)), bar);
+    } else {
+        ptx::mbar_arrive_expect_tx(bar, (unsigned)(N * sizeof(cf)));
+        ptx::bulk_g2s(win, src, (unsigned)(N * sizeof(cf)), bar);
+    }
 }
 
 } // namespace lk

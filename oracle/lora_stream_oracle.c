@@ -34,7 +34,7 @@ void oracle_stream_tables(unsigned sf, ocplx* up, ocplx* down, ocplx* fine /* N 
         const double re = cos(acc), im = sin(acc);
         up[i].re = (float)re;   up[i].im = (float)(-im);
         down[i].re = (float)re; down[i].im = (float)im;
-        phase += (float)((2 * M_PI) / (double)N);
+        phase = (float)((double)phase + (2 * M_PI) / (double)N);   /* float += double: summed in double, rounded once */
     }
     acc = 0.0;
     phase = (float)(2.0 * M_PI / (double)(N * FINE_STEPS));

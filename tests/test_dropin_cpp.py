@@ -16,15 +16,15 @@ PKG = os.path.join(ROOT, "lora-sdr-lightweight-standalone-library-clean_b200")
 REFTESTS = os.path.join(ROOT, "oracle", "_ref", "reftests")
 
 
-def build_dropin():
+def build_dropin(name="phy_dropin_test"):
     out_dir = os.path.join(HERE, "cpp", "build")
     os.makedirs(out_dir, exist_ok=True)
-    exe = os.path.join(out_dir, "phy_dropin_test")
+    exe = os.path.join(out_dir, name)
     if not os.path.exists(os.path.join(PKG, "liblora_phy_cuda.so")):
         import lora_phy_b200
         lora_phy_b200.build()
     subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"),
-                    os.path.join(HERE, "cpp", "phy_dropin_test.cpp"), "-o", exe, "-L", PKG, "-llora_phy_cuda",
+                    os.path.join(HERE, "cpp", name + ".cpp"), "-o", exe, "-L", PKG, "-llora_phy_cuda", "-pthread",
                     "-Wl,-rpath," + PKG], check=True)
     return exe
 
@@ -40,6 +40,18 @@ def test_dropin_header_argument_contract():
 @pytest.mark.gpu
 def test_dropin_header_end_to_end():
     r = subprocess.run([build_dropin(), "gpu"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_threads_program_compiles():
+    build_dropin("phy_threads_test")
+
+
+@pytest.mark.gpu
+def test_two_threads_one_workspace_each():
+    """the drop-in wrapper funnels every workspace through one context; its entry points must serialise
+    (context mutex held from staging to copy-out) so reference-style one-workspace-per-thread use stays correct."""
+    r = subprocess.run([build_dropin("phy_threads_test")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
 
 

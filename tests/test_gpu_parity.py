@@ -317,31 +317,6 @@ def test_full_chain_batch_properties(phy, lp):
     assert bool((out["sync"] == 0x12).all()) and bool((out["status"] == 2 * L).all())
 
 
-# ---- experimental fused persistent launch (demod_fused.cu): same results, one cooperative kernel -----------
-@pytest.mark.gpu
-@pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
-@pytest.mark.parametrize("kind", ["clean", "noise"])
-def test_fused_launch_parity(phy, lp, oracle, sf, kind):
-    rng = np.random.default_rng(sf * 31 + len(kind))
-    n_pkt = 7 if sf <= 9 else 3
-    iq = make_packets(oracle, rng, sf, 1, n_pkt, 9 if sf <= 10 else 5, kind=kind)
-    check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_FUSED)
-    check_legacy(phy, lp, oracle, iq, sf, 1, 1, flags=lp.F_FUSED)
-
-
-@pytest.mark.gpu
-def test_fused_launch_ragged_and_scratch(phy, lp, oracle):
-    rng = np.random.default_rng(11)
-    sf = 7
-    iq = make_packets(oracle, rng, sf, 1, 5, 6)
-    iq[1] *= np.float32(2.0)
-    iq[2] *= np.float32(0.25)
-    check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_FUSED | lp.F_NO_SCRATCH)
-    check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_FUSED)
-    counts = np.array([0, 128, 256, 128 * 5 + 17, 128 * 8], dtype=np.uint32)
-    check_legacy(phy, lp, oracle, iq, sf, 1, 0, flags=lp.F_FUSED, counts=counts)
-
-
 @pytest.mark.gpu
 @pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
 @pytest.mark.parametrize("kind", ["clean", "noisy", "noise", "loud"])
