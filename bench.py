@@ -162,7 +162,7 @@ def run_ours(args, wl):
     two = args.two_kernel
     cfg_pre = lp.make_cfg(sf, flags=lp.F_ONLY_PREPASS)
     cfg_sym = lp.make_cfg(sf, flags=lp.F_ONLY_SYMBOLS)
-    cfg_one = cfg
+    cfg_one = lp.make_cfg(sf, flags=lp.F_EXACT) if args.exact else cfg
 
     def step(ev=None):
         if not two:                            # default: ONE launch per batch (demod_packet_kernel, one CTA per packet)
@@ -193,6 +193,7 @@ def run_ours(args, wl):
         dist.barrier()
     torch.cuda.synchronize()
     launches0 = phy.launch_count()
+    cert0 = phy.cert_stats()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t0.record()
@@ -203,6 +204,7 @@ def run_ours(args, wl):
     if world > 1:
         dist.barrier()
     launches = phy.launch_count() - launches0
+    cert1 = phy.cert_stats()
     sampler.stop_flag = True
     sampler.join(timeout=3)
     ms_total = t0.elapsed_time(t1)
@@ -248,7 +250,7 @@ def run_ours(args, wl):
         kname = "symbols_stream_kernel<SF%d>" % sf
         sym_bytes = P * (nsym - 2) * b_sym              # symbols kernel: data symbols of every packet, once
     else:
-        kname = ("demod_warp_kernel<SF%d>" if sf <= 11 else "demod_packet_kernel<SF%d>") % sf   # demod_packet.cu: pipeline per packet SF7-11
+        kname = (("demod_warp_kernel<SF%d>" if sf <= 11 else "demod_packet_kernel<SF%d>") if args.exact else "demod_cert_kernel<SF%d>") % sf
         sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
@@ -270,6 +272,8 @@ def run_ours(args, wl):
         "e2e": {"value": e2e_value, "unit": "symbols/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "packets_per_step": Pe},
         "gpu_launches": launches,
+        "certified": {"windows": cert1[0] - cert0[0], "fallback_windows": cert1[1] - cert0[1],
+                      "second_estimates": cert1[2] - cert0[2], "rewalked_packets": cert1[3] - cert0[3]},
         "clocks": sampler.summary(),
     }
     if not args.no_cpu and world == 1:
@@ -298,6 +302,7 @@ def main():
     ap.add_argument("--e2e-packets", type=int, default=1 << 15)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--two-kernel", action="store_true", help="A/B: time the older prepass + symbols kernel pair")
+    ap.add_argument("--exact", action="store_true", help="A/B: F_EXACT, every window through the operation-for-operation replay (round-1 kernel)")
     args = ap.parse_args()
     # stdout carries the ONE JSON line and nothing else: libraries that write to fd 1 (NCCL prints its version
     # banner there under some NCCL_DEBUG settings) are sent to stderr for the rest of the run

@@ -84,6 +84,11 @@ uint64_t lora_phy_cuda_launch_count(const lora_phy_cuda_ctx* ctx);
 /* Make every later call of this context enqueue on `stream` (cudaStream_t as void*). */
 int  lora_phy_cuda_set_stream(lora_phy_cuda_ctx* ctx, void* stream);
 int  lora_phy_cuda_synchronize(lora_phy_cuda_ctx* ctx);
+/* Counters of the default (margin-certified) demodulator, accumulated since the context was created; waits for the
+ * context's stream.  out[0] windows walked by the throughput transform, out[1] windows replayed through the exact
+ * chain because the proof failed (or the packet was exact throughout), out[2] packets whose two estimator symbols
+ * were redone after a max-abs misprediction, out[3] packets walked a second time.  No reference counterpart.       */
+int  lora_phy_cuda_cert_stats(lora_phy_cuda_ctx* ctx, uint64_t out[4]);
 
 /* ---- demodulator: K1 + K2a ------------------------------------------------------------- */
 /* replaces lora_demodulate (LoRaDemod.cpp:50-197) -- and, with F_DECHIRP, demodulate

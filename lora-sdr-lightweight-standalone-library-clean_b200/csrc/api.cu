@@ -72,6 +72,7 @@ struct lora_phy_cuda_ctx {
     std::mutex mc_mu;
     size_t mc_scratch_bytes = (size_t)4 << 30;           // IQ bytes per Monte-Carlo chunk (LORA_PHY_MC_SCRATCH_MB)
     DevBuf lfsr;                                         // dewhitening byte table of the coding chain (chain.cu)
+    unsigned long long* cert_stats = nullptr;           // [4] counters of the certified demodulator (demod_cert.cu)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
     std::recursive_mutex mu;                            // held for a whole entry point (staging buffers, scratch, err)
@@ -168,6 +169,11 @@ int lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device)
         }
         ctx->launches += 2;
     }
+    if (cudaMalloc(&ctx->cert_stats, 4 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemsetAsync(ctx->cert_stats, 0, 4 * sizeof(unsigned long long), ctx->stream) != cudaSuccess) {
+        lora_phy_cuda_destroy(ctx);
+        return -EIO;
+    }
     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { lora_phy_cuda_destroy(ctx); return -EIO; }
     *out = ctx;
     return 0;
@@ -183,6 +189,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
         if (ctx->tab[sf].ct) cudaFree(ctx->tab[sf].ct);
         if (ctx->tab[sf].hann) cudaFree(ctx->tab[sf].hann);
     }
+    if (ctx->cert_stats) cudaFree(ctx->cert_stats);
     for (auto& kv : ctx->chirps) cudaFree(kv.second);
     for (int sf = 0; sf <= 12; ++sf) if (ctx->sync_tab[sf]) cudaFree(ctx->sync_tab[sf]);
     ctx->lfsr.release();
@@ -207,6 +214,15 @@ int lora_phy_cuda_set_stream(lora_phy_cuda_ctx* ctx, void* stream)
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     ctx->stream = static_cast<cudaStream_t>(stream);
     ctx->own_stream = false;
+    return 0;
+}
+
+int lora_phy_cuda_cert_stats(lora_phy_cuda_ctx* ctx, uint64_t out[4])
+{
+    if (!ctx || !out) return -EINVAL;
+    CtxGuard g(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(out, ctx->cert_stats, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return 0;
 }
 
@@ -279,8 +295,19 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.cfo = d_cfo;
     a.time_offset = d_to;
     a.status = d_status;
+    a.force_exact = 0;
+    a.cert_stats = ctx->cert_stats;
     unsigned launches = 0;
-    // default: one launch, one CTA per packet (demod_packet.cu)
+    // default: one launch, one pipeline per packet, margin-certified throughput transform with exact replay of the
+    // windows that cannot be proven (demod_cert.cu)
+    if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&
+        lk::cert_supported((int)cfg->sf, a)) {
+        cudaError_t e = lk::launch_demod_cert((int)cfg->sf, a, ctx->sm_count, ctx->stream);
+        ++ctx->launches;
+        if (e != cudaSuccess) return fail(ctx, -EIO, "certified demodulator launch", e);
+        return 0;
+    }
+    // F_EXACT (A/B): one launch, every window through the operation-for-operation replay (demod_packet.cu)
     if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL)) &&
         lk::packet_supported((int)cfg->sf, a)) {
         cudaError_t e = lk::launch_demod_packet((int)cfg->sf, a, ctx->sm_count, ctx->stream);

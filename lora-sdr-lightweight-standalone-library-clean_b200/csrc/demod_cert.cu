@@ -1,0 +1,655 @@
+// demod_cert.cu -- the default demodulator (SF 7..12, osr == 1): lora_demodulate (LoRaDemod.cpp:50-197) and
+// demodulate (phy.cpp:182-243) for a batch, ONE launch, one pipeline per packet, HBM read once -- with the
+// per-window work done by a THROUGHPUT transform whose argmax is PROVEN to be the reference's, window by window.
+//
+// Why: replaying the reference's float operations (glibc-exact sincosf per sample in FP64, un-fused kissfft
+// butterflies; demod_packet.cu) costs 92 thread-instructions per sample and leaves the kernel issue-bound at a
+// third of the HBM rate.  north_star asks for bit-exact SYMBOLS (and 1e-4 on |X|^2), not bit-exact spectra, so:
+//
+//   E units (exact)   symbols 0,1 raw through the exact-order FFT: cfo, time_offset, rate, t_off bit for bit
+//                     (LoRaDemod.cpp:80-139) -- unchanged from demod_packet.cu.
+//   C units (fast)    every symbol: samples * f_c, where f_c = scale * [down_i] * exp(j*rate*i) * [w_i] is computed ONCE
+//                     PER PACKET per thread (|X|^2 does not depend on the per-symbol start phase, LoRaDemod.cpp:152-159),
+//                     then ff::Plan (fft_fast.cuh: FMA radix-16/8/4, 1-2 exchanges), |Y|^2, and the top bin.
+//   certification     the reference's computed spectrum X^ and ours Y both approximate the same ideal DFT Z; with
+//                     S = sqrt(N * sum|u_i|^2) >= sum|u_i| every bin obeys | |X^_k| - |Y_k| | <= K*S, K = u*(C0 +
+//                     |start| + 2|rate|N), u = 2^-24 (DESIGN.md derives C0 from kissfft's stage count, its float twiddle
+//                     table, the libm bounds and our own rounding).  The window is accepted iff the top |Y|^2 beats the
+//                     second by more than that margin (tier 1: the top bin holds > 3/4 of N*E, by Parseval nothing else
+//                     can come near; tier 2: the true second maximum).  Then X^ has the same strict, unique maximum.
+//   fallback          windows that fail -- ties, noise-only windows with close bins, NaN / Inf / denormal input -- are
+//                     replayed through the exact chain of demod_packet.cu at the end of the packet, same launch.
+//                     Symbols, sync word, status, cfo and time_offset are therefore bit-exact BY CONSTRUCTION.
+//
+// The 1/max normalisation (LoRaDemod.cpp:61-78) no longer forces a second walk: the certified decision is invariant to
+// the (positive, finite) scale, so a packet is walked once with the previous packet's max folded into f_c while the
+// true max is tracked; on a mismatch only the two E units are redone with the true scale, and the walk stands if the
+// new rate / t_off agree with the ones it used to within the tolerance its margin already budgeted.
+#include <atomic>
+#include <cstdlib>
+#include "stream_common.cuh"
+#include "fft_fast.cuh"
+#include "internal.h"
+
+namespace lk {
+
+#ifndef CERT_CTAS_PER_SM
+#define CERT_CTAS_PER_SM 2
+#endif
+
+constexpr int CERT_CAP = 512;                 // symbols per packet the fallback bitmap / symbol staging cover (255-byte payload
+                                              // in the shipped framing); longer packets take the exact chain throughout
+// ---- certification constants (units of u = 2^-24), DESIGN.md section 5 ---------------------------------------------
+constexpr float CERT_U = 5.9604644775390625e-08f;
+constexpr float CERT_C0 = 384.0f;             // 160 reference (6 radix-4 stages x 19u + input chain + libm + |X|^2) + 96 ours
+                                              // + 16 key quantisation + 64 rate tolerance + slack
+constexpr float CERT_RATE_TOL = 64.0f * CERT_U;   // |rate' - rate| * N a finished walk tolerates (budgeted in C0)
+
+struct EstSymC { int idx; float fi; float phase; };
+
+struct CertShared {                           // one per pipeline
+    EstSymC est[2];
+    int sw[2];
+    float bc_rate; int bc_toff;
+    unsigned fb[CERT_CAP / 32];               // windows that failed certification
+    uint16_t sym[CERT_CAP];                   // data symbols of the packet, flushed in one coalesced run
+};
+
+template <int SF, int CTA>
+struct CertCfg {
+    using F = ff::Plan<SF>;
+    static constexpr int T = F::T, N = F::N;
+    static constexpr int DT = T <= 32 ? 32 : T;            // threads of one pipeline (one packet at a time)
+    static constexpr int DOMS = CTA / DT;
+    static constexpr int GD = DT / T;                      // windows per pipeline step
+    static constexpr int PITCH = F::pitch();
+    static constexpr int SLOT = GD * PITCH;
+    static constexpr size_t stage_bytes = (size_t)DOMS * SLOT * sizeof(cf);
+    static constexpr size_t red_bytes = 256;               // Peak[8] | RedCell[8] | float[8] (multi-warp windows only)
+    static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + 256;
+    // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
+    static constexpr int fit = (int)(((size_t)227 * 1024 / CERT_CTAS_PER_SM - 1024 - fixed_bytes) / stage_bytes);
+    static constexpr int STAGES = fit >= 3 ? 3 : 2;
+    static constexpr size_t slot_bytes = stage_bytes * STAGES;
+    static constexpr size_t bar_off = slot_bytes;
+    static constexpr size_t red_off = bar_off + (size_t)DOMS * STAGES * sizeof(uint64_t);
+    static constexpr size_t tw1_off = (red_off + red_bytes + 15) & ~(size_t)15;
+    static constexpr size_t ws_off = (tw1_off + (size_t)F::TW1_SIZE * sizeof(cf) + 15) & ~(size_t)15;
+    static constexpr size_t bytes = ws_off + (size_t)DOMS * sizeof(CertShared);
+};
+
+struct RedCell { unsigned key; float e; unsigned m1; unsigned m2; };      // per warp, multi-warp windows only
+
+__device__ __forceinline__ unsigned umax3(unsigned a, unsigned b, unsigned c) { return max(max(a, b), c); }
+
+template <int DT>
+__device__ __forceinline__ void csync()
+{
+    if (DT <= 32) __syncwarp(); else group_sync<DT>();
+}
+
+template <int DT>
+__device__ __forceinline__ bool cany(bool p)
+{
+    if (DT <= 32) return __any_sync(0xffffffffu, p) != 0;
+    if (DT >= CTA_THREADS) return __syncthreads_or(p) != 0;
+    int r;
+    asm volatile("{\n\t.reg .pred q, r;\n\tsetp.ne.b32 q, %1, 0;\n\tbarrier.cta.red.or.pred r, %2, %3, q;\n\tselp.b32 %0, 1, 0, r;\n\t}"
+                 : "=r"(r) : "r"((int)p), "r"(1 + (int)threadIdx.x / DT), "n"(DT) : "memory");
+    return r != 0;
+}
+
+// max over [0, count) of max(|re|,|im|) with the reference's comparison chain (LoRaDemod.cpp:61-68), one pipeline
+template <int DT>
+__device__ __forceinline__ float cert_scan_max(const cf* __restrict__ pkt, uint32_t count, int lane, float* redf)
+{
+    float m = 0.0f;
+    uint32_t head = 0;
+    if ((reinterpret_cast<uintptr_t>(pkt) & 15) != 0 && count > 0) {
+        if (lane == 0) { const cf x = ldg_cf(pkt); const float r = fabsf(x.x), i = fabsf(x.y); m = fmaxf(m, (r < i) ? i : r); }
+        head = 1;
+    }
+    const float4* p4 = reinterpret_cast<const float4*>(pkt + head);
+    const uint32_t pairs = (count - head) >> 1;
+#pragma unroll 8
+    for (uint32_t j = lane; j < pairs; j += DT) {
+        const float4 q = __ldg(p4 + j);
+        const float r0 = fabsf(q.x), i0 = fabsf(q.y), r1 = fabsf(q.z), i1 = fabsf(q.w);
+        m = fmaxf(m, (r0 < i0) ? i0 : r0);
+        m = fmaxf(m, (r1 < i1) ? i1 : r1);
+    }
+    if (((count - head) & 1) && lane == 0) {
+        const cf x = ldg_cf(pkt + count - 1);
+        const float r = fabsf(x.x), i = fabsf(x.y);
+        m = fmaxf(m, (r < i) ? i : r);
+    }
+    if (DT <= 32) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+        return m;
+    }
+    return group_max<DT>(m, redf);
+}
+
+template <int SF, bool EXTRA, int CTA>
+__global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const DemodArgs a)
+{
+    using C = CertCfg<SF, CTA>;
+    using P = fx::Plan<SF>;
+    using F = ff::Plan<SF>;
+    constexpr int T = C::T, N = C::N, GD = C::GD, DT = C::DT, STAGES = C::STAGES, NP = F::NP;
+    static_assert(T <= 32 || CTA == CTA_THREADS, "multi-warp windows use the CTA_THREADS-wide helpers");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int dom = threadIdx.x / DT;
+    const int lane = threadIdx.x % DT;
+    const int gq = lane / T, tid = lane % T;
+
+    cf* slots = reinterpret_cast<cf*>(smem_raw) + (size_t)dom * STAGES * C::SLOT;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::bar_off) + dom * STAGES;
+    Peak* red = reinterpret_cast<Peak*>(smem_raw + C::red_off);                   // [8] exact units (group_peak)
+    RedCell* redc = reinterpret_cast<RedCell*>(smem_raw + C::red_off + 64);       // [8] fast units, multi-warp windows
+    float* redf = reinterpret_cast<float*>(smem_raw + C::red_off + 192);          // [8] group_max
+    cf* tw1 = reinterpret_cast<cf*>(smem_raw + C::tw1_off);
+    CertShared& ws = reinterpret_cast<CertShared*>(smem_raw + C::ws_off)[dom];
+
+    // ---- start-up: barriers, twiddles, address bases ------------------------------------------------------------
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) ptx::mbar_init(&full[s], GD);
+        ptx::fence_mbar_init();
+    }
+    if (NP == 3) {
+        constexpr int LO1 = F::lo(1), M1 = 1 << (F::lo(1) + F::width(1));
+        for (int j = threadIdx.x; j < F::TW1_SIZE; j += CTA) {
+            const int k = j >> LO1, ir = j & ((1 << LO1) - 1);
+            double sn, cs;
+            sincospi(-2.0 * (double)((k * ir) & (M1 - 1)) / (double)M1, &sn, &cs);
+            tw1[j] = fx::mk((float)cs, (float)sn);
+        }
+    }
+    cf tw0[16];                                    // W_N^{tid * k}: correctly rounded, kept in registers
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        double sn, cs;
+        sincospi(-2.0 * (double)F::tw0_exp(tid, k) / (double)N, &sn, &cs);
+        tw0[k] = fx::mk((float)cs, (float)sn);
+    }
+    const int wr0 = F::wr_base(0, tid), rd0 = F::rd_base(0, tid);
+    const int wr1 = NP == 3 ? F::wr_base(1, tid) : 0, rd1 = NP == 3 ? F::rd_base(1, tid) : 0;
+    const int ir1 = NP == 3 ? F::i_rest(1, tid) : 0;
+    const int bin0 = F::bin_base(tid);
+    __syncthreads();
+
+    int stage = 0;
+    unsigned phase_bits = 0;
+    const uint32_t n_pipes = gridDim.x * C::DOMS;
+    float pred_max = 0.0f;                         // max-abs of the last packet this pipeline saw
+    unsigned st_windows = 0, st_fallback = 0, st_est2 = 0, st_rewalk = 0;      // per-thread statistics, summed at the end
+
+    for (uint32_t pid = blockIdx.x * C::DOMS + dom; pid < a.n_packets; pid += n_pipes) {
+        const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
+        const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
+        const uint32_t total = count / (uint32_t)N;
+        const bool have_sync = total >= 2;
+        const bool legacy = a.mode == MODE_LEGACY;
+        const uint32_t n_units = (total + GD - 1) / GD;
+        const uint32_t n_data = have_sync ? total - 2 : total;
+        uint16_t* out_sym = a.symbols + (size_t)pid * a.symbol_stride;
+
+        int flags = 0, status = 0;
+        if (!legacy) {                                     // phy.cpp:190-194
+            if (count % (uint32_t)N != 0) { flags |= PS_SKIP; status = -22; }
+            else if (total < 2) { flags |= PS_SKIP; status = -34; }
+        }
+        float cfo = 0.0f, toff = 0.0f;
+        bool have_metrics = false;
+        bool all_exact = total > (uint32_t)CERT_CAP || a.force_exact != 0;
+        if (lane < CERT_CAP / 32) ws.fb[lane] = 0u;
+        if (lane == 0) { ws.sw[0] = 0; ws.sw[1] = 0; }
+
+        // which max-abs to walk with (LoRaDemod.cpp:61-78): the previous packet's, verified against the samples the walk
+        // streams anyway; a packet that may have to be refused (no scratch) or is exact throughout is scanned first
+        float use_max = pred_max;
+        bool known = !legacy;
+        if (legacy && (a.no_scratch || all_exact || !(pred_max < 3.0e38f))) {       // (a non-finite prediction is never walked with)
+            use_max = cert_scan_max<DT>(pkt, count, lane, redf);
+            known = true;
+            pred_max = use_max;
+        }
+
+        float rate = 0.0f, scale = 1.0f, rate_walk = 0.0f;
+        int t_off = 0, t_off_walk = 0;
+        bool walked = false;
+        const bool odd_pkt = window_is_odd(pkt);
+
+#pragma unroll 1
+        for (int attempt = 0; attempt < 3 && !(flags & PS_SKIP); ++attempt) {
+            scale = 1.0f;
+            flags &= ~PS_NORM;
+            if (legacy && use_max > 1.0f) {
+                if (a.no_scratch) { flags |= PS_SKIP; status = -34; have_metrics = false; break; }   // LoRaDemod.cpp:70-72
+                flags |= PS_NORM;
+                scale = __fdiv_rn(1.0f, use_max);
+            }
+            const bool norm = (flags & PS_NORM) != 0;
+            const uint32_t n_est = total < 2 ? total : 2u;
+
+            // ---- E units (exact), LoRaDemod.cpp:80-124 / phy.cpp:93-134 ---------------------------------------------
+            for (uint32_t s0 = 0; s0 < n_est; s0 += GD) {
+                const uint32_t s = s0 + gq;
+                const bool live = s < n_est;
+                cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
+                if (tid == 0) {
+                    if (live) fetch_window<N>(win, pkt + (size_t)s * N, &full[stage]);
+                    else ptx::mbar_arrive(&full[stage]);
+                }
+                ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+                cf v[P::R];
+                const cf* raw = win + (odd_pkt ? 1 : 0) + tid;          // s * N is even: the window shares the packet's parity
+#pragma unroll
+                for (int c = 0; c < P::R; ++c) {
+                    cf x = fx::mk(0.0f, 0.0f);
+                    if (live) {
+                        x = raw[T * c];
+                        if (norm) x = fx::cscale(x, scale);                                  // LoRaDemod.cpp:75-77
+                        if (EXTRA && a.window) x = fx::cscale(x, __ldg(a.window + tid + T * c));
+                    }
+                    v[c] = x;
+                }
+                fft_inplace<SF, true>(v, tid, a.tw, a.ct, win);
+                const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+                csync<DT>();                                  // last exchange fully read: the slot becomes the spectrum
+#pragma unroll
+                for (int r = 0; r < P::R; ++r) win[P::bin_of_reg(tid, r)] = v[r];
+                csync<DT>();
+                if (tid == 0 && live) {
+                    EstSymC e; e.idx = 0; e.fi = 0.0f; e.phase = 0.0f;
+                    cf best_bin = fx::mk(0.0f, 0.0f);
+                    if (pk.val > 0.0f) {                       // candidate kept iff its power beats -1e30 dB: max > 0
+                        const float fundamental = __fsqrt_rn(pk.val);
+                        const cf l = win[pk.idx > 0 ? pk.idx - 1 : N - 1];
+                        const cf r = win[pk.idx < N - 1 ? pk.idx + 1 : 0];
+                        const float left = gm::hypotf_g(l.x, l.y), right = gm::hypotf_g(r.x, r.y);
+                        const double demon = (2.0 * (double)fundamental) - (double)right - (double)left;
+                        e.fi = (demon == 0.0) ? 0.0f : (float)(0.5 * (double)fx::fsub(right, left) / demon);
+                        e.idx = pk.idx;
+                        best_bin = win[pk.idx];
+                    }
+                    e.phase = gm::atan2f_g(best_bin.y, best_bin.x);
+                    ws.est[s] = e;
+                }
+                ptx::fence_proxy_async();
+                csync<DT>();
+                stage = stage + 1 == STAGES ? 0 : stage + 1;
+            }
+
+            // ---- combine (lane 0), LoRaDemod.cpp:126-139 -----------------------------------------------------------
+            if (lane == 0) {
+                const float PI_F = 3.14159265358979323846f;
+                float sum_index = 0.0f, phase_diff = 0.0f, prev_phase = 0.0f;
+                for (uint32_t s = 0; s < n_est; ++s) {
+                    const EstSymC e = ws.est[s];
+                    sum_index = fx::fadd(sum_index, fx::fadd((float)e.idx, e.fi));
+                    if (s > 0) {
+                        float dd = fx::fsub(e.phase, prev_phase);
+                        while (dd > PI_F) dd = fx::fsub(dd, 2.0f * PI_F);
+                        while (dd < -PI_F) dd = fx::fadd(dd, 2.0f * PI_F);
+                        phase_diff = fx::fadd(phase_diff, dd);
+                    }
+                    prev_phase = e.phase;
+                }
+                const float avg_index = __fdiv_rn(sum_index, (float)n_est);
+                const float cfo_coarse = __fdiv_rn(avg_index, (float)N);
+                float cfo_fine = 0.0f;
+                if (n_est > 1)
+                    cfo_fine = __fdiv_rn(__fdiv_rn(phase_diff, (float)(n_est - 1)), fx::fmul(2.0f * PI_F, (float)N));
+                cfo = fx::fadd(cfo_coarse, cfo_fine);
+                const float frac = fx::fsub(avg_index, floorf(fx::fadd(avg_index, 0.5f)));
+                const float avg_t = __fdiv_rn(0.0f, (float)n_est);
+                toff = fx::fsub(avg_t, fx::fmul(frac, (float)N));
+                t_off = (int)roundf(toff);
+                rate = __fdiv_rn(fx::fmul(-2.0f * PI_F, cfo), (float)N);
+            }
+            if (DT <= 32) {
+                rate = __shfl_sync(0xffffffffu, rate, 0);
+                t_off = __shfl_sync(0xffffffffu, t_off, 0);
+            } else {
+                if (lane == 0) { ws.bc_rate = rate; ws.bc_toff = t_off; }
+                csync<DT>();
+                rate = ws.bc_rate; t_off = ws.bc_toff;
+            }
+            have_metrics = true;
+
+            if (!(use_max < 3.0e38f)) all_exact = true;        // 1/inf == 0 wipes the packet: nothing is scale-invariant there
+            if (all_exact) break;
+            if (walked) {
+                // second estimate after a max-abs misprediction: the finished walk is scale-invariant, so it stands when
+                // it used the same window bases and a rate within the tolerance its certification margin budgeted
+                if (lane == 0) ++st_est2;
+                const bool same = t_off == t_off_walk && fabsf(fx::fsub(rate, rate_walk)) * (float)N <= CERT_RATE_TOL;
+                if (same) break;
+                if (lane == 0) ++st_rewalk;
+                if (lane < CERT_CAP / 32) ws.fb[lane] = 0u;
+                csync<DT>();
+            }
+
+            // ---- per-packet factors f_c = scale * [down_i] * exp(j*rate*i) * [w_i], i = tid + T*c ------------------
+            cf f[16];
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                const int i = tid + T * c;
+                float ph = fx::fmul(rate, (float)i);
+                ph = __fmaf_rn(-6.283185307179586f, rintf(ph * 0.15915494309189535f), ph);      // into [-pi, pi]
+                float sn, cs;
+                __sincosf(ph, &sn, &cs);
+                cf r = fx::mk(cs * scale, sn * scale);
+                if (EXTRA && a.down) r = ff::fcmul(ldg_cf(a.down + i), r);
+                if (EXTRA && a.window) { const float w = __ldg(a.window + i); r = fx::mk(r.x * w, r.y * w); }
+                f[c] = r;
+            }
+            // certification constant: K = u * (C0 + |start|max + 2|rate|N); accepted iff d^2 > 16 K^2 (N E) q1
+            const float start_max = fabsf(rate) * ((float)total * (float)N + fabsf((float)t_off)) * 1.01f;
+            const float Kc = CERT_U * (CERT_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
+            const float c2 = 16.32f * Kc * Kc * (float)N;
+            const float tier1 = (Kc < 0.0078125f) ? 0.75f * (float)N : __int_as_float(0x7f800000);
+
+            // ---- C units: the walk ------------------------------------------------------------------------------
+            float m = 0.0f;
+            bool suspicious = false;
+            auto prefetch = [&](uint32_t u, int stg) {
+                if (tid != 0) return;
+                const uint32_t s = u * GD + gq;
+                if (s < total) {
+                    const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);       // LoRaDemod.cpp:143-150
+                    fetch_window<N>(slots + (size_t)stg * C::SLOT + (size_t)gq * C::PITCH, pkt + base, &full[stg]);
+                } else {
+                    ptx::mbar_arrive(&full[stg]);
+                }
+            };
+            {
+                int stg = stage;
+                for (uint32_t u = 0; u < (uint32_t)(STAGES - 1) && u < n_units; ++u) { prefetch(u, stg); stg = stg + 1 == STAGES ? 0 : stg + 1; }
+            }
+            for (uint32_t u = 0; u < n_units; ++u) {
+                if (u + (STAGES - 1) < n_units) {
+                    int stg = stage + (STAGES - 1);
+                    if (stg >= STAGES) stg -= STAGES;
+                    prefetch(u + (STAGES - 1), stg);
+                }
+                const uint32_t s = u * GD + gq;
+                const bool active = s < total;
+                const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);
+                const bool odd = odd_pkt != ((base & 1u) != 0);
+                ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+                cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
+                const cf* raw = win + (odd ? 1 : 0) + tid;
+
+                cf v[16];
+                float mw = 0.0f, e0 = 0.0f, e1 = 0.0f;
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    const cf r = raw[T * c];
+                    mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                     // running max-abs (LoRaDemod.cpp:61-68)
+                    const cf y = ff::fcmul(r, f[c]);
+                    if (c & 1) e1 = __fmaf_rn(y.x, y.x, __fmaf_rn(y.y, y.y, e1));
+                    else e0 = __fmaf_rn(y.x, y.x, __fmaf_rn(y.y, y.y, e0));
+                    v[c] = y;
+                }
+                if (active) m = fmaxf(m, mw);
+                float en = e0 + e1;
+
+                // pass 0 in registers, twiddle, exchange(s) in the window's own slot
+                ff::dft16(v);
+#pragma unroll
+                for (int k = 1; k < 16; ++k) v[k] = ff::fcmul(v[k], tw0[k]);
+                group_sync<T>();                               // every thread of the window has its raw samples
+#pragma unroll
+                for (int e = 0; e < 16; ++e) win[wr0 + F::wr_off(0, e)] = v[e];
+                group_sync<T>();
+#pragma unroll
+                for (int e = 0; e < 16; ++e) v[e] = win[rd0 + F::rd_off(0, e)];
+                F::butterflies(1, v);
+                if (NP == 3) {
+                    constexpr int W1 = F::width(1), LO1 = F::lo(1);
+#pragma unroll
+                    for (int k = 1; k < (1 << W1); ++k) {
+                        const cf t = tw1[(k << LO1) + ir1];
+#pragma unroll
+                        for (int e = k; e < 16; e += (1 << W1)) v[e] = ff::fcmul(v[e], t);
+                    }
+                    group_sync<T>();
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) win[wr1 + F::wr_off(1, e)] = v[e];
+                    group_sync<T>();
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) v[e] = win[rd1 + F::rd_off(1, e)];
+                    F::butterflies(2, v);
+                }
+
+                // |Y|^2 keyed with the register index in the low four mantissa bits; top key of the window
+                unsigned key[16];
+#pragma unroll
+                for (int e = 0; e < 16; ++e) key[e] = (__float_as_uint(ff::fnorm(v[e])) & ~15u) | (unsigned)e;
+                unsigned kloc = 0u;
+#pragma unroll
+                for (int e = 0; e < 16; e += 2) kloc = umax3(kloc, key[e], key[e + 1]);
+                unsigned kmax = kloc;
+                constexpr int W = T < 32 ? T : 32;
+#pragma unroll
+                for (int off = W / 2; off > 0; off >>= 1) {
+                    kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, off));
+                    en += __shfl_xor_sync(0xffffffffu, en, off);
+                }
+                if (T > 32) {
+                    const int warp = threadIdx.x >> 5;
+                    if ((threadIdx.x & 31) == 0) { redc[warp].key = kmax; redc[warp].e = en; }
+                    group_sync<T>();
+                    const int w0 = (threadIdx.x / T) * (T / 32);
+                    kmax = redc[w0].key; en = redc[w0].e;
+#pragma unroll
+                    for (int k = 1; k < T / 32; ++k) { kmax = max(kmax, redc[w0 + k].key); en += redc[w0 + k].e; }
+                }
+                const float q1 = __uint_as_float(kmax & ~15u);
+                // tier 1: the top bin holds more than 3/4 of N*E (Parseval: every other bin is below half its modulus)
+                bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
+                if (cany<DT>(!cert && active)) {
+                    // tier 2: the true second maximum of the window.  Keys inside a thread are distinct (register index in
+                    // the low bits); (m1, m2) pairs merge as sorted pairs, so a key held by two threads shows up as m2 == m1
+                    unsigned m1 = kloc, m2 = 0u;
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) m2 = max(m2, key[e] == kloc ? 0u : key[e]);
+#pragma unroll
+                    for (int off = W / 2; off > 0; off >>= 1) {
+                        const unsigned o1 = __shfl_xor_sync(0xffffffffu, m1, off), o2 = __shfl_xor_sync(0xffffffffu, m2, off);
+                        m2 = umax3(min(m1, o1), m2, o2);
+                        m1 = max(m1, o1);
+                    }
+                    if (T > 32) {
+                        const int warp = threadIdx.x >> 5;
+                        if ((threadIdx.x & 31) == 0) { redc[warp].m1 = m1; redc[warp].m2 = m2; }
+                        group_sync<T>();
+                        const int w0 = (threadIdx.x / T) * (T / 32);
+                        m1 = redc[w0].m1; m2 = redc[w0].m2;
+#pragma unroll
+                        for (int k = 1; k < T / 32; ++k) {
+                            const unsigned o1 = redc[w0 + k].m1, o2 = redc[w0 + k].m2;
+                            m2 = umax3(min(m1, o1), m2, o2);
+                            m1 = max(m1, o1);
+                        }
+                    }
+                    const float q2 = __uint_as_float(m2 & ~15u);
+                    const float d = q1 - q2 * 1.000004f;
+                    const bool t2 = (d > 0.0f) && (d * d > c2 * en * q1) && (en < 1.0e30f) && (q1 >= 8.3e-25f) && (q1 < 1.0e30f);
+                    cert = cert || t2;
+                }
+                if (!(en < 1.0e30f) && active) suspicious = true;          // NaN / Inf in the window: invisible to the tracked max
+                if (active) {
+                    if (tid == 0) { ++st_windows; if (!cert) ++st_fallback; }
+                    if (kloc == kmax) {                                    // the lane that holds the top bin
+                        if (cert) {
+                            const unsigned e = kmax & 15u;
+                            const int idx = bin0 + ((e & 1u) ? F::bin_off(1) : 0) + ((e & 2u) ? F::bin_off(2) : 0) +
+                                            ((e & 4u) ? F::bin_off(4) : 0) + ((e & 8u) ? F::bin_off(8) : 0);
+                            if (have_sync && s < 2) ws.sw[s] = idx;
+                            else ws.sym[have_sync ? s - 2 : s] = (uint16_t)idx;
+                        } else {
+                            atomicOr(&ws.fb[s >> 5], 1u << (s & 31));
+                        }
+                    }
+                }
+                ptx::fence_proxy_async();
+                csync<DT>();
+                stage = stage + 1 == STAGES ? 0 : stage + 1;
+            }
+            walked = true;
+            rate_walk = rate;
+            t_off_walk = t_off;
+
+            // ---- verify the trusted max against the samples actually walked -----------------------------------------
+            if (known) break;
+            if (t_off != 0 || count != total * (uint32_t)N || cany<DT>(suspicious)) {
+                m = cert_scan_max<DT>(pkt, count, lane, redf);       // shifted windows / partial tail / NaN: the reference's own scan
+            } else if (DT <= 32) {
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+            } else {
+                m = group_max<DT>(m, redf);
+            }
+            const bool ok = (m > 1.0f) ? (m == use_max) : !(use_max > 1.0f);
+            pred_max = m;
+            known = true;
+            if (ok) break;
+            use_max = m;                                   // redo the two E units with the packet's own max
+        }
+
+        // ---- exact units: windows that failed certification (or the whole packet), LoRaDemod.cpp:142-176 ------------
+        csync<DT>();
+        const bool run = !(flags & PS_SKIP);
+        bool any_fb = all_exact;
+        if (!all_exact) {
+            bool mine = false;
+            if (lane < CERT_CAP / 32) mine = ws.fb[lane] != 0u;
+            any_fb = cany<DT>(mine);
+        }
+        if (run && any_fb) {
+            uint32_t cursor = 0;
+            while (true) {
+                int mine_s = -1;
+                bool found = false;
+#pragma unroll 1
+                for (int g = 0; g < GD; ++g) {
+                    uint32_t s = cursor;
+                    if (!all_exact) {
+                        while (s < total && s < (uint32_t)CERT_CAP) {
+                            const unsigned w = ws.fb[s >> 5] >> (s & 31);
+                            if (w) { s += __ffs(w) - 1; break; }
+                            s = (s | 31u) + 1u;
+                        }
+                        if (s >= (uint32_t)CERT_CAP) s = total;
+                    }
+                    if (s < total) { if (g == gq) mine_s = (int)s; cursor = s + 1; found = true; }
+                    else cursor = total;
+                }
+                if (!found) break;
+                const bool active = mine_s >= 0;
+                const uint32_t s = active ? (uint32_t)mine_s : 0u;
+                const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);
+                cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
+                if (tid == 0) {
+                    if (active) fetch_window<N>(win, pkt + base, &full[stage]);
+                    else ptx::mbar_arrive(&full[stage]);
+                }
+                const bool odd = odd_pkt != ((base & 1u) != 0);
+                const float start = start_phase(rate, s, (uint32_t)N, t_off);           // LoRaDemod.cpp:152-153
+                const bool slow = phases_need_slow_path(start, fx::fadd(start, fx::fmul(rate, (float)(N - 1))));
+                ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+                cf v[P::R];
+                chain_window<SF, EXTRA, false>(v, win + (odd ? 1 : 0) + tid, tid, scale, rate, start, slow, a.down, a.window);
+                fft_inplace<SF, false>(v, tid, a.tw, a.ct, win);
+                const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+                if (tid == 0 && active) {
+                    const uint32_t ds = have_sync ? s - 2 : s;
+                    if (have_sync && s < 2) ws.sw[s] = pk.idx;
+                    else if (ds < (uint32_t)CERT_CAP) ws.sym[ds] = (uint16_t)pk.idx;
+                    else out_sym[ds] = (uint16_t)pk.idx;                 // beyond the staging buffer (exact-throughout packets only)
+                    if (all_exact) { ++st_windows; ++st_fallback; }
+                }
+                ptx::fence_proxy_async();
+                csync<DT>();
+                stage = stage + 1 == STAGES ? 0 : stage + 1;
+            }
+        }
+
+        // ---- bookkeeping: LoRaDemod.cpp:166-196; the packet's symbols leave in one coalesced run ----------------------
+        csync<DT>();
+        if (run) {
+            const uint32_t n_stage = n_data < (uint32_t)CERT_CAP ? n_data : (uint32_t)CERT_CAP;
+            for (uint32_t i = lane; i < n_stage; i += DT) out_sym[i] = ws.sym[i];
+        }
+        if (lane == 0) {
+            if (run) status = have_sync ? (int)(total - 2) : (int)total;
+            if (have_metrics) {
+                if (a.cfo) a.cfo[pid] = cfo;
+                if (a.time_offset) a.time_offset[pid] = toff;
+            }
+            if (a.sync) {
+                const unsigned shift = SF > 4 ? SF - 4 : 0;
+                a.sync[pid] = (run && have_sync) ? (uint8_t)((((ws.sw[0] >> shift) & 0xf) << 4) | ((ws.sw[1] >> shift) & 0xf)) : 0;
+            }
+            if (a.status) a.status[pid] = status;
+        }
+        csync<DT>();
+    }
+
+    if (a.cert_stats) {
+        if (st_windows) atomicAdd(a.cert_stats + 0, (unsigned long long)st_windows);
+        if (st_fallback) atomicAdd(a.cert_stats + 1, (unsigned long long)st_fallback);
+        if (lane == 0 && st_est2) atomicAdd(a.cert_stats + 2, (unsigned long long)st_est2);
+        if (lane == 0 && st_rewalk) atomicAdd(a.cert_stats + 3, (unsigned long long)st_rewalk);
+    }
+}
+
+template <int SF, int CTA>
+static cudaError_t launch_cert_sf(const DemodArgs& a, int sm_count, cudaStream_t stream)
+{
+    using C = CertCfg<SF, CTA>;
+    const bool extra = a.down != nullptr || a.window != nullptr;
+    static std::atomic<bool> attr_done[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
+        cudaFuncSetAttribute(demod_cert_kernel<SF, false, CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        cudaFuncSetAttribute(demod_cert_kernel<SF, true, CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        attr_done[dev & 63].store(true, std::memory_order_release);
+    }
+    const unsigned max_ctas = (unsigned)sm_count * CERT_CTAS_PER_SM;      // persistent grid: every CTA resident
+    const unsigned need = (a.n_packets + C::DOMS - 1) / C::DOMS;
+    const unsigned grid = need < max_ctas ? need : max_ctas;
+    if (extra) demod_cert_kernel<SF, true, CTA><<<grid, CTA, C::bytes, stream>>>(a);
+    else demod_cert_kernel<SF, false, CTA><<<grid, CTA, C::bytes, stream>>>(a);
+    return cudaGetLastError();
+}
+
+bool cert_supported(int sf, const DemodArgs& a)
+{
+    return sf >= 7 && sf <= 12 && a.osr == 1 && (a.mode == MODE_LEGACY || a.mode == MODE_HIGHLEVEL) &&
+           (unsigned long long)a.samples_per_packet < 0xf0000000ull;
+}
+
+cudaError_t launch_demod_cert(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream)
+{
+    switch (sf) {
+    case 7: return launch_cert_sf<7, CTA_THREADS>(a, sm_count, stream);
+    case 8: return launch_cert_sf<8, CTA_THREADS>(a, sm_count, stream);
+    case 9: return launch_cert_sf<9, CTA_THREADS>(a, sm_count, stream);
+    case 10: return launch_cert_sf<10, CTA_THREADS>(a, sm_count, stream);
+    case 11: return launch_cert_sf<11, CTA_THREADS>(a, sm_count, stream);
+    case 12: return launch_cert_sf<12, CTA_THREADS>(a, sm_count, stream);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+} // namespace lk

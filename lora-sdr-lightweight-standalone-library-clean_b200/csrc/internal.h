@@ -35,6 +35,11 @@ cudaError_t launch_symbols_stream(int sf, const DemodArgs& a, int sm_count, cuda
 // demod_packet.cu: one CTA per packet, scan -> estimator -> symbols in one launch (SF 7..12, osr == 1)
 bool packet_supported(int sf, const DemodArgs& a);
 cudaError_t launch_demod_packet(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
+// demod_cert.cu: the default -- pipeline per packet, throughput FFT with a per-window proof that its argmax is the
+// reference's, exact replay of the windows that cannot be proven (SF 7..12, osr == 1)
+bool cert_supported(int sf, const DemodArgs& a);
+cudaError_t launch_demod_cert(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
+
 // tables.cu
 cudaError_t launch_build_tables(int sf, cf* tw, cf* ct, int ct_size, float* hann, cudaStream_t stream);
 cudaError_t launch_build_chirp(int sf, int osr, float bw_scale, cf* out /* N*osr */, cudaStream_t stream);

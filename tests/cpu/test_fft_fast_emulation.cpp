@@ -1,0 +1,160 @@
+// Thread-loop emulation of csrc/fft_fast.cuh on the CPU (SF 7..12): the fast transform of the certified
+// demodulator path against a double-precision DFT, plus the properties the kernel relies on and that no
+// GPU tool checks on this pool (compute-sanitizer is closed, profiles/r02_sanitizer_unavailable.txt):
+//   * every exchange writes each address of a window exactly once and reads only addresses it wrote
+//     (no two threads race on an entry; reads and writes are separated by the kernel's barriers);
+//   * the addresses stay inside the window's slot (Plan::pitch());
+//   * every 64-bit access phase (16 consecutive lanes of the CTA) is bank-conflict free, for the raw
+//     sample loads, the exchange stores and loads, and the middle-pass twiddle loads;
+//   * the output bin map is a permutation of 0..N-1.
+// Prints one JSON line per SF; exit 0 iff everything holds and the relative spectrum error is < 2e-6.
+#include <algorithm>
+#include <cmath>
+#include <complex>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include "fft_fast.cuh"
+
+using ff::cf;
+
+static int worst_conflict(const std::vector<long>& addr /* per CTA lane, complex entries, -1 = idle */)
+{
+    int worst = 1;
+    for (size_t base = 0; base < addr.size(); base += 16) {
+        std::vector<long> seen[16];
+        for (size_t l = base; l < std::min(addr.size(), base + 16); ++l) {
+            if (addr[l] < 0) continue;
+            auto& v = seen[addr[l] & 15];
+            if (std::find(v.begin(), v.end(), addr[l]) == v.end()) v.push_back(addr[l]);
+        }
+        for (auto& v : seen) worst = std::max(worst, (int)v.size());
+    }
+    return worst;
+}
+
+template <int SF>
+static bool run(unsigned seed)
+{
+    using P = ff::Plan<SF>;
+    constexpr int N = P::N, T = P::T, NP = P::NP;
+    constexpr int CTA = 256;
+    constexpr int G = CTA / T;                       // windows a CTA's threads hold at once
+    const int PITCH = P::pitch();
+    const double PI = 3.14159265358979323846;
+    bool ok = true;
+    int worst = 1;
+
+    srand(seed);
+    std::vector<std::complex<double>> x((size_t)G * N);
+    for (auto& z : x) z = { (double)rand() / RAND_MAX - 0.5, (double)rand() / RAND_MAX - 0.5 };
+    // one window is a pure tone: the case the kernel cares about
+    for (int i = 0; i < N; ++i) x[i] = std::polar(1.0, 2 * PI * 37.0 * i / N);
+
+    std::vector<cf> regs((size_t)G * T * 16);
+    auto V = [&](int g, int tid) -> cf(&)[16] { return *reinterpret_cast<cf(*)[16]>(&regs[((size_t)g * T + tid) * 16]); };
+    std::vector<cf> sm((size_t)G * PITCH);
+    std::vector<int> written((size_t)G * PITCH);
+
+    // raw loads: lane reads win[tid + T*c]
+    for (int c = 0; c < 16; ++c) {
+        std::vector<long> addr(CTA, -1);
+        for (int g = 0; g < G; ++g)
+            for (int tid = 0; tid < T; ++tid) addr[g * T + tid] = (long)g * PITCH + tid + T * c;
+        worst = std::max(worst, worst_conflict(addr));
+    }
+    for (int g = 0; g < G; ++g)
+        for (int tid = 0; tid < T; ++tid) {
+            cf(&v)[16] = V(g, tid);
+            for (int c = 0; c < 16; ++c) v[c] = ff::mk((float)x[(size_t)g * N + tid + T * c].real(), (float)x[(size_t)g * N + tid + T * c].imag());
+        }
+
+    for (int p = 0; p < NP; ++p) {
+        for (int g = 0; g < G; ++g)
+            for (int tid = 0; tid < T; ++tid) {
+                cf(&v)[16] = V(g, tid);
+                P::butterflies(p, v);
+                if (p + 1 < NP) {                                   // twiddle W_M^{k * i_rest}
+                    const int w = P::width(p), M = 1 << (P::lo(p) + w), ir = P::i_rest(p, tid);
+                    for (int e = 0; e < 16; ++e) {
+                        const int k = e & ((1 << w) - 1);
+                        const double ang = -2 * PI * (double)((k * ir) % M) / M;
+                        v[e] = ff::fcmul(v[e], ff::mk((float)cos(ang), (float)sin(ang)));
+                    }
+                    if (p == 0 && ir != tid) ok = false;
+                }
+            }
+        if (p + 1 == NP) break;
+        // twiddle-table loads of the middle pass: entry (k << lo) | i_rest
+        if (p == 1)
+            for (int k = 0; k < (1 << P::width(1)); ++k) {
+                std::vector<long> addr(CTA, -1);
+                for (int g = 0; g < G; ++g)
+                    for (int tid = 0; tid < T; ++tid) addr[g * T + tid] = (k << P::lo(1)) | P::i_rest(1, tid);
+                worst = std::max(worst, worst_conflict(addr));
+            }
+        std::fill(written.begin(), written.end(), 0);
+        for (int e = 0; e < 16; ++e) {
+            std::vector<long> addr(CTA, -1);
+            for (int g = 0; g < G; ++g)
+                for (int tid = 0; tid < T; ++tid) {
+                    const int a = P::wr_base(p, tid) + P::wr_off(p, e);
+                    if (a < 0 || a >= PITCH) { ok = false; continue; }
+                    addr[g * T + tid] = (long)g * PITCH + a;
+                    if (written[(size_t)g * PITCH + a]++) ok = false;           // two writers for one entry
+                    sm[(size_t)g * PITCH + a] = V(g, tid)[e];
+                }
+            worst = std::max(worst, worst_conflict(addr));
+        }
+        for (int e = 0; e < 16; ++e) {
+            std::vector<long> addr(CTA, -1);
+            for (int g = 0; g < G; ++g)
+                for (int tid = 0; tid < T; ++tid) {
+                    const int a = P::rd_base(p, tid) + P::rd_off(p, e);
+                    if (a < 0 || a >= PITCH || written[(size_t)g * PITCH + a] != 1) { ok = false; continue; }
+                    written[(size_t)g * PITCH + a] = 2;                          // read exactly once as well
+                    addr[g * T + tid] = (long)g * PITCH + a;
+                    V(g, tid)[e] = sm[(size_t)g * PITCH + a];
+                }
+            worst = std::max(worst, worst_conflict(addr));
+        }
+    }
+
+    // spectrum against the double DFT, bin map a permutation
+    double max_rel = 0.0;
+    for (int g = 0; g < G; ++g) {
+        std::vector<std::complex<double>> X(N);
+        std::vector<int> hit(N, 0);
+        double peak = 0.0;
+        for (int k = 0; k < N; ++k) {
+            std::complex<double> acc = 0;
+            for (int i = 0; i < N; ++i) acc += x[(size_t)g * N + i] * std::polar(1.0, -2 * PI * (double)((long)i * k % N) / N);
+            X[k] = acc;
+            peak = std::max(peak, std::abs(acc));
+        }
+        for (int tid = 0; tid < T; ++tid)
+            for (int e = 0; e < 16; ++e) {
+                const int bin = P::bin_base(tid) + P::bin_off(e);
+                if (bin < 0 || bin >= N || hit[bin]++) { ok = false; continue; }
+                const cf y = V(g, tid)[e];
+                max_rel = std::max(max_rel, std::abs(std::complex<double>(y.x, y.y) - X[bin]) / peak);
+            }
+    }
+    if (max_rel > 2e-6) ok = false;
+    if (worst != 1) ok = false;
+    std::printf("{\"sf\": %d, \"passes\": %d, \"pitch\": %d, \"max_rel_err\": %.3g, \"worst_bank_conflict\": %d, \"match\": %s}\n", SF, NP,
+                PITCH, max_rel, worst, ok ? "true" : "false");
+    return ok;
+}
+
+int main()
+{
+    bool ok = true;
+    ok &= run<7>(1);
+    ok &= run<8>(2);
+    ok &= run<9>(3);
+    ok &= run<10>(4);
+    ok &= run<11>(5);
+    ok &= run<12>(6);
+    return ok ? 0 : 1;
+}
