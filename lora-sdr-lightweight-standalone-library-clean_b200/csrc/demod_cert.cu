@@ -82,6 +82,15 @@ struct RedCell { unsigned key; float e; unsigned m1; unsigned m2; };      // per
 
 __device__ __forceinline__ unsigned umax3(unsigned a, unsigned b, unsigned c) { return max(max(a, b), c); }
 
+// |Y|^2 with the register index in the low four mantissa bits: (bits & mask) | e as ONE three-input logic op (the mask
+// lives in a register: two immediates would cost two instructions)
+__device__ __forceinline__ unsigned key_of(float q, unsigned mask, int e)
+{
+    unsigned k;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(__float_as_uint(q)), "r"(mask), "r"((unsigned)e));
+    return k;
+}
+
 template <int DT>
 __device__ __forceinline__ void csync()
 {
@@ -178,6 +187,8 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
     const int wr1 = NP == 3 ? F::wr_base(1, tid) : 0, rd1 = NP == 3 ? F::rd_base(1, tid) : 0;
     const int ir1 = NP == 3 ? F::i_rest(1, tid) : 0;
     const int bin0 = F::bin_base(tid);
+    unsigned keymask = 0xfffffff0u;
+    asm volatile("" : "+r"(keymask));              // opaque to constant folding: stays in a register for key_of
     __syncthreads();
 
     int stage = 0;
@@ -355,50 +366,59 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             const float tier1 = (Kc < 0.0078125f) ? 0.75f * (float)N : __int_as_float(0x7f800000);
 
             // ---- C units: the walk ------------------------------------------------------------------------------
+            // Loop bookkeeping is kept out of the issue slots: the window slot, its mbarrier and the prefetch target are
+            // cursors advanced by a constant (shared-memory addresses as 32-bit integers), a packet without time shift
+            // (t_off == 0, the usual case) has window s at sample s*N with the packet's own parity.
             float m = 0.0f;
             bool suspicious = false;
-            auto prefetch = [&](uint32_t u, int stg) {
-                if (tid != 0) return;
-                const uint32_t s = u * GD + gq;
-                if (s < total) {
-                    const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);       // LoRaDemod.cpp:143-150
-                    fetch_window<N>(slots + (size_t)stg * C::SLOT + (size_t)gq * C::PITCH, pkt + base, &full[stg]);
+            const bool regular = t_off == 0;
+            const uint32_t slot0 = ptx::smem_u32(slots) + (uint32_t)(gq * C::PITCH * sizeof(cf));
+            const uint32_t bar0 = ptx::smem_u32(full);
+            constexpr uint32_t SLOT_B = C::SLOT * sizeof(cf);
+            auto prefetch = [&](uint32_t sp, int stg) {              // leader only: window of symbol sp into stage stg
+                if (sp < total) {
+                    const uint32_t base = regular ? sp * (uint32_t)N : shifted_base(sp, (uint32_t)N, t_off, count);   // LoRaDemod.cpp:143-150
+                    fetch_window_sa<N>(slot0 + (uint32_t)stg * SLOT_B, pkt + base, bar0 + 8u * (uint32_t)stg);
                 } else {
-                    ptx::mbar_arrive(&full[stg]);
+                    ptx::mbar_arrive_sa(bar0 + 8u * (uint32_t)stg);
                 }
             };
-            {
+            if (tid == 0) {
                 int stg = stage;
-                for (uint32_t u = 0; u < (uint32_t)(STAGES - 1) && u < n_units; ++u) { prefetch(u, stg); stg = stg + 1 == STAGES ? 0 : stg + 1; }
+                for (uint32_t u = 0; u < (uint32_t)(STAGES - 1) && u < n_units; ++u) { prefetch(u * GD + gq, stg); stg = stg + 1 == STAGES ? 0 : stg + 1; }
             }
-            for (uint32_t u = 0; u < n_units; ++u) {
-                if (u + (STAGES - 1) < n_units) {
+            uint32_t s = (uint32_t)gq;                              // this window's symbol; += GD per step
+            int roff = (odd_pkt ? 1 : 0) + tid;
+#pragma unroll 1
+            for (uint32_t u = 0; u < n_units; ++u, s += GD) {
+                if (tid == 0) {
                     int stg = stage + (STAGES - 1);
                     if (stg >= STAGES) stg -= STAGES;
-                    prefetch(u + (STAGES - 1), stg);
+                    if (u + (STAGES - 1) < n_units) prefetch(s + (STAGES - 1) * GD, stg);
                 }
-                const uint32_t s = u * GD + gq;
                 const bool active = s < total;
-                const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);
-                const bool odd = odd_pkt != ((base & 1u) != 0);
-                ptx::mbar_wait(&full[stage], (phase_bits >> stage) & 1u);
+                if (!regular) {
+                    const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);
+                    roff = ((odd_pkt != ((base & 1u) != 0)) ? 1 : 0) + tid;
+                }
+                ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
                 phase_bits ^= 1u << stage;
                 cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
-                const cf* raw = win + (odd ? 1 : 0) + tid;
+                const cf* raw = win + roff;
 
                 cf v[16];
-                float mw = 0.0f, e0 = 0.0f, e1 = 0.0f;
+                float mw = 0.0f;
+                cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);                   // (sum re^2, sum im^2), two chains
 #pragma unroll
                 for (int c = 0; c < 16; ++c) {
                     const cf r = raw[T * c];
                     mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                     // running max-abs (LoRaDemod.cpp:61-68)
                     const cf y = ff::fcmul(r, f[c]);
-                    if (c & 1) e1 = __fmaf_rn(y.x, y.x, __fmaf_rn(y.y, y.y, e1));
-                    else e0 = __fmaf_rn(y.x, y.x, __fmaf_rn(y.y, y.y, e0));
+                    if (c & 1) e1 = ff::sqacc(e1, y); else e0 = ff::sqacc(e0, y);      // one packed FMA per sample
                     v[c] = y;
                 }
                 if (active) m = fmaxf(m, mw);
-                float en = e0 + e1;
+                float en = (e0.x + e0.y) + (e1.x + e1.y);
 
                 // pass 0 in registers, twiddle, exchange(s) in the window's own slot
                 ff::dft16(v);
@@ -431,7 +451,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 // |Y|^2 keyed with the register index in the low four mantissa bits; top key of the window
                 unsigned key[16];
 #pragma unroll
-                for (int e = 0; e < 16; ++e) key[e] = (__float_as_uint(ff::fnorm(v[e])) & ~15u) | (unsigned)e;
+                for (int e = 0; e < 16; ++e) key[e] = key_of(ff::fnorm(v[e]), keymask, e);
                 unsigned kloc = 0u;
 #pragma unroll
                 for (int e = 0; e < 16; e += 2) kloc = umax3(kloc, key[e], key[e + 1]);
@@ -484,9 +504,8 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     const bool t2 = (d > 0.0f) && (d * d > c2 * en * q1) && (en < 1.0e30f) && (q1 >= 8.3e-25f) && (q1 < 1.0e30f);
                     cert = cert || t2;
                 }
-                if (!(en < 1.0e30f) && active) suspicious = true;          // NaN / Inf in the window: invisible to the tracked max
                 if (active) {
-                    if (tid == 0) { ++st_windows; if (!cert) ++st_fallback; }
+                    if (!cert && !(en < 1.0e30f)) suspicious = true;       // NaN / Inf in the window: invisible to the tracked max
                     if (kloc == kmax) {                                    // the lane that holds the top bin
                         if (cert) {
                             const unsigned e = kmax & 15u;
@@ -503,6 +522,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 csync<DT>();
                 stage = stage + 1 == STAGES ? 0 : stage + 1;
             }
+            if (lane == 0) st_windows += total;
             walked = true;
             rate_walk = rate;
             t_off_walk = t_off;
@@ -575,7 +595,8 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     if (have_sync && s < 2) ws.sw[s] = pk.idx;
                     else if (ds < (uint32_t)CERT_CAP) ws.sym[ds] = (uint16_t)pk.idx;
                     else out_sym[ds] = (uint16_t)pk.idx;                 // beyond the staging buffer (exact-throughout packets only)
-                    if (all_exact) { ++st_windows; ++st_fallback; }
+                    if (all_exact) ++st_windows;
+                    ++st_fallback;
                 }
                 ptx::fence_proxy_async();
                 csync<DT>();

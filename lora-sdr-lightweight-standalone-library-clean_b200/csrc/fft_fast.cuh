@@ -50,10 +50,33 @@ FF_HD float fma_(float a, float b, float c)
 #endif
 }
 FF_HD float mul_(float a, float b) { return fx::fmul(a, b); }
-FF_HD cf add(cf a, cf b) { return mk(fx::fadd(a.x, b.x), fx::fadd(a.y, b.y)); }
-FF_HD cf sub(cf a, cf b) { return mk(fx::fsub(a.x, b.x), fx::fsub(a.y, b.y)); }
+// complex add / sub: ONE packed f32x2 instruction on the device (the (re, im) pair sits in an aligned register pair)
+FF_HD cf add(cf a, cf b) { return fx::cadd(a, b); }
+FF_HD cf sub(cf a, cf b) { return fx::csub(a, b); }
+// a + s * b and a - s * b with a real scalar s: one packed fused multiply-add each
+FF_HD cf axpy(cf a, float s, cf b)
+{
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(fx::pk2(mk(s, s))), "l"(fx::pk2(b)), "l"(fx::pk2(a)));
+    return fx::upk2(r);
+#else
+    return mk(fma_(s, b.x, a.x), fma_(s, b.y, a.y));
+#endif
+}
 // a * w: two multiplies, two fused multiply-adds
 FF_HD cf fcmul(cf a, cf w) { return mk(fma_(-a.y, w.y, mul_(a.x, w.x)), fma_(a.y, w.x, mul_(a.x, w.y))); }
+// acc + (z.re^2, z.im^2): one packed fused multiply-add
+FF_HD cf sqacc(cf acc, cf z)
+{
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(r) : "l"(fx::pk2(z)), "l"(fx::pk2(acc)));
+    return fx::upk2(r);
+#else
+    return mk(fma_(z.x, z.x, acc.x), fma_(z.y, z.y, acc.y));
+#endif
+}
 // |z|^2
 FF_HD float fnorm(cf a) { return fma_(a.y, a.y, mul_(a.x, a.x)); }
 
@@ -87,8 +110,8 @@ FF_HD void dft8(cf& a0, cf& a1, cf& a2, cf& a3, cf& a4, cf& a5, cf& a6, cf& a7)
     const cf t0 = add(d0, r2), t1 = sub(d0, r2);
     const cf u = add(p1, p3), v = sub(p1, p3);                  // t2 = S u, t3 = S v
     a0 = s0; a2 = s1; a4 = s2; a6 = s3;
-    a1 = mk(fma_(S, u.x, t0.x), fma_(S, u.y, t0.y));            // t0 + t2
-    a5 = mk(fma_(-S, u.x, t0.x), fma_(-S, u.y, t0.y));          // t0 - t2
+    a1 = axpy(t0, S, u);                                        // t0 + t2
+    a5 = axpy(t0, -S, u);                                       // t0 - t2
     a3 = mk(fma_(S, v.y, t1.x), fma_(-S, v.x, t1.y));           // t1 - j t3
     a7 = mk(fma_(-S, v.y, t1.x), fma_(S, v.x, t1.y));           // t1 + j t3
 }

@@ -179,4 +179,22 @@ __device__ __forceinline__ void fetch_window(cf* win, const cf* src, uint64_t* b
     }
 }
 
+// fetch_window on 32-bit shared addresses (window slot, mbarrier)
+template <int N>
+__device__ __forceinline__ void fetch_window_sa(uint32_t win, const cf* src, uint32_t bar)
+{
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(src);
+    const unsigned odd = (unsigned)(addr >> 3) & 1u;
+    if (odd) {
+        const cf a = ldg_cf(src), b = ldg_cf(src + (N - 1));
+        ptx::sts_cf_sa(win + 8u, a.x, a.y);
+        ptx::sts_cf_sa(win + 8u * N, b.x, b.y);
+        ptx::mbar_arrive_expect_tx_sa(bar, (unsigned)((N - 2) * sizeof(cf)));
+        ptx::bulk_g2s_sa(win + 16u, src + 1, (unsigned)((N - 2) * sizeof(cf)), bar);
+    } else {
+        ptx::mbar_arrive_expect_tx_sa(bar, (unsigned)(N * sizeof(cf)));
+        ptx::bulk_g2s_sa(win, src, (unsigned)(N * sizeof(cf)), bar);
+    }
+}
+
 } // namespace lk

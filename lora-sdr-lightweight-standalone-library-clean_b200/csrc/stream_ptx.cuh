@@ -55,6 +55,36 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity)
     while (!mbar_try_wait(bar, parity)) { }
 }
 
+// the same primitives on 32-bit shared-window addresses (no generic -> shared conversion in the caller's loop)
+__device__ __forceinline__ void mbar_arrive_sa(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx_sa(uint32_t bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_sa(uint32_t bar, unsigned parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s_sa(uint32_t dst, const void* src_gmem, unsigned bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void sts_cf_sa(uint32_t dst, float x, float y)
+{
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(dst), "f"(x), "f"(y) : "memory");
+}
+
 // bytes: multiple of 16; dst (shared) and src (global) 16-byte aligned
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, uint64_t* bar)
 {
