@@ -3,8 +3,12 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload sf7..sf12] [--impl reference]
 
-A "step" is one pass of the demodulator (lora_phy_cuda_demodulate_batch: one launch of
-demod_packet_kernel, one CTA per packet: scan -> estimator -> symbols) over one batch of synthetic, clean, pre-dechirped IQ already resident in HBM.
+A "step" is one pass of the demodulator (lora_phy_cuda_demodulate_batch: one launch of demod_cert_kernel, one
+pipeline per packet: exact estimator symbols, margin-certified throughput transform for every window, exact replay of
+the windows that cannot be proven) over one batch of synthetic, clean, pre-dechirped IQ already resident in HBM.
+The default run (cfg 2, one GPU) also measures, in an `also` block of the same JSON line: a batch with per-packet random
+gain, the raw-IQ variant with the on-chip downchirp, F_EXACT, SF8-SF11, the cfg-3 SF12 chunk, the stream detector and
+one AWGN Monte-Carlo cell.
 Workloads (BASELINE.json configs[1] / configs[2]):
   sf7   SF7 BW125k, 32-byte payloads (66 symbols = 8448 samples = 67.6 KB per packet), 1 Mi packets
   sf12  SF12 BW125k, 64-byte payloads (130 symbols = 4.26 MB per packet), 16 Ki packets resident
@@ -124,6 +128,127 @@ def run_reference(args, wl):
     }))
 
 
+def make_batch(phy, lp, torch, sf, L, P, seed, raw=False, gains=False):
+    """P packets of L random bytes: encode -> modulate (-> caller-side dechirp unless raw) on the device, in chunks.
+    gains: every packet scaled by its own random factor in [0.5, 2) -- the max-abs prediction then misses every packet."""
+    dev = phy.device
+    N = 1 << sf
+    nsym = 2 * L + 2
+    spp = nsym * N
+    cfg = lp.make_cfg(sf)
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    iq = torch.empty((P, spp), dtype=torch.complex64, device=dev)
+    chunk = max(1, min(P, (1 << 28) // spp))
+    payload = torch.randint(0, 256, (P, L), dtype=torch.uint8, generator=g)
+    for lo in range(0, P, chunk):
+        hi = min(P, lo + chunk)
+        sym = phy.encode_batch(payload[lo:hi].to(dev))
+        phy.modulate_batch(cfg, sym, iq[lo:hi])
+        if not raw:
+            phy.dechirp_batch(cfg, iq[lo:hi])
+        if gains:
+            gv = (0.5 + 1.5 * torch.rand((hi - lo, 1), generator=g)).to(dev)
+            torch.view_as_real(iq[lo:hi]).mul_(gv.unsqueeze(-1))
+    torch.cuda.synchronize()
+    return iq, payload
+
+
+def time_demod(phy, lp, torch, cfg, iq, out, steps, warmup):
+    """CUDA-event time of `steps` demodulate_batch launches on torch's current stream (the context enqueues there)."""
+    for _ in range(warmup):
+        phy.demodulate_batch(cfg, iq, out=out)
+    torch.cuda.synchronize()
+    c0 = phy.cert_stats()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in evs:
+        a.record()
+        phy.demodulate_batch(cfg, iq, out=out)
+        b.record()
+    torch.cuda.synchronize()
+    c1 = phy.cert_stats()
+    ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    return ms, {"windows": (c1[0] - c0[0]) // steps, "fallback_windows": (c1[1] - c0[1]) // steps,
+                "second_estimates": (c1[2] - c0[2]) // steps, "rewalked_packets": (c1[3] - c0[3]) // steps}
+
+
+def also_demod(phy, lp, torch, peak, name, sf, L, P, raw=False, gains=False, exact=False, steps=3):
+    """One extra demodulator workload for the `also` block: ms per launch, fraction of the measured HBM peak."""
+    import numpy as np
+    N = 1 << sf
+    nsym = 2 * L + 2
+    iq, payload = make_batch(phy, lp, torch, sf, L, P, 0x10AA51F7 ^ (sf << 8) ^ (raw << 4) ^ gains, raw=raw, gains=gains)
+    flags = (lp.F_DECHIRP if raw else 0) | (lp.F_EXACT if exact else 0)
+    cfg = lp.make_cfg(sf, flags=flags)
+    out = phy.alloc_demod_outputs(P, nsym - 2)
+    sampler = ClockSampler(phy.device.index or 0)
+    sampler.start()
+    ms, cert = time_demod(phy, lp, torch, cfg, iq, out, steps, 2)
+    sampler.stop_flag = True
+    sampler.join(timeout=3)
+    ok = bool((out["status"] == nsym - 2).all())
+    if not raw:                                            # the legacy path round-trips: the batch must decode to its payload
+        _, pay, _ = phy.decode_batch(out["symbols"])
+        ok = ok and torch.equal(pay.cpu(), payload)
+    byts = P * nsym * (8 * N + 2)
+    rec = {"workload": name, "sf": sf, "packets": P, "ms": ms, "symbols_per_s": P * nsym / (ms * 1e-3),
+           "msamples_per_s": P * nsym * N / (ms * 1e-3) / 1e6, "achieved_gbs": byts / (ms * 1e-3) / 1e9,
+           "frac": byts / (ms * 1e-3) / 1e9 / peak, "validated": ok, "certified": None if exact else cert,
+           "clocks": sampler.summary()}
+    del iq, out
+    torch.cuda.empty_cache()
+    return rec
+
+
+def also_stream(phy, lp, torch, peak, sf, gbytes=4.0, symbols=32, steps=3):
+    """Streaming preamble / sync-word detector (cfg 4 shape, one SF): frames back to back in noise, every frame found."""
+    N = 1 << sf
+    cfg = lp.make_cfg(sf, amplitude=1.0)
+    per_frame = (14 + symbols + 2) * N + N // 4
+    F = max(1, (1 << 17) // per_frame)              # many short streams: the detector's parallelism is streams x N/16 threads
+    S = max(1, int(gbytes * 1e9 / 8 / (F * per_frame)))
+    g = torch.Generator(device=phy.device).manual_seed(sf)
+    sym = torch.randint(0, N, (S * F, symbols), device=phy.device, generator=g).to(torch.uint16)
+    iq = phy.modulate_frames_batch(cfg, sym, padding=2).reshape(S, F * per_frame)
+    iq = torch.cat([iq, torch.zeros((S, 3 * N), dtype=iq.dtype, device=iq.device)], dim=1).contiguous()
+    iq = (iq + torch.view_as_complex(torch.randn((S, iq.shape[1], 2), device=phy.device, generator=g) * 0.05)).contiguous()
+    times = []
+    out = None
+    for it in range(steps + 1):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = phy.detect_stream(sf, iq, thresh_db=-8.0, mtu=symbols, max_frames=F + 1)
+        b.record()
+        torch.cuda.synchronize()
+        if it:
+            times.append(a.elapsed_time(b))
+    ok = bool((out["n_frames"] == F).all())
+    got = out["symbols"][:, :F, :].reshape(S * F, symbols).to(torch.int32)
+    ok = ok and bool((got == sym.to(torch.int32)).all())
+    ms = sum(times) / len(times)
+    n = S * iq.shape[1]
+    rec = {"workload": "stream detector SF%d, %d streams x %d frames back to back in noise" % (sf, S, F), "sf": sf, "ms": ms,
+           "msamples_per_s": n / ms / 1e3, "achieved_gbs": n * 8 / ms / 1e6, "frac": n * 8 / ms / 1e6 / peak, "validated": ok}
+    del iq, out, sym, got
+    torch.cuda.empty_cache()
+    return rec
+
+
+def also_awgn(phy, lp, torch, sf=7, snr_db=-6.0, packets=200000, payload=16):
+    """AWGN Monte-Carlo driver (cfg 5 shape, one cell): modulate + noise + demodulate + decode + score on the device."""
+    cc = lp.make_chain_cfg(sf, cr=4)
+    phy.awgn_roundtrip(cc, snr_db, 2048, payload, cell_id=1)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    counts, _ = phy.awgn_roundtrip(cc, snr_db, packets, payload, cell_id=2)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b)
+    c = counts.cpu().tolist()
+    return {"workload": "AWGN Monte-Carlo cell SF%d %.0f dB, %d packets x %d B, CR4/8" % (sf, snr_db, packets, payload), "sf": sf,
+            "ms": ms, "packets_per_s": packets / (ms * 1e-3), "packet_error_rate": c[1] / max(c[0], 1), "validated": c[0] == packets}
+
+
 def run_ours(args, wl):
     import numpy as np
     import torch
@@ -147,17 +272,8 @@ def run_ours(args, wl):
     cfg = lp.make_cfg(sf)
 
     # ---- synthetic batch, generated on the device by our own modulator (per-rank packet range) ----
-    g = torch.Generator(device="cpu").manual_seed(0x10AA51F7 + rank)
-    iq = torch.empty((P, spp), dtype=torch.complex64, device=dev)
-    chunk = max(1, min(P, (1 << 28) // spp))
-    payload_all = torch.randint(0, 256, (P, L), dtype=torch.uint8, generator=g)
-    for lo in range(0, P, chunk):
-        hi = min(P, lo + chunk)
-        sym = phy.encode_batch(payload_all[lo:hi].to(dev))
-        phy.modulate_batch(cfg, sym, iq[lo:hi])
-        phy.dechirp_batch(cfg, iq[lo:hi])
+    iq, payload_all = make_batch(phy, lp, torch, sf, L, P, 0x10AA51F7 + rank)
     out = phy.alloc_demod_outputs(P, nsym - 2)
-    torch.cuda.synchronize()
 
     two = args.two_kernel
     cfg_pre = lp.make_cfg(sf, flags=lp.F_ONLY_PREPASS)
@@ -165,7 +281,7 @@ def run_ours(args, wl):
     cfg_one = lp.make_cfg(sf, flags=lp.F_EXACT) if args.exact else cfg
 
     def step(ev=None):
-        if not two:                            # default: ONE launch per batch (demod_packet_kernel, one CTA per packet)
+        if not two:                            # default: ONE launch per batch (demod_cert_kernel, one pipeline per packet)
             if ev is not None:
                 ev[0].record()
             phy.demodulate_batch(cfg_one, iq, out=out)
@@ -231,6 +347,7 @@ def run_ours(args, wl):
         rc, o = phy.demodulate_batch_host(cfg, h_iq_np)
     te = (time.perf_counter() - te) / e2e_steps
     assert rc == 0 and np.array_equal(o["symbols"], out["symbols"][:Pe].cpu().numpy())
+    te_rank = te
     if world > 1:
         tt = torch.tensor([te], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -238,6 +355,14 @@ def run_ours(args, wl):
     e2e_value = world * Pe * nsym / te
     h2d = Pe * spp * 8
     d2h = Pe * ((nsym - 2) * 2 + 4 + 4 + 4 + 1)
+    h2d_gbs = h2d / te_rank / 1e9                           # this rank's own host -> device rate inside the call
+    if world > 1:
+        tt = torch.tensor([h2d_gbs], device=dev)
+        allg = [torch.zeros_like(tt) for _ in range(world)]
+        dist.all_gather(allg, tt)
+        h2d_all = [float(x.item()) for x in allg]
+    else:
+        h2d_all = [h2d_gbs]
 
     if rank != 0:
         if world > 1:
@@ -252,10 +377,11 @@ def run_ours(args, wl):
     else:
         kname = (("demod_warp_kernel<SF%d>" if sf <= 11 else "demod_packet_kernel<SF%d>") if args.exact else "demod_cert_kernel<SF%d>") % sf
         sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if not two and os.path.exists(tpath):
-        traffic = (json.load(open(tpath)).get("%s:%d" % (args.workload, P)) or {}).get("bytes")
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if not two and not args.exact and os.path.exists(tpath):
+        t = json.load(open(tpath)).get("%s:%d" % (args.workload, P)) or {}
+        traffic, traffic_src = t.get("bytes"), t.get("source")
     achieved = sym_bytes / (sym_kernel_ms * 1e-3) / 1e9
     step_bytes = P * nsym * b_sym
     line = {
@@ -265,12 +391,14 @@ def run_ours(args, wl):
         "msamples_per_s": world * P * spp / (ms_step * 1e-3) / 1e6,
         "step_hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
         "config": {"workload": wl["name"], "packets_per_gpu": P, "symbols_per_packet": nsym, "sf": sf,
+                   "batch": "homogeneous amplitude (every packet's max-abs is the same: the max prediction always hits; "
+                            "also.sf7_random_gain is the batch where it never does)",
                    "l2_policy": "inputs larger than L2 (%.1f GB per GPU per step)" % (P * spp * 8 / 1e9)},
         "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
-                     "kernel_ms": sym_kernel_ms, "algorithmic_bytes_per_launch": sym_bytes},
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_kind": peak_kind, "kernel_ms": sym_kernel_ms, "algorithmic_bytes_per_launch": sym_bytes},
         "e2e": {"value": e2e_value, "unit": "symbols/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "packets_per_step": Pe},
+                "packets_per_step": Pe, "h2d_gbs_per_rank": h2d_all},
         "gpu_launches": launches,
         "certified": {"windows": cert1[0] - cert0[0], "fallback_windows": cert1[1] - cert0[1],
                       "second_estimates": cert1[2] - cert0[2], "rewalked_packets": cert1[3] - cert0[3]},
@@ -284,8 +412,27 @@ def run_ours(args, wl):
         line["cpu_baseline"] = {"value": reps * n_pkt * nsym_c / s, "unit": "symbols/s", "cores": cores, "kind": kind,
                                 "sample": f"{reps} passes over {n_pkt} packets ({n_pkt * per_pkt * 8 / 1e6:.0f} MB IQ), one packet "
                                           f"per thread, {s:.1f} s wall = {s * cores:.0f} CPU-seconds"}
+        del ciq
     else:
         line["cpu_baseline"] = None
+    # ---- the other workloads north_star names, measured in the same run (single GPU only; ~16 GB resident each) ----
+    if world == 1 and not args.no_also and not two and not args.exact and args.workload == "sf7" and not args.packets:
+        del iq, out, h_iq
+        torch.cuda.empty_cache()
+        also = {}
+        also["sf7_random_gain"] = also_demod(phy, lp, torch, peak, "SF7, per-packet random gain in [0.5, 2): the max-abs prediction misses "
+                                             "every packet (estimator symbols redone, walk stands)", 7, 32, 1 << 18, gains=True)
+        also["sf7_raw_iq"] = also_demod(phy, lp, torch, peak, "SF7 raw (un-dechirped) IQ, on-chip conjugate downchirp (F_DECHIRP, "
+                                        "phy.cpp:182-243)", 7, 32, 1 << 18, raw=True)
+        also["sf7_exact"] = also_demod(phy, lp, torch, peak, "SF7, F_EXACT: every window through the operation-for-operation replay "
+                                       "(round-1 kernel)", 7, 32, 1 << 18, exact=True)
+        for s8, p8 in ((8, 1 << 17), (9, 1 << 16), (10, 1 << 15), (11, 1 << 14)):
+            also["sf%d" % s8] = also_demod(phy, lp, torch, peak, "SF%d BW125k, 32-byte payload, clean pre-dechirped IQ" % s8, s8, 32, p8)
+        also["sf12_cfg3"] = also_demod(phy, lp, torch, peak, WORKLOADS["sf12"]["name"], 12, 64, 1 << 14)
+        also["stream_sf7"] = also_stream(phy, lp, torch, peak, 7)
+        also["stream_sf12"] = also_stream(phy, lp, torch, peak, 12)
+        also["awgn_sf7"] = also_awgn(phy, lp, torch)
+        line["also"] = also
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -301,6 +448,7 @@ def main():
     ap.add_argument("--packets", type=int, default=0, help="packets per GPU (default: the workload's)")
     ap.add_argument("--e2e-packets", type=int, default=1 << 15)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-also", action="store_true", help="skip the `also` block (SF8-12, raw IQ, random gain, stream detector, AWGN)")
     ap.add_argument("--two-kernel", action="store_true", help="A/B: time the older prepass + symbols kernel pair")
     ap.add_argument("--exact", action="store_true", help="A/B: F_EXACT, every window through the operation-for-operation replay (round-1 kernel)")
     args = ap.parse_args()

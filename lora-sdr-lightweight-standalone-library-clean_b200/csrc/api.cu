@@ -75,6 +75,11 @@ struct lora_phy_cuda_ctx {
     unsigned long long* cert_stats = nullptr;           // [4] counters of the certified demodulator (demod_cert.cu)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
+    // host-variant pipeline (demodulate_batch_host): the batch is cut into chunks, chunk k+1 crosses PCIe on copy_stream
+    // into the other half of d_in while chunk k is demodulated on `stream`
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_h2d[2] = { nullptr, nullptr }, ev_done[2] = { nullptr, nullptr }, ev_start = nullptr;
+    size_t host_chunk_bytes = (size_t)64 << 20;         // LORA_PHY_HOST_CHUNK_MB
     std::recursive_mutex mu;                            // held for a whole entry point (staging buffers, scratch, err)
 };
 
@@ -198,6 +203,12 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
     ctx->state.release(); ctx->phases.release(); ctx->tmp.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
     ctx->h_in.release(); ctx->h_out.release();
+    for (int i = 0; i < 2; ++i) {
+        if (ctx->ev_h2d[i]) cudaEventDestroy(ctx->ev_h2d[i]);
+        if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+    }
+    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -355,13 +366,29 @@ int lora_phy_cuda_demodulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_c
     if (n_packets == 0) return demod_common(ctx, cfg, (cfg->flags & LORA_PHY_CUDA_F_DECHIRP) ? lk::MODE_HIGHLEVEL : lk::MODE_LEGACY,
                                             h_iq, packet_stride, nullptr, spp, 0, h_symbols, symbol_stride, nullptr, nullptr, nullptr, nullptr);
     CtxGuard g(ctx);
-    const size_t iq_bytes = n_packets * packet_stride * sizeof(cf);
+    if (!ctx->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            CK(cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+        }
+        CK(cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming));
+        if (const char* mb = getenv("LORA_PHY_HOST_CHUNK_MB")) {
+            const long v = strtol(mb, nullptr, 10);
+            if (v > 0 && v <= 4096) ctx->host_chunk_bytes = (size_t)v << 20;
+        }
+    }
+    const size_t pkt_bytes = packet_stride * sizeof(cf);
     const size_t sym_bytes = n_packets * symbol_stride * sizeof(uint16_t);
     // device scratch layout (d_out): symbols | cfo | time_offset | status | sync
     const size_t off_cfo = (sym_bytes + 15) & ~(size_t)15;
     const size_t off_to = off_cfo + n_packets * 4, off_st = off_to + n_packets * 4, off_sync = off_st + n_packets * 4;
     const size_t out_bytes = off_sync + n_packets;
-    CK(ctx->d_in.reserve(iq_bytes + 16));
+    size_t chunk = pkt_bytes ? ctx->host_chunk_bytes / pkt_bytes : n_packets;
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_packets) chunk = n_packets;
+    const size_t half = (chunk * pkt_bytes + 255) & ~(size_t)255;       // one chunk of IQ; d_in holds two
+    CK(ctx->d_in.reserve(2 * half + 16));
     CK(ctx->d_out.reserve(out_bytes));
     CK(ctx->h_out.reserve(out_bytes));
     uint32_t* d_counts = nullptr;
@@ -372,21 +399,45 @@ int lora_phy_cuda_demodulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_c
         d_counts = static_cast<uint32_t*>(ctx->d_aux.p);
         CK(cudaMemcpyAsync(d_counts, h_counts, n_packets * 4, cudaMemcpyHostToDevice, ctx->stream));
     }
-    CK(cudaMemcpyAsync(ctx->d_in.p, h_iq, iq_bytes, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemsetAsync(ctx->d_out.p, 0, out_bytes, ctx->stream));
+    CK(cudaEventRecord(ctx->ev_start, ctx->stream));                     // the copy stream starts after earlier work of the context
+    CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_start, 0));
     unsigned char* o = static_cast<unsigned char*>(ctx->d_out.p);
-    rc = lora_phy_cuda_demodulate_batch(ctx, cfg, ctx->d_in.p, packet_stride, d_counts, spp, n_packets,
-                                        reinterpret_cast<uint16_t*>(o), symbol_stride, o + off_sync,
-                                        reinterpret_cast<float*>(o + off_cfo), reinterpret_cast<float*>(o + off_to),
-                                        reinterpret_cast<int32_t*>(o + off_st));
-    if (rc) return rc;
+    const unsigned char* src = static_cast<const unsigned char*>(h_iq);
+    size_t k = 0;
+    for (size_t lo = 0; lo < n_packets; lo += chunk, ++k) {
+        const size_t n = std::min(chunk, n_packets - lo);
+        const int b = (int)(k & 1);
+        unsigned char* d_chunk = static_cast<unsigned char*>(ctx->d_in.p) + (size_t)b * half;
+        if (k >= 2) CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_done[b], 0));       // chunk k-2 has left this half
+        CK(cudaMemcpyAsync(d_chunk, src + lo * pkt_bytes, n * pkt_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+        CK(cudaEventRecord(ctx->ev_h2d[b], ctx->copy_stream));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d[b], 0));
+        rc = lora_phy_cuda_demodulate_batch(ctx, cfg, d_chunk, packet_stride, d_counts ? d_counts + lo : nullptr, spp, n,
+                                            reinterpret_cast<uint16_t*>(o) + lo * symbol_stride, symbol_stride, o + off_sync + lo,
+                                            reinterpret_cast<float*>(o + off_cfo) + lo, reinterpret_cast<float*>(o + off_to) + lo,
+                                            reinterpret_cast<int32_t*>(o + off_st) + lo);
+        if (rc) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamSynchronize(ctx->stream); return rc; }
+        CK(cudaEventRecord(ctx->ev_done[b], ctx->stream));
+    }
     CK(cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     const unsigned char* h = static_cast<const unsigned char*>(ctx->h_out.p);
     const int32_t* st = reinterpret_cast<const int32_t*>(h + off_st);
-    for (size_t p = 0; p < n_packets; ++p) {           // only the symbols the reference would have written
-        const int32_t cnt = st[p];
-        if (cnt > 0) memcpy(h_symbols + p * symbol_stride, h + p * symbol_stride * 2, (size_t)cnt * 2);
+    // only the symbols the reference would have written: rows of equal length leave in one strided copy
+    const size_t step = ((size_t)1 << cfg->sf) * cfg->osr;
+    const size_t total = step ? spp / step : 0;
+    const size_t uniform = total >= 2 ? total - 2 : total;
+    bool all_uniform = !h_counts;
+    for (size_t p = 0; all_uniform && p < n_packets; ++p) all_uniform = st[p] == (int32_t)uniform;
+    if (all_uniform) {
+        if (uniform == symbol_stride) memcpy(h_symbols, h, n_packets * symbol_stride * 2);
+        else for (size_t p = 0; p < n_packets; ++p) memcpy(h_symbols + p * symbol_stride, h + p * symbol_stride * 2, uniform * 2);
+    } else {
+        for (size_t p = 0; p < n_packets; ++p) {
+            const int32_t cnt = st[p];
+            if (cnt > 0) memcpy(h_symbols + p * symbol_stride, h + p * symbol_stride * 2, (size_t)cnt * 2);
+        }
     }
     if (h_cfo) memcpy(h_cfo, h + off_cfo, n_packets * 4);
     if (h_to) memcpy(h_to, h + off_to, n_packets * 4);

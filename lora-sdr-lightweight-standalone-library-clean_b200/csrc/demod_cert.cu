@@ -37,6 +37,14 @@ namespace lk {
 #define CERT_CTAS_PER_SM 2
 #endif
 
+#ifndef CERT_CTA_SMALL
+#define CERT_CTA_SMALL 256                    // threads per CTA for SF7-9 (a window is at most one warp there: any multiple of 32)
+#endif
+
+#ifndef CERT_TW0_SMEM_MAX_SF
+#define CERT_TW0_SMEM_MAX_SF 0                // pass-0 twiddles in shared memory up to this SF (A/B knob; registers measured faster)
+#endif
+
 constexpr int CERT_CAP = 512;                 // symbols per packet the fallback bitmap / symbol staging cover (255-byte payload
                                               // in the shipped framing); longer packets take the exact chain throughout
 // ---- certification constants (units of u = 2^-24), DESIGN.md section 5 ---------------------------------------------
@@ -66,7 +74,11 @@ struct CertCfg {
     static constexpr int SLOT = GD * PITCH;
     static constexpr size_t stage_bytes = (size_t)DOMS * SLOT * sizeof(cf);
     static constexpr size_t red_bytes = 256;               // Peak[8] | RedCell[8] | float[8] (multi-warp windows only)
-    static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + 256;
+    // pass-0 twiddles W_N^{tid*k}: a [16][T] table in shared memory for SF7-9 (15 conflict-free 64-bit loads per window
+    // instead of 30 registers for the kernel's lifetime -- the loop is register-bound there), registers for SF10-12
+    static constexpr bool TW0_SMEM = SF <= CERT_TW0_SMEM_MAX_SF;
+    static constexpr size_t tw0_bytes = TW0_SMEM ? (size_t)N * sizeof(cf) : 0;
+    static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + 256;
     // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
     static constexpr int fit = (int)(((size_t)227 * 1024 / CERT_CTAS_PER_SM - 1024 - fixed_bytes) / stage_bytes);
     static constexpr int STAGES = fit >= 3 ? 3 : 2;
@@ -74,7 +86,8 @@ struct CertCfg {
     static constexpr size_t bar_off = slot_bytes;
     static constexpr size_t red_off = bar_off + (size_t)DOMS * STAGES * sizeof(uint64_t);
     static constexpr size_t tw1_off = (red_off + red_bytes + 15) & ~(size_t)15;
-    static constexpr size_t ws_off = (tw1_off + (size_t)F::TW1_SIZE * sizeof(cf) + 15) & ~(size_t)15;
+    static constexpr size_t tw0_off = (tw1_off + (size_t)F::TW1_SIZE * sizeof(cf) + 15) & ~(size_t)15;
+    static constexpr size_t ws_off = (tw0_off + tw0_bytes + 15) & ~(size_t)15;
     static constexpr size_t bytes = ws_off + (size_t)DOMS * sizeof(CertShared);
 };
 
@@ -176,12 +189,21 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             tw1[j] = fx::mk((float)cs, (float)sn);
         }
     }
-    cf tw0[16];                                    // W_N^{tid * k}: correctly rounded, kept in registers
+    cf tw0[16];                                    // W_N^{tid * k}: correctly rounded; registers (SF10-12) or shared memory
+    cf* tw0s = reinterpret_cast<cf*>(smem_raw + C::tw0_off);
+    if (C::TW0_SMEM) {
+        for (int j = threadIdx.x; j < N; j += CTA) {             // entry [k * T + t]
+            double sn, cs;
+            sincospi(-2.0 * (double)F::tw0_exp(j % T, j / T) / (double)N, &sn, &cs);
+            tw0s[j] = fx::mk((float)cs, (float)sn);
+        }
+    } else {
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        double sn, cs;
-        sincospi(-2.0 * (double)F::tw0_exp(tid, k) / (double)N, &sn, &cs);
-        tw0[k] = fx::mk((float)cs, (float)sn);
+        for (int k = 0; k < 16; ++k) {
+            double sn, cs;
+            sincospi(-2.0 * (double)F::tw0_exp(tid, k) / (double)N, &sn, &cs);
+            tw0[k] = fx::mk((float)cs, (float)sn);
+        }
     }
     const int wr0 = F::wr_base(0, tid), rd0 = F::rd_base(0, tid);
     const int wr1 = NP == 3 ? F::wr_base(1, tid) : 0, rd1 = NP == 3 ? F::rd_base(1, tid) : 0;
@@ -219,10 +241,14 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
         if (lane == 0) { ws.sw[0] = 0; ws.sw[1] = 0; }
 
         // which max-abs to walk with (LoRaDemod.cpp:61-78): the previous packet's, verified against the samples the walk
-        // streams anyway; a packet that may have to be refused (no scratch) or is exact throughout is scanned first
+        // streams anyway.  A miss costs a second pair of exact estimator symbols and nothing else (measured: scanning
+        // first after a miss, as the round-1 kernel did, is slower at every SF -- SF12 24.4 -> 31.3 ms -- because clean
+        // batches alternate between max-abs classes <= 1 and 1 + 2^-23 and the scan re-reads HBM for long packets).
+        // Scanned first: a packet that may have to be refused (no scratch), one that is exact throughout, and any packet
+        // after a non-finite max.
         float use_max = pred_max;
         bool known = !legacy;
-        if (legacy && (a.no_scratch || all_exact || !(pred_max < 3.0e38f))) {       // (a non-finite prediction is never walked with)
+        if (legacy && (a.no_scratch || all_exact || !(pred_max < 3.0e38f))) {
             use_max = cert_scan_max<DT>(pkt, count, lane, redf);
             known = true;
             pred_max = use_max;
@@ -423,7 +449,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 // pass 0 in registers, twiddle, exchange(s) in the window's own slot
                 ff::dft16(v);
 #pragma unroll
-                for (int k = 1; k < 16; ++k) v[k] = ff::fcmul(v[k], tw0[k]);
+                for (int k = 1; k < 16; ++k) v[k] = ff::fcmul(v[k], C::TW0_SMEM ? tw0s[k * T + tid] : tw0[k]);
                 group_sync<T>();                               // every thread of the window has its raw samples
 #pragma unroll
                 for (int e = 0; e < 16; ++e) win[wr0 + F::wr_off(0, e)] = v[e];
@@ -663,9 +689,9 @@ bool cert_supported(int sf, const DemodArgs& a)
 cudaError_t launch_demod_cert(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream)
 {
     switch (sf) {
-    case 7: return launch_cert_sf<7, CTA_THREADS>(a, sm_count, stream);
-    case 8: return launch_cert_sf<8, CTA_THREADS>(a, sm_count, stream);
-    case 9: return launch_cert_sf<9, CTA_THREADS>(a, sm_count, stream);
+    case 7: return launch_cert_sf<7, CERT_CTA_SMALL>(a, sm_count, stream);
+    case 8: return launch_cert_sf<8, CERT_CTA_SMALL>(a, sm_count, stream);
+    case 9: return launch_cert_sf<9, CERT_CTA_SMALL>(a, sm_count, stream);
     case 10: return launch_cert_sf<10, CTA_THREADS>(a, sm_count, stream);
     case 11: return launch_cert_sf<11, CTA_THREADS>(a, sm_count, stream);
     case 12: return launch_cert_sf<12, CTA_THREADS>(a, sm_count, stream);
