@@ -417,11 +417,16 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             int roff = (odd_pkt ? 1 : 0) + tid;
 #pragma unroll 1
             for (uint32_t u = 0; u < n_units; ++u, s += GD) {
-                if (tid == 0) {
-                    int stg = stage + (STAGES - 1);
-                    if (stg >= STAGES) stg -= STAGES;
-                    if (u + (STAGES - 1) < n_units) prefetch(s + (STAGES - 1) * GD, stg);
-                }
+                // The slot refilled during this step is the one the PREVIOUS step consumed.  Its refill is issued after
+                // this step's first barrier: a thread that has reached that barrier has finished the previous step (its
+                // last generic-proxy store there is followed by fence.proxy.async), so no end-of-step barrier is needed.
+                auto refill = [&]() {
+                    if (tid == 0) {
+                        int stg = stage + (STAGES - 1);
+                        if (stg >= STAGES) stg -= STAGES;
+                        if (u + (STAGES - 1) < n_units) prefetch(s + (STAGES - 1) * GD, stg);
+                    }
+                };
                 const bool active = s < total;
                 if (!regular) {
                     const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);
@@ -450,10 +455,15 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 ff::dft16(v);
 #pragma unroll
                 for (int k = 1; k < 16; ++k) v[k] = ff::fcmul(v[k], C::TW0_SMEM ? tw0s[k * T + tid] : tw0[k]);
-                group_sync<T>();                               // every thread of the window has its raw samples
+                // exchange 0 in the window's own slot.  With natural strides (SF12) a thread overwrites exactly the entries it
+                // read its own samples from, unless the window sits one entry later (odd alignment): no barrier needed first.
+                constexpr bool OWN = F::stride(0, SF - 1) == (1 << (SF - 1));
+                const bool pre_sync = !OWN || roff != tid;
+                if (pre_sync) { group_sync<T>(); refill(); }  // every thread of the window has its raw samples
 #pragma unroll
                 for (int e = 0; e < 16; ++e) win[wr0 + F::wr_off(0, e)] = v[e];
                 group_sync<T>();
+                if (!pre_sync) refill();
 #pragma unroll
                 for (int e = 0; e < 16; ++e) v[e] = win[rd0 + F::rd_off(0, e)];
                 F::butterflies(1, v);
@@ -500,7 +510,8 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 const float q1 = __uint_as_float(kmax & ~15u);
                 // tier 1: the top bin holds more than 3/4 of N*E (Parseval: every other bin is below half its modulus)
                 bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
-                if (cany<DT>(!cert && active)) {
+                // (a window that is the whole pipeline needs no vote: cert is uniform across it)
+                if (GD == 1 ? (!cert && active) : cany<DT>(!cert && active)) {
                     // tier 2: the true second maximum of the window.  Keys inside a thread are distinct (register index in
                     // the low bits); (m1, m2) pairs merge as sorted pairs, so a key held by two threads shows up as m2 == m1
                     unsigned m1 = kloc, m2 = 0u;
@@ -544,10 +555,10 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                         }
                     }
                 }
-                ptx::fence_proxy_async();
-                csync<DT>();
+                ptx::fence_proxy_async();                      // this thread's stores to the slot precede its next refill
                 stage = stage + 1 == STAGES ? 0 : stage + 1;
             }
+            csync<DT>();                                       // the last step's slot and staging cells are settled
             if (lane == 0) st_windows += total;
             walked = true;
             rate_walk = rate;
