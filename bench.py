@@ -379,9 +379,10 @@ def run_ours(args, wl):
         sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
     traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "r02_traffic.json")
-    if not two and not args.exact and os.path.exists(tpath):
-        t = json.load(open(tpath)).get("%s:%d" % (args.workload, P)) or {}
-        traffic, traffic_src = t.get("bytes"), t.get("source")
+    if not two and not args.exact and os.path.exists(tpath):     # profiled, not measured in this run: per-packet DRAM bytes x packets
+        t = json.load(open(tpath)).get(args.workload) or {}
+        if t:
+            traffic, traffic_src = t["bytes_per_packet"] * P, "profiled: " + t["source"]
     achieved = sym_bytes / (sym_kernel_ms * 1e-3) / 1e9
     step_bytes = P * nsym * b_sym
     line = {
