@@ -325,3 +325,48 @@ def test_batch_starting_8_bytes_into_an_allocation(phy, lp, oracle, sf):
     rc = phy.lib.lora_phy_cuda_demodulate_batch(phy.h, __import__("ctypes").byref(bad), flat.data_ptr() + 4, spp, None, spp, 1,
                                                 out["symbols"].data_ptr(), out["symbols"].shape[1], None, None, None, None)
     assert rc == -errno.EINVAL
+
+
+# ---- 6. the certified path: its replay branch really runs, and every kernel family on awkward small cases ---------------
+def test_certified_fallbacks_fire(phy, lp, oracle):
+    """Windows whose argmax cannot be proven are replayed through the exact chain: noise-only packets (close top bins),
+    exact ties ([1,0,1,0]...), all-zero and NaN windows must show up in the replay counter, clean chirps must not --
+    and every packet still equals the oracle."""
+    rng = np.random.default_rng(77)
+    for sf in (7, 9, 12):
+        N = 1 << sf
+        S = 6 if sf < 12 else 4
+        clean = make_packets(oracle, rng, sf, 1, 4, S - 2, kind="clean")
+        c0 = phy.cert_stats()
+        check_legacy(phy, lp, oracle, clean, sf, 1, 0)
+        c1 = phy.cert_stats()
+        assert c1[0] - c0[0] >= 4 * S and c1[1] == c0[1], "clean chirps must certify without replay"
+        hard = np.zeros((5, S * N), np.complex64)
+        hard[0] = np.tile(np.array([1, 0, 1, 0], np.complex64), S * N // 4)          # bins 0 and N/2 tie exactly
+        hard[1] = 0                                                               # all-zero: q1 == 0
+        hard[2] = clean[0]
+        hard[2, N + 3] = np.complex64(complex(np.nan, 1.0))                        # one NaN window
+        hard[3] = (1e-30 * clean[1]).astype(np.complex64)                         # |X|^2 underflows in the reference
+        hard[4] = clean[2]
+        hard[4, 2 * N:3 * N] = np.exp(2j * np.pi * (5.5 - 0.09) * np.arange(N) / N).astype(np.complex64)   # half-bin tone: two close bins
+        with np.errstate(all="ignore"):
+            check_legacy(phy, lp, oracle, hard, sf, 1, 0)
+        c2 = phy.cert_stats()
+        assert c2[1] - c1[1] >= 3 * S, (sf, c2[1] - c1[1])
+    z = np.load(os.path.join(GOLD, "detection_inputs.npz"))
+    c0 = phy.cert_stats()
+    for case in range(6):
+        sf = int(z[f"case{case}_meta"][0])
+        check_legacy(phy, lp, oracle, z[f"case{case}_iq"][None, :].copy(), sf, 1, 0)
+    c1 = phy.cert_stats()
+    print("golden detection inputs: %d windows, %d replayed" % (c1[0] - c0[0], c1[1] - c0[1]))
+
+
+def test_every_kernel_family_small_cases():
+    """tools/sanitize_driver.py (written for compute-sanitizer, which is closed on this pool) as a plain run: every kernel
+    family on ragged / oversized / odd-aligned / loud / noise-only inputs must complete without a CUDA error."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "sanitize_driver.py")], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "sanitize_driver ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
