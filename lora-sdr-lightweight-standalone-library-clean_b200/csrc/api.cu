@@ -70,6 +70,7 @@ struct lora_phy_cuda_ctx {
     DevBuf txrx[3];                                      // tx/rx pipelines: symbols, status, host-variant results
     DevBuf mc[8];                                        // Monte-Carlo driver: payload, tx symbols, IQ, rx symbols, status+sync, decoded, len, flags
     std::mutex mc_mu;
+    lk::McChannel mc_channel = {};                      // set by awgn_roundtrip around its modulate call (fused channel)
     size_t mc_scratch_bytes = (size_t)4 << 30;           // IQ bytes per Monte-Carlo chunk (LORA_PHY_MC_SCRATCH_MB)
     DevBuf lfsr;                                         // dewhitening byte table of the coding chain (chain.cu)
     unsigned long long* cert_stats = nullptr;           // [4] counters of the certified demodulator (demod_cert.cu)
@@ -559,6 +560,7 @@ long lora_phy_cuda_modulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cf
     a.amplitude = cfg->amplitude; a.sync = cfg->sync_word & 0xff;
     a.phase_scratch = static_cast<float*>(ctx->phases.p);
     a.frame = 0; a.padding = 0;
+    a.channel = ctx->mc_channel;                    // off unless the Monte-Carlo driver is the caller
     unsigned launches = 0;
     cudaError_t e = lk::launch_modulate(a, ctx->sm_count, ctx->stream, &launches);
     ctx->launches += launches;
@@ -589,6 +591,7 @@ long lora_phy_cuda_modulate_frames_batch(lora_phy_cuda_ctx* ctx, const lora_phy_
     CtxGuard g(ctx);
     CK(ctx->phases.reserve(n_frames * (spf + 15) * sizeof(float)));
     lk::ModArgs a;
+    a.channel = lk::McChannel{};
     a.symbols = d_symbols; a.symbol_stride = symbol_stride; a.symbols_per_packet = (uint32_t)spf;
     a.n_packets = (uint32_t)n_frames; a.iq = static_cast<cf*>(d_iq); a.packet_stride = frame_stride;
     a.sf = (int)cfg->sf; a.osr = cfg->osr; a.bw_scale = 1.0f;
@@ -1111,10 +1114,21 @@ int lora_phy_cuda_awgn_roundtrip(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cha
         ++ctx->launches;
         long r = lora_phy_cuda_encode_chain_batch(ctx, cc, pay, 256, payload_len, n, txs, nsym);
         if (r < 0) return (int)r;
+        // synthesis + AWGN + caller-side dechirp in ONE pass: the modulator's store applies the channel, so the frame
+        // crosses HBM once on its way to the demodulator (LORA_PHY_MC_UNFUSED=1: the separate channel kernel, A/B)
+        static const bool unfused = getenv("LORA_PHY_MC_UNFUSED") != nullptr;
+        if (!unfused) {
+            ctx->mc_channel.on = 1; ctx->mc_channel.seed = seed; ctx->mc_channel.first_packet = first_packet + done;
+            ctx->mc_channel.cell = cell_id; ctx->mc_channel.noise_std = noise_std; ctx->mc_channel.chirp = table;
+            ctx->mc_channel.chirp_mask = (uint32_t)N - 1;
+        }
         r = lora_phy_cuda_modulate_batch(ctx, &cfg, txs, nsym, nsym, n, iq, spp);
+        ctx->mc_channel.on = 0;
         if (r < 0) return (int)r;
-        CK(lk::launch_awgn_dechirp(a, ctx->sm_count, ctx->stream));
-        ++ctx->launches;
+        if (unfused) {
+            CK(lk::launch_awgn_dechirp(a, ctx->sm_count, ctx->stream));
+            ++ctx->launches;
+        }
         int rc = lora_phy_cuda_demodulate_batch(ctx, &cfg, iq, spp, nullptr, spp, n, rxs, nsym, sync, nullptr, nullptr, status);
         if (rc < 0) return rc;
         rc = lora_phy_cuda_decode_chain_batch(ctx, cc, rxs, nsym, status, nsym, n, dec, dec_stride, len, flags);

@@ -108,15 +108,25 @@ GM_HD double sc_cos_poly(double x2)
     return dfma(x6, t2, c);
 }
 
+// __inv_pio4[]: consecutive 32-bit windows (8-bit steps) of 4/pi's binary expansion.  Tables indexed at run time live at
+// namespace scope (device: global memory through the read-only cache): as function-local arrays they were rebuilt
+// in LOCAL memory by every call -- two dozen stores per sample in the Monte-Carlo channel.
+#define GM_INV_PIO4_INIT { \
+        0xa2u, 0xa2f9u, 0xa2f983u, 0xa2f9836eu, 0xf9836e4eu, 0x836e4e44u, 0x6e4e4415u, 0x4e441529u, \
+        0x441529fcu, 0x1529fc27u, 0x29fc2757u, 0xfc2757d1u, 0x2757d1f5u, 0x57d1f534u, 0xd1f534ddu, \
+        0xf534ddc0u, 0x34ddc0dbu, 0xddc0db62u, 0xc0db6295u, 0xdb629599u, 0x6295993cu, 0x95993c43u, \
+        0x993c4390u, 0x3c439041u }
+#if defined(__CUDACC__)
+static __device__ const uint32_t gm_inv_pio4_d[24] = GM_INV_PIO4_INIT;
+#endif
+static const uint32_t gm_inv_pio4_h[24] = GM_INV_PIO4_INIT;
 GM_HD uint32_t sc_inv_pio4(int i)
 {
-    // __inv_pio4[]: consecutive 32-bit windows (8-bit steps) of 4/pi's binary expansion
-    const uint32_t t[24] = {
-        0xa2u, 0xa2f9u, 0xa2f983u, 0xa2f9836eu, 0xf9836e4eu, 0x836e4e44u, 0x6e4e4415u, 0x4e441529u,
-        0x441529fcu, 0x1529fc27u, 0x29fc2757u, 0xfc2757d1u, 0x2757d1f5u, 0x57d1f534u, 0xd1f534ddu,
-        0xf534ddc0u, 0x34ddc0dbu, 0xddc0db62u, 0xc0db6295u, 0xdb629599u, 0x6295993cu, 0x95993c43u,
-        0x993c4390u, 0x3c439041u };
-    return t[i];
+#if defined(__CUDA_ARCH__)
+    return __ldg(&gm_inv_pio4_d[i]);
+#else
+    return gm_inv_pio4_h[i];
+#endif
 }
 
 GM_HD double sc_reduce_large(uint32_t xi, int* np)
@@ -252,6 +262,7 @@ GM_HD float atanf_g(float x)
 {
     const float hi[4] = { 4.6364760399e-01f, 7.8539812565e-01f, 9.8279368877e-01f, 1.5707962513e+00f };
     const float lo[4] = { 5.0121582440e-09f, 3.7748947079e-08f, 3.4473217170e-08f, 7.5497894159e-08f };
+    // (indexed through selects below, never through memory)
     const float aT[11] = { 3.3333334327e-01f, -2.0000000298e-01f, 1.4285714924e-01f, -1.1111110449e-01f,
                            9.0908870101e-02f, -7.6918758452e-02f, 6.6610731184e-02f, -5.8335702866e-02f,
                            4.9768779427e-02f, -3.6531571299e-02f, 1.6285819933e-02f };
@@ -280,7 +291,9 @@ GM_HD float atanf_g(float x)
     float s1 = z * (aT[0] + w * (aT[2] + w * (aT[4] + w * (aT[6] + w * (aT[8] + w * aT[10])))));
     float s2 = w * (aT[1] + w * (aT[3] + w * (aT[5] + w * (aT[7] + w * aT[9]))));
     if (id < 0) return x - x * (s1 + s2);
-    z = hi[id] - ((x * (s1 + s2) - lo[id]) - x);
+    const float hid = id == 0 ? hi[0] : id == 1 ? hi[1] : id == 2 ? hi[2] : hi[3];
+    const float lod = id == 0 ? lo[0] : id == 1 ? lo[1] : id == 2 ? lo[2] : lo[3];
+    z = hid - ((x * (s1 + s2) - lod) - x);
     return hx < 0 ? -z : z;
 }
 
@@ -335,18 +348,26 @@ GM_HD float atan2f_g(float y, float x)
 // ------------------------------------------------------------------------------------
 // logf / log10f : glibc sysdeps/ieee754/flt-32/{e_logf.c,e_log10f.c}
 // ------------------------------------------------------------------------------------
+#define GM_LOGF_TAB_INIT { \
+        0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2, 0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2, \
+        0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2, 0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3, \
+        0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3, 0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3, \
+        0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4, 0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4, \
+        0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5, 0x1p+0, 0x0p+0, \
+        0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5, 0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4, \
+        0x1.b2036576afce6p-1, 0x1.526e57720db08p-3, 0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3, \
+        0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2, 0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2 }
+#if defined(__CUDACC__)
+static __device__ const double gm_logf_tab_d[32] = GM_LOGF_TAB_INIT;
+#endif
+static const double gm_logf_tab_h[32] = GM_LOGF_TAB_INIT;
 GM_HD void logf_tab(int i, double* invc, double* logc)
 {
-    const double t[32] = {
-        0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2, 0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2,
-        0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2, 0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3,
-        0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3, 0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3,
-        0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4, 0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4,
-        0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5, 0x1p+0, 0x0p+0,
-        0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5, 0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4,
-        0x1.b2036576afce6p-1, 0x1.526e57720db08p-3, 0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3,
-        0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2, 0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2 };
-    *invc = t[2 * i]; *logc = t[2 * i + 1];
+#if defined(__CUDA_ARCH__)
+    *invc = __ldg(&gm_logf_tab_d[2 * i]); *logc = __ldg(&gm_logf_tab_d[2 * i + 1]);
+#else
+    *invc = gm_logf_tab_h[2 * i]; *logc = gm_logf_tab_h[2 * i + 1];
+#endif
 }
 
 GM_HD float logf_g(float x)

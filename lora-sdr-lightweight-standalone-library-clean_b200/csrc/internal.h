@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stddef.h>
 #include "fft_exact.cuh"
+#include "mc_noise.cuh"
 
 namespace lk {
 
@@ -50,6 +51,7 @@ struct ModArgs {
     const uint16_t* symbols; size_t symbol_stride; uint32_t symbols_per_packet; uint32_t n_packets;
     cf* iq; size_t packet_stride; int sf; uint32_t osr; float bw_scale; float amplitude; uint32_t sync;
     float* phase_scratch;   // [n_packets][chirps] start phase of every chirp
+    McChannel channel;      // Monte-Carlo driver: AWGN + dechirp fused into the store (channel.on), else untouched
     int frame;              // 0: shipped framing (2 sync chirps + data); 1: upstream frame format (LoRaMod.cpp:109-238)
     uint32_t padding;       // frame format: trailing zero symbols
 };

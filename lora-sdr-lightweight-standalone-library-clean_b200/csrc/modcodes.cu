@@ -7,6 +7,7 @@
 //   compensate_offsets   src/phy/phy.cpp:150-180
 #include "internal.h"
 #include "glibc_math.cuh"
+#include "mc_noise.cuh"
 
 namespace lk {
 
@@ -154,6 +155,7 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) mod_emit_kernel(const ModArgs
                 tile[warp][lane][j] = fx::mk(fx::fmul(amp, cs), fx::fmul(amp, sn));
             }
             __syncwarp();
+#pragma unroll 4
             for (int r = 0; r < 32; ++r) {
                 const unsigned long long ch = w * 32 + r;
                 if (ch < n_chirps && (uint32_t)lane < jn) {
@@ -163,7 +165,13 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) mod_emit_kernel(const ModArgs
                         len = rs == 14 ? step / 4 : step;
                         off = rs <= 14 ? rs * step : 14 * step + step / 4 + (rs - 15) * step;
                     }
-                    if (j0 + lane < len) a.iq[(size_t)rp * a.packet_stride + off + j0 + lane] = tile[warp][r][lane];
+                    if (j0 + lane < len) {
+                        // Monte-Carlo driver: noise and the caller-side dechirp are applied HERE, so the clean frame never
+                        // exists in HBM and the channel costs no pass of its own (same arithmetic as awgn_dechirp_kernel)
+                        cf v = tile[warp][r][lane];
+                        if (a.channel.on) v = mc_channel_sample(a.channel, a.channel.first_packet + rp, off + j0 + lane, v);
+                        a.iq[(size_t)rp * a.packet_stride + off + j0 + lane] = v;
+                    }
                 }
             }
             __syncwarp();

@@ -10,29 +10,15 @@
 //   mc_score_kernel      compares decoded bytes / demodulated symbols with what was sent, accumulates counters
 #include "internal.h"
 #include "glibc_math.cuh"
+#include "mc_noise.cuh"
 
 namespace lk {
 
 namespace {
 
-constexpr uint32_t MC_DOMAIN_NOISE = 0x4e4f4953u, MC_DOMAIN_PAYLOAD = 0x50415931u;
-
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
-{
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-    }
-    return c;
-}
-
 __device__ __forceinline__ uint4 mc_block(const McArgs& a, unsigned long long packet, uint32_t index, uint32_t domain)
 {
-    return philox4x32_10(make_uint4(index, (uint32_t)packet, (uint32_t)(packet >> 32) ^ (a.cell << 8), domain),
-                         (uint32_t)a.seed, (uint32_t)(a.seed >> 32));
+    return mc_philox(a.seed, a.cell, packet, index, domain);
 }
 
 __global__ void __launch_bounds__(256) mc_payload_kernel(const McArgs a)
@@ -56,18 +42,11 @@ __global__ void __launch_bounds__(256) awgn_dechirp_kernel(const McArgs a)
     for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < total;
          k += (unsigned long long)gridDim.x * blockDim.x) {
         const uint32_t p = (uint32_t)(k / a.spp), i = (uint32_t)(k % a.spp);
-        const uint4 x = mc_block(a, a.first_packet + p, i, MC_DOMAIN_NOISE);
-        const float u1 = fx::fmul(fx::fadd((float)(x.x >> 9), 0.5f), 0x1p-23f);
-        const float u2 = fx::fmul(fx::fadd((float)(x.y >> 9), 0.5f), 0x1p-23f);
-        const float r = __fsqrt_rn(fx::fmul(-4.605170185988092f, gm::log10f_g(u1)));
-        float sn, cs;
-        gm::sincosf_g(fx::fmul(6.283185307179586f, u2), &sn, &cs);
+        McChannel ch;
+        ch.on = 1; ch.seed = a.seed; ch.first_packet = a.first_packet; ch.cell = a.cell; ch.noise_std = a.noise_std;
+        ch.chirp = a.chirp; ch.chirp_mask = mask;
         cf* q = a.iq + (size_t)p * a.packet_stride + i;
-        const cf v = *q;
-        const cf y = fx::mk(fx::fadd(v.x, fx::fmul(a.noise_std, fx::fmul(r, cs))),
-                            fx::fadd(v.y, fx::fmul(a.noise_std, fx::fmul(r, sn))));
-        const float2 t = __ldg(reinterpret_cast<const float2*>(a.chirp + (i & mask)));
-        *q = fx::cmul(y, fx::mk(t.x, t.y));
+        *q = mc_channel_sample(ch, a.first_packet + p, i, *q);
     }
 }
 
