@@ -233,6 +233,63 @@ def also_stream(phy, lp, torch, peak, sf, gbytes=4.0, symbols=32, steps=3):
     return rec
 
 
+def also_stream_mixed(phy, lp, torch, peak, gbytes=3.0, symbols=24, steps=3):
+    """BASELINE configs[3] shape: ONE batch of continuous streams that differ in SF (7..12), bandwidth (the reference's
+    bw_scale semantics) and oversampling, frames in the upstream format back to back with a per-stream carrier offset,
+    through lora_phy_cuda_detect_streams_ex (one launch per distinct (sf, bw, osr))."""
+    import math
+    import numpy as np
+    groups = [(sf, k, osr) for sf in range(7, 13) for (k, osr) in ((1, 1), (2, 1), (1, 2), (1, 4))]
+    per_group = gbytes * 1e9 / 8 / len(groups)
+    n_row = 1 << 17
+    g = torch.Generator(device=phy.device).manual_seed(0xC0FFEE)
+    rows, sfs, bws, osrs, counts, want = [], [], [], [], [], []
+    for sf, k, osr in groups:
+        NN = (1 << sf) * osr
+        per_frame = (14 + symbols + 2) * NN + NN // 4
+        F = max(1, (n_row - 3 * NN) // per_frame)
+        S = max(1, int(per_group / n_row))
+        sym = torch.randint(0, 1 << sf, (S * F, symbols), device=phy.device, generator=g).to(torch.uint16)
+        fr = phy.modulate_frames_batch(lp.make_cfg(sf, bw_hz=125000 * k, osr=osr, amplitude=1.0), sym, padding=2).reshape(S, F * per_frame)
+        # per-stream carrier offset, phase restarting every symbol length (scripts/generate_lora_phy_vectors.py:113-117)
+        cfo = (torch.rand((S, 1), device=phy.device, generator=g) - 0.5) * 0.5
+        ph = 2 * math.pi * cfo * (torch.arange(fr.shape[1], device=phy.device) % NN).to(torch.float32)[None, :] / NN
+        fr = fr * torch.polar(torch.ones_like(ph), ph)
+        row = torch.zeros((S, n_row), dtype=torch.complex64, device=phy.device)
+        row[:, :fr.shape[1]] = fr
+        rows.append(row)
+        sfs += [sf] * S; bws += [k] * S; osrs += [osr] * S
+        counts += [fr.shape[1] + 3 * NN] * S
+        want += [F] * S
+    iq = torch.cat(rows)
+    del rows
+    iq = (iq + torch.view_as_complex(torch.randn((iq.shape[0], n_row, 2), device=phy.device, generator=g) * 0.05)).contiguous()
+    d_counts = torch.tensor(counts, dtype=torch.int64).to(torch.uint32).to(phy.device)
+    Fmax = max(want) + 1
+    times, out = [], None
+    for it in range(steps + 1):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = phy.detect_stream(sfs, iq, thresh_db=-8.0, mtu=symbols, max_frames=Fmax, sample_counts=d_counts, bw_scale=bws, osr=osrs)
+        b.record()
+        torch.cuda.synchronize()
+        if it:
+            times.append(a.elapsed_time(b))
+    nf = out["n_frames"].cpu().numpy()
+    want = np.array(want)
+    home = (np.array(bws) == 1) & (np.array(osrs) == 1)
+    ms = sum(times) / len(times)
+    n = int(sum(counts))
+    rec = {"workload": "cfg-4 shape: %d streams, SF7-12 x (BW125, BW250, osr 2, osr 4), frames back to back with per-stream CFO in "
+                       "noise, one detect_streams_ex call (%d launches)" % (iq.shape[0], len(groups)),
+           "ms": ms, "msamples_per_s": n / ms / 1e3, "achieved_gbs": n * 8 / ms / 1e6, "frac": n * 8 / ms / 1e6 / peak,
+           "frames_found_frac": float(np.minimum(nf, want).sum() / want.sum()),
+           "validated": bool((nf[home] == want[home]).all())}
+    del iq, out
+    torch.cuda.empty_cache()
+    return rec
+
+
 def also_awgn(phy, lp, torch, sf=7, snr_db=-6.0, packets=200000, payload=16):
     """AWGN Monte-Carlo driver (cfg 5 shape, one cell): modulate + noise + demodulate + decode + score on the device."""
     cc = lp.make_chain_cfg(sf, cr=4)
@@ -432,7 +489,9 @@ def run_ours(args, wl):
         also["sf12_cfg3"] = also_demod(phy, lp, torch, peak, WORKLOADS["sf12"]["name"], 12, 64, 1 << 14)
         also["stream_sf7"] = also_stream(phy, lp, torch, peak, 7)
         also["stream_sf12"] = also_stream(phy, lp, torch, peak, 12)
+        also["stream_cfg4_mixed"] = also_stream_mixed(phy, lp, torch, peak)
         also["awgn_sf7"] = also_awgn(phy, lp, torch)
+        also["awgn_sf10"] = also_awgn(phy, lp, torch, sf=10, packets=40000)
         line["also"] = also
     print(json.dumps(line))
     if world > 1:

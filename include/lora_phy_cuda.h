@@ -239,6 +239,24 @@ int lora_phy_cuda_detect_streams_mixed(lora_phy_cuda_ctx* ctx, const uint8_t* h_
                                        int32_t* d_frame_nsym, int16_t* d_symbols, uint32_t* d_n_frames,
                                        uint32_t* d_end_pos);
 
+/* cfg 4 of BASELINE.json: continuous streams that differ in spreading factor, bandwidth and oversampling, optionally
+ * pre-compensated.  Per stream: h_sf[s] in 7..12; h_bw_scale[s] in {1, 2, 4} (BW125 / 250 / 500 with the REFERENCE's
+ * semantics -- bw_scale multiplies chirp slope and symbol offset, ChirpGenerator.hpp:28-30, LoRaMod.cpp:24-25,36-37 --
+ * so dechirp tables, sync-word targets and the bin->time conversions of the state machine scale with it and the
+ * symbols come out as (bw_scale*s) mod N); h_osr[s] in 1..8 samples per chip (windows of N*osr samples, phase 0 of
+ * every chip as LoRaDemod.cpp:94-99 takes it, slides in chips).  NULL h_bw_scale / h_osr = 1.  One launch per distinct
+ * (sf, bw_scale, osr).  d_cfo / d_time_offset: NULL, or [n_streams] offsets applied to each stream exactly as
+ * compensate_offsets (phy.cpp:150-180: rotate by exp(-j*2*pi*cfo*n/(N*osr)), shift by round(time_offset) with zero
+ * fill) INSIDE the window load -- no compensated copy of the stream is made.  frame_start / end_pos are in samples.
+ * With bw_scale = osr = 1 and no offsets this is lora_phy_cuda_detect_streams_mixed.                                  */
+int lora_phy_cuda_detect_streams_ex(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, const uint8_t* h_bw_scale,
+                                    const uint8_t* h_osr, uint32_t sync_word, float thresh_db, uint32_t mtu,
+                                    const void* d_iq, size_t stream_stride, const uint32_t* d_sample_counts,
+                                    size_t n_samples, size_t n_streams, size_t max_frames,
+                                    const float* d_cfo, const float* d_time_offset,
+                                    uint32_t* d_frame_start, int32_t* d_frame_err, int32_t* d_frame_nsym,
+                                    int16_t* d_symbols, uint32_t* d_n_frames, uint32_t* d_end_pos);
+
 /* ---- bit pipeline: K4 (full upstream coding chain) -------------------------------------------- */
 /* The chain the reference vendors under external/LoRa-SDR and its README's LoRaParams{cr, explicit_header,
  * crc_enabled} refer to (LoRaEncoder.cpp:161-233, LoRaDecoder.cpp:196-397): CRC-16, 3-byte explicit

@@ -96,6 +96,8 @@ SIGNATURES = {
     "lora_phy_cuda_detect_stream": (C.c_int, [_vp, _u32, _u32, _f32, _u32, _vp, _sz, _vp, _sz, _sz, _sz, _vp, _vp, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_detect_streams_mixed": (C.c_int, [_vp, _vp, _u32, _f32, _u32, _vp, _sz, _vp, _sz, _sz, _sz, _vp, _vp, _vp, _vp,
                                                      _vp, _vp]),
+    "lora_phy_cuda_detect_streams_ex": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _f32, _u32, _vp, _sz, _vp, _sz, _sz, _sz, _vp, _vp, _vp, _vp,
+                                                  _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_chain_symbols": (C.c_long, [_vp, _sz]),
     "lora_phy_cuda_encode_chain_batch": (C.c_long, [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_decode_chain_batch": (C.c_int, [_vp, _vp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp, _vp]),
@@ -299,37 +301,42 @@ class LoraPhyCuda:
         return rc, pay, crc
 
     # ---- streaming front end ---------------------------------------------------------------------
-    def detect_stream(self, sf, iq, sync_word=0x12, thresh_db=-30.0, mtu=256, max_frames=16, sample_counts=None):
+    def detect_stream(self, sf, iq, sync_word=0x12, thresh_db=-30.0, mtu=256, max_frames=16, sample_counts=None, bw_scale=None,
+                      osr=None, cfo=None, time_offset=None):
         """iq: complex64 [n_streams, n_samples] continuous IQ.  Returns dict of per-stream frame reports.
-        sf: one spreading factor, or a sequence with one per stream (mixed batch)."""
+        sf / bw_scale / osr: one value, or a sequence with one per stream (mixed batch, cfg 4); cfo / time_offset:
+        optional per-stream float tensors applied as compensate_offsets inside the window load."""
+        import numpy as np
         t = self.torch
         S, n = iq.shape
-        if not isinstance(sf, int):
-            import numpy as np
-            sfs = np.ascontiguousarray(sf, dtype=np.uint8)
-            if sfs.size != S:
-                raise ValueError("one spreading factor per stream")
-            out = dict(frame_start=t.zeros((S, max_frames), dtype=t.int32, device=self.device),
-                       frame_err=t.zeros((S, max_frames), dtype=t.int32, device=self.device),
-                       frame_nsym=t.zeros((S, max_frames), dtype=t.int32, device=self.device),
-                       symbols=t.zeros((S, max_frames, mtu), dtype=t.int16, device=self.device),
-                       n_frames=t.zeros(S, dtype=t.int32, device=self.device),
-                       end_pos=t.zeros(S, dtype=t.int32, device=self.device))
-            self._check(self.lib.lora_phy_cuda_detect_streams_mixed(
-                self.h, sfs.ctypes.data, sync_word, thresh_db, mtu, _ptr(iq), iq.stride(0), _ptr(sample_counts), n, S,
-                max_frames, _ptr(out["frame_start"]), _ptr(out["frame_err"]), _ptr(out["frame_nsym"]),
-                _ptr(out["symbols"]), _ptr(out["n_frames"]), _ptr(out["end_pos"])))
-            return out
         out = dict(frame_start=t.zeros((S, max_frames), dtype=t.int32, device=self.device),
                    frame_err=t.zeros((S, max_frames), dtype=t.int32, device=self.device),
                    frame_nsym=t.zeros((S, max_frames), dtype=t.int32, device=self.device),
                    symbols=t.zeros((S, max_frames, mtu), dtype=t.int16, device=self.device),
                    n_frames=t.zeros(S, dtype=t.int32, device=self.device),
                    end_pos=t.zeros(S, dtype=t.int32, device=self.device))
-        self._check(self.lib.lora_phy_cuda_detect_stream(
-            self.h, sf, sync_word, thresh_db, mtu, _ptr(iq), iq.stride(0), _ptr(sample_counts), n, S, max_frames,
-            _ptr(out["frame_start"]), _ptr(out["frame_err"]), _ptr(out["frame_nsym"]), _ptr(out["symbols"]),
-            _ptr(out["n_frames"]), _ptr(out["end_pos"])))
+        tail = (_ptr(out["frame_start"]), _ptr(out["frame_err"]), _ptr(out["frame_nsym"]), _ptr(out["symbols"]),
+                _ptr(out["n_frames"]), _ptr(out["end_pos"]))
+        plain = bw_scale is None and osr is None and cfo is None and time_offset is None
+        if isinstance(sf, int) and plain:
+            self._check(self.lib.lora_phy_cuda_detect_stream(self.h, sf, sync_word, thresh_db, mtu, _ptr(iq), iq.stride(0),
+                                                             _ptr(sample_counts), n, S, max_frames, *tail))
+            return out
+
+        def per_stream(v, default):
+            if v is None:
+                v = default
+            a = np.ascontiguousarray(np.broadcast_to(np.asarray(v, dtype=np.uint8), (S,)))
+            return a
+        sfs = per_stream(sf, 7)
+        if plain:
+            self._check(self.lib.lora_phy_cuda_detect_streams_mixed(self.h, sfs.ctypes.data, sync_word, thresh_db, mtu, _ptr(iq),
+                                                                    iq.stride(0), _ptr(sample_counts), n, S, max_frames, *tail))
+            return out
+        bws, osrs = per_stream(bw_scale, 1), per_stream(osr, 1)
+        self._check(self.lib.lora_phy_cuda_detect_streams_ex(self.h, sfs.ctypes.data, bws.ctypes.data, osrs.ctypes.data, sync_word,
+                                                             thresh_db, mtu, _ptr(iq), iq.stride(0), _ptr(sample_counts), n, S,
+                                                             max_frames, _ptr(cfo), _ptr(time_offset), *tail))
         return out
 
     # ---- full coding chain --------------------------------------------------------------------

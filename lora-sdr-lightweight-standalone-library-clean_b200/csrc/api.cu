@@ -66,7 +66,7 @@ struct lora_phy_cuda_ctx {
     SfTables tab[13];
     std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
     DevBuf state, phases, tmp;                          // PacketState[], modulator phases, compensate scratch
-    cf* sync_tab[13] = { nullptr };                      // stream detector tables per sf: up | down | fine (stream_sync.cu)
+    cf* sync_tab[3][13] = {};                            // stream detector tables per (bandwidth scale, sf): up | down | fine
     DevBuf txrx[3];                                      // tx/rx pipelines: symbols, status, host-variant results
     DevBuf mc[8];                                        // Monte-Carlo driver: payload, tx symbols, IQ, rx symbols, status+sync, decoded, len, flags
     std::mutex mc_mu;
@@ -197,7 +197,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
     }
     if (ctx->cert_stats) cudaFree(ctx->cert_stats);
     for (auto& kv : ctx->chirps) cudaFree(kv.second);
-    for (int sf = 0; sf <= 12; ++sf) if (ctx->sync_tab[sf]) cudaFree(ctx->sync_tab[sf]);
+    for (int k = 0; k < 3; ++k) for (int sf = 0; sf <= 12; ++sf) if (ctx->sync_tab[k][sf]) cudaFree(ctx->sync_tab[k][sf]);
     ctx->lfsr.release();
     for (auto& b : ctx->mc) b.release();
     for (auto& b : ctx->txrx) b.release();
@@ -594,7 +594,7 @@ long lora_phy_cuda_modulate_frames_batch(lora_phy_cuda_ctx* ctx, const lora_phy_
     a.channel = lk::McChannel{};
     a.symbols = d_symbols; a.symbol_stride = symbol_stride; a.symbols_per_packet = (uint32_t)spf;
     a.n_packets = (uint32_t)n_frames; a.iq = static_cast<cf*>(d_iq); a.packet_stride = frame_stride;
-    a.sf = (int)cfg->sf; a.osr = cfg->osr; a.bw_scale = 1.0f;
+    a.sf = (int)cfg->sf; a.osr = cfg->osr; a.bw_scale = (float)(cfg->bw_hz / 125000u);   // 1: upstream's frame; 2 / 4: bw_scale semantics
     a.amplitude = cfg->amplitude; a.sync = cfg->sync_word & 0xff;
     a.phase_scratch = static_cast<float*>(ctx->phases.p);
     a.frame = 1; a.padding = padding_symbols;
@@ -740,20 +740,22 @@ long lora_phy_cuda_decode_batch_host(lora_phy_cuda_ctx* ctx, const uint16_t* h_s
 
 // ---------------------------------------------------------------------------------------------
 // Tables of the upstream receiver (LoRaDemod.cpp:96-117): std::polar(1.0, double phase) narrowed to float, built
-// with the host's libm exactly as the reference's constructor does, once per (context, sf).
-static int sync_tables(lora_phy_cuda_ctx* ctx, uint32_t sf, cf** out)
+// with the host's libm exactly as the reference's constructor does, once per (context, sf, bandwidth scale).
+// bw_k = 2 / 4: the reference's bandwidth semantics (ChirpGenerator.hpp:28-30: bw_scale on start frequency and slope).
+static int sync_tables(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t bw_k, cf** out)
 {
-    if (ctx->sync_tab[sf]) { *out = ctx->sync_tab[sf]; return 0; }
+    const int slot = bw_k == 1 ? 0 : bw_k == 2 ? 1 : 2;
+    if (ctx->sync_tab[slot][sf]) { *out = ctx->sync_tab[slot][sf]; return 0; }
     const size_t N = (size_t)1 << sf, fine_n = N * 128;
     std::vector<cf> host(2 * N + fine_n);
-    float phase = (float)-M_PI;
+    float phase = (float)(-M_PI * (double)bw_k);
     double acc = 0.0;
     for (size_t i = 0; i < N; ++i) {
         acc += phase;
         const std::complex<double> e = std::polar(1.0, acc);
         host[i] = fx::mk((float)e.real(), (float)-e.imag());          // _upChirpTable = conj(entry)
         host[N + i] = fx::mk((float)e.real(), (float)e.imag());       // _downChirpTable
-        phase = (float)((double)phase + (2 * M_PI) / (double)N);      // float += double: summed in double, rounded once
+        phase = (float)((double)phase + (2 * M_PI * (double)bw_k) / (double)N);   // float += double: summed in double, rounded once
     }
     acc = 0.0;
     phase = (float)(2.0 * M_PI / (double)fine_n);
@@ -766,8 +768,73 @@ static int sync_tables(lora_phy_cuda_ctx* ctx, uint32_t sf, cf** out)
     CK(cudaMalloc(&d, host.size() * sizeof(cf)));
     CK(cudaMemcpyAsync(d, host.data(), host.size() * sizeof(cf), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    ctx->sync_tab[sf] = d;
+    ctx->sync_tab[slot][sf] = d;
     *out = d;
+    return 0;
+}
+
+// one launch per distinct (sf, bandwidth scale, osr) among the streams, rows selected through an id list
+static int detect_streams_common(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, uint32_t sf_all, const uint8_t* h_bw_k,
+                                 const uint8_t* h_osr, uint32_t sync_word, float thresh_db, uint32_t mtu, const void* d_iq,
+                                 size_t stream_stride, const uint32_t* d_counts, size_t n_samples, size_t n_streams,
+                                 size_t max_frames, uint32_t* d_frame_start, int32_t* d_frame_err, int32_t* d_frame_nsym,
+                                 int16_t* d_symbols, uint32_t* d_n_frames, uint32_t* d_end_pos, const float* d_cfo,
+                                 const float* d_to)
+{
+    if (!ctx) return -EINVAL;
+    if (!mtu || mtu > 32767) return fail(ctx, -EINVAL, "mtu out of range 1..32767");
+    if (n_samples > stream_stride && n_streams > 1) return fail(ctx, -EINVAL, "n_samples exceeds stream_stride");
+    if (n_samples > 0xf0000000ull || n_streams > 0xffffffffull || max_frames > 0xffffffffull) return fail(ctx, -EINVAL, "too large");
+    if (n_streams && (!d_iq || !d_n_frames || (max_frames && (!d_frame_start || !d_frame_err || !d_frame_nsym || !d_symbols))))
+        return fail(ctx, -EINVAL, "NULL buffer");
+    if ((d_cfo == nullptr) != (d_to == nullptr)) return fail(ctx, -EINVAL, "cfo and time_offset go together");
+    if (reinterpret_cast<uintptr_t>(d_iq) & 7u) return fail(ctx, -EINVAL, "d_iq is not 8-byte aligned");
+    std::map<std::tuple<int, int, int>, std::vector<uint32_t>> groups;
+    for (size_t s = 0; s < n_streams; ++s) {
+        const int sf = h_sf ? h_sf[s] : (int)sf_all, k = h_bw_k ? h_bw_k[s] : 1, osr = h_osr ? h_osr[s] : 1;
+        if (sf < 7 || sf > 12) return fail(ctx, -EINVAL, "stream sf out of range 7..12");
+        if (k != 1 && k != 2 && k != 4) return fail(ctx, -EINVAL, "stream bandwidth scale must be 1, 2 or 4");
+        if (osr < 1 || osr > 8) return fail(ctx, -EINVAL, "stream osr out of range 1..8");
+        groups[std::make_tuple(sf, k, osr)].push_back((uint32_t)s);
+    }
+    if (!n_streams) return 0;
+    CtxGuard g(ctx);
+    uint32_t* d_ids = nullptr;
+    const bool one_group = groups.size() == 1;
+    if (!one_group) {
+        CK(ctx->tmp.reserve(n_streams * sizeof(uint32_t)));
+        d_ids = static_cast<uint32_t*>(ctx->tmp.p);
+        size_t off = 0;
+        for (auto& kv : groups) {                                  // rows of one group are contiguous in the id list
+            CK(cudaMemcpyAsync(d_ids + off, kv.second.data(), kv.second.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+            off += kv.second.size();
+        }
+        CK(cudaStreamSynchronize(ctx->stream));                    // the host vectors go out of scope below
+    }
+    size_t off = 0;
+    for (auto& kv : groups) {
+        const uint32_t sf = (uint32_t)std::get<0>(kv.first), k = (uint32_t)std::get<1>(kv.first), osr = (uint32_t)std::get<2>(kv.first);
+        cf* tab = nullptr;
+        int rc = sync_tables(ctx, sf, k, &tab);
+        if (rc) return rc;
+        const size_t N = (size_t)1 << sf;
+        lk::StreamSyncArgs a;
+        a.iq = static_cast<const cf*>(d_iq); a.stream_stride = stream_stride; a.counts = d_counts;
+        a.n_samples = (uint32_t)n_samples; a.n_streams = (uint32_t)kv.second.size();
+        a.up = tab; a.down = tab + N; a.fine = tab + 2 * N;
+        a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
+        a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
+        a.osr = osr; a.bw_k = k;
+        a.sync0 = (uint32_t)((((sync_word >> 4) & 0xf) * k) % (N / 8));     // the modulator puts the nibbles at nibble*8*bw_k bins
+        a.sync1 = (uint32_t)(((sync_word & 0xf) * k) % (N / 8));
+        a.comp_cfo = d_cfo; a.comp_to = d_to;
+        { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
+        a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
+        a.n_frames = d_n_frames; a.end_pos = d_end_pos; a.ids = one_group ? nullptr : d_ids + off;
+        CK(lk::launch_stream_sync((int)sf, a, ctx->stream));
+        ++ctx->launches;
+        off += kv.second.size();
+    }
     return 0;
 }
 
@@ -778,29 +845,9 @@ int lora_phy_cuda_detect_stream(lora_phy_cuda_ctx* ctx, uint32_t sf, uint32_t sy
 {
     if (!ctx) return -EINVAL;
     if (sf < 7 || sf > 12) return fail(ctx, -EINVAL, "sf out of range 7..12");
-    if (!mtu || mtu > 32767) return fail(ctx, -EINVAL, "mtu out of range 1..32767");
-    if (n_samples > stream_stride && n_streams > 1) return fail(ctx, -EINVAL, "n_samples exceeds stream_stride");
-    if (n_samples > 0xf0000000ull || n_streams > 0xffffffffull || max_frames > 0xffffffffull) return fail(ctx, -EINVAL, "too large");
-    if (n_streams && (!d_iq || !d_n_frames || (max_frames && (!d_frame_start || !d_frame_err || !d_frame_nsym || !d_symbols))))
-        return fail(ctx, -EINVAL, "NULL buffer");
-    if (!n_streams) return 0;
-    CtxGuard g(ctx);
-    cf* tab = nullptr;
-    int rc = sync_tables(ctx, sf, &tab);
-    if (rc) return rc;
-    const size_t N = (size_t)1 << sf;
-    lk::StreamSyncArgs a;
-    a.iq = static_cast<const cf*>(d_iq); a.stream_stride = stream_stride; a.counts = d_counts;
-    a.n_samples = (uint32_t)n_samples; a.n_streams = (uint32_t)n_streams;
-    a.up = tab; a.down = tab + N; a.fine = tab + 2 * N;
-    a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
-    a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
-    { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
-    a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
-    a.n_frames = d_n_frames; a.end_pos = d_end_pos; a.ids = nullptr;
-    CK(lk::launch_stream_sync((int)sf, a, ctx->stream));
-    ++ctx->launches;
-    return 0;
+    return detect_streams_common(ctx, nullptr, sf, nullptr, nullptr, sync_word, thresh_db, mtu, d_iq, stream_stride, d_counts,
+                                 n_samples, n_streams, max_frames, d_frame_start, d_frame_err, d_frame_nsym, d_symbols,
+                                 d_n_frames, d_end_pos, nullptr, nullptr);
 }
 
 int lora_phy_cuda_detect_streams_mixed(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, uint32_t sync_word, float thresh_db,
@@ -811,48 +858,23 @@ int lora_phy_cuda_detect_streams_mixed(lora_phy_cuda_ctx* ctx, const uint8_t* h_
 {
     if (!ctx) return -EINVAL;
     if (!h_sf && n_streams) return fail(ctx, -EINVAL, "h_sf is NULL");
-    if (!mtu || mtu > 32767) return fail(ctx, -EINVAL, "mtu out of range 1..32767");
-    if (n_samples > stream_stride && n_streams > 1) return fail(ctx, -EINVAL, "n_samples exceeds stream_stride");
-    if (n_samples > 0xf0000000ull || n_streams > 0xffffffffull || max_frames > 0xffffffffull) return fail(ctx, -EINVAL, "too large");
-    if (n_streams && (!d_iq || !d_n_frames || (max_frames && (!d_frame_start || !d_frame_err || !d_frame_nsym || !d_symbols))))
-        return fail(ctx, -EINVAL, "NULL buffer");
-    std::vector<uint32_t> ids[13];
-    for (size_t s = 0; s < n_streams; ++s) {
-        if (h_sf[s] < 7 || h_sf[s] > 12) return fail(ctx, -EINVAL, "per-stream sf out of range 7..12");
-        ids[h_sf[s]].push_back((uint32_t)s);
-    }
-    if (!n_streams) return 0;
-    CtxGuard g(ctx);
-    CK(ctx->tmp.reserve(n_streams * sizeof(uint32_t)));
-    uint32_t* d_ids = static_cast<uint32_t*>(ctx->tmp.p);
-    size_t off = 0;
-    for (uint32_t sf = 7; sf <= 12; ++sf) {                     // rows of one SF are contiguous in the id list
-        if (ids[sf].empty()) continue;
-        CK(cudaMemcpyAsync(d_ids + off, ids[sf].data(), ids[sf].size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
-        off += ids[sf].size();
-    }
-    CK(cudaStreamSynchronize(ctx->stream));                      // the host vectors go out of scope below
-    off = 0;
-    for (uint32_t sf = 7; sf <= 12; ++sf) {
-        if (ids[sf].empty()) continue;
-        cf* tab = nullptr;
-        int rc = sync_tables(ctx, sf, &tab);
-        if (rc) return rc;
-        const size_t N = (size_t)1 << sf;
-        lk::StreamSyncArgs a;
-        a.iq = static_cast<const cf*>(d_iq); a.stream_stride = stream_stride; a.counts = d_counts;
-        a.n_samples = (uint32_t)n_samples; a.n_streams = (uint32_t)ids[sf].size();
-        a.up = tab; a.down = tab + N; a.fine = tab + 2 * N;
-        a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
-        a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
-        { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
-        a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
-        a.n_frames = d_n_frames; a.end_pos = d_end_pos; a.ids = d_ids + off;
-        CK(lk::launch_stream_sync((int)sf, a, ctx->stream));
-        ++ctx->launches;
-        off += ids[sf].size();
-    }
-    return 0;
+    return detect_streams_common(ctx, h_sf, 0, nullptr, nullptr, sync_word, thresh_db, mtu, d_iq, stream_stride, d_counts,
+                                 n_samples, n_streams, max_frames, d_frame_start, d_frame_err, d_frame_nsym, d_symbols,
+                                 d_n_frames, d_end_pos, nullptr, nullptr);
+}
+
+int lora_phy_cuda_detect_streams_ex(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, const uint8_t* h_bw_scale, const uint8_t* h_osr,
+                                    uint32_t sync_word, float thresh_db, uint32_t mtu, const void* d_iq, size_t stream_stride,
+                                    const uint32_t* d_counts, size_t n_samples, size_t n_streams, size_t max_frames,
+                                    const float* d_cfo, const float* d_time_offset, uint32_t* d_frame_start,
+                                    int32_t* d_frame_err, int32_t* d_frame_nsym, int16_t* d_symbols, uint32_t* d_n_frames,
+                                    uint32_t* d_end_pos)
+{
+    if (!ctx) return -EINVAL;
+    if (!h_sf && n_streams) return fail(ctx, -EINVAL, "h_sf is NULL");
+    return detect_streams_common(ctx, h_sf, 0, h_bw_scale, h_osr, sync_word, thresh_db, mtu, d_iq, stream_stride, d_counts,
+                                 n_samples, n_streams, max_frames, d_frame_start, d_frame_err, d_frame_nsym, d_symbols,
+                                 d_n_frames, d_end_pos, d_cfo, d_time_offset);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -88,6 +88,9 @@ struct StreamSyncArgs {
     const cf* up; const cf* down; const cf* fine;          // LoRaDemod.cpp:96-117 tables (N, N, N*128 entries)
     const cf* tw; const cf* ct; float power_scale;
     uint32_t sync; float thresh; uint32_t mtu; uint32_t max_frames;
+    uint32_t osr, bw_k;                                     // samples per chip (windows are N*osr samples); bandwidth scale 1 / 2 / 4
+    uint32_t sync0, sync1;                                  // (value + 4) / 8 targets of the two sync-word chirps: nibble * bw_k mod N/8
+    const float* comp_cfo; const float* comp_to;            // NULL, or [n_streams] compensate_offsets fused into the window load
     const uint32_t* ids;                                    // NULL, or [n_streams] rows this launch walks (mixed-SF batches)
     int force_serial;                                       // tests: take the literal serial loops (LORA_PHY_STREAM_SERIAL=1)
     uint32_t* frame_start; int32_t* frame_err; int32_t* frame_nsym; int16_t* symbols;   // [n_streams][max_frames]([mtu])

@@ -53,12 +53,13 @@ __device__ __forceinline__ unsigned chirp_value(const ModArgs& a, uint32_t pid, 
 // Constants there are double expressions narrowed to float, f0 = float((2*M_PI*v)/NN), the wrap is all double.
 constexpr double PI_D = 3.14159265358979323846;
 
-__device__ __forceinline__ ChirpConst frame_const(int N, unsigned ovs)
+// bw_k = 1: upstream's constants; 2 / 4: the reference's bandwidth semantics on the same frame (LoRaMod.cpp:24-25,36-37)
+__device__ __forceinline__ ChirpConst frame_const(int N, unsigned ovs, int bw_k)
 {
     ChirpConst c;
-    c.fMin = (float)(-PI_D / (double)(int)ovs);
-    c.fMax = (float)(PI_D / (double)(int)ovs);
-    c.fStep = (float)((2 * PI_D) / (double)(int)(N * ovs * ovs));
+    c.fMin = (float)(-PI_D * (double)bw_k / (double)(int)ovs);
+    c.fMax = (float)(PI_D * (double)bw_k / (double)(int)ovs);
+    c.fStep = (float)((2 * PI_D * (double)bw_k) / (double)(int)(N * ovs * ovs));
     c.span = fx::fsub(c.fMax, c.fMin);
     return c;
 }
@@ -81,7 +82,7 @@ __device__ __forceinline__ ChirpDesc chirp_desc(const ModArgs& a, uint32_t pid, 
     if (s == 10) v = (int)((a.sync >> 4) & 0xf) * 8;
     else if (s == 11) v = (int)(a.sync & 0xf) * 8;
     else if (s >= 15) v = (int)a.symbols[(size_t)pid * a.symbol_stride + (s - 15)];
-    d.f0 = (float)((2 * PI_D * (double)v) / (double)step);
+    d.f0 = (float)((2 * PI_D * (double)v * (double)(int)a.bw_scale) / (double)step);
     return d;
 }
 
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(128) mod_phase_kernel(const ModArgs a)
     if (pid >= a.n_packets) return;
     const int N = 1 << a.sf;
     const uint32_t step = (uint32_t)N * a.osr;
-    const ChirpConst c = a.frame ? frame_const(N, a.osr) : chirp_const(N, a.osr, a.bw_scale);
+    const ChirpConst c = a.frame ? frame_const(N, a.osr, (int)a.bw_scale) : chirp_const(N, a.osr, a.bw_scale);
     const uint32_t chirps = mod_chirps(a);
     float phase = 0.0f;
     float* out = a.phase_scratch + (size_t)pid * chirps;
@@ -129,7 +130,7 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) mod_emit_kernel(const ModArgs
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = 1 << a.sf;
     const uint32_t step = (uint32_t)N * a.osr;
-    const ChirpConst c = a.frame ? frame_const(N, a.osr) : chirp_const(N, a.osr, a.bw_scale);
+    const ChirpConst c = a.frame ? frame_const(N, a.osr, (int)a.bw_scale) : chirp_const(N, a.osr, a.bw_scale);
     const uint32_t chirps = mod_chirps(a);
     const unsigned long long n_chirps = (unsigned long long)a.n_packets * chirps;
     const float amp = a.frame ? a.amplitude : fmaxf(-1.0f, fminf(1.0f, a.amplitude));      // LoRaMod.cpp:18 (upstream: as given)

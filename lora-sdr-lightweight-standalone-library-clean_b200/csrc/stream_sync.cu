@@ -84,8 +84,28 @@ __device__ __forceinline__ double group_dsum(double x, double* redd)
 //  * detector total: the ascending double sum differs from any other summation order by at most
 //    2(N-1)u * total.  If float(total - max) is the same at both ends of that interval (the map is
 //    monotone) the order cannot matter and the tree sum is used.
+// Sample m of the stream as the detector sees it.  Without compensation: iq[m].  With per-stream (cfo, time_offset)
+// (compensate_offsets, phy.cpp:150-180, fused into the load -- no temporary copy of the stream): the reference first
+// rotates sample n by exp(j*rate*n), rate = -2*pi*cfo/(N*osr), then shifts the buffer by round(time_offset) with zero fill,
+// so position m holds the rotated sample m - offset, or zero when that falls outside [0, n).
+struct StreamView {
+    const cf* iq; uint32_t n; float rate; int offset; bool comp;
+};
+__device__ __forceinline__ cf stream_sample(const StreamView& v, uint32_t m)
+{
+    if (!v.comp) return ldg_cf(v.iq + m);
+    const long long k = (long long)m - v.offset;
+    // |offset| >= n: the reference leaves the buffer unshifted (phy.cpp:166,171)
+    const long long idx = ((v.offset > 0 && (uint32_t)v.offset < v.n) || (v.offset < 0 && (uint32_t)(-v.offset) < v.n)) ? k : (long long)m;
+    if (idx < 0 || idx >= (long long)v.n) return fx::mk(0.0f, 0.0f);
+    const cf x = ldg_cf(v.iq + idx);
+    float sn, cs;
+    gm::sincosf_g(fx::fmul(v.rate, (float)(uint32_t)idx), &sn, &cs);
+    return fx::cmul(x, fx::mk(cs, sn));
+}
+
 template <int SF>
-__device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const cf* __restrict__ src, bool live,
+__device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const StreamView& view, uint32_t wpos, bool live,
                                                  const cf* __restrict__ chirp, int idx0, int* ft_out, float fine_err,
                                                  int tid, cf* buf0, cf* buf1, int& flip, int* ftidx, Peak* red,
                                                  double* redd, volatile int* ok_flag)
@@ -138,7 +158,7 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
         const int i = tid + T * c;
         cf x = fx::mk(0.0f, 0.0f);
         if (live) {
-            x = fx::cmul(ldg_cf(src + i), ldg_cf(chirp + i));
+            x = fx::cmul(stream_sample(view, wpos + (uint32_t)i * a.osr), ldg_cf(chirp + i));   // osr > 1: phase 0 of every chip
             x = fx::cmul(x, ldg_cf(a.fine + ci[c]));
         }
         v[c] = x;
@@ -200,7 +220,15 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
     const bool have = slot < a.n_streams;
     const uint32_t sid = have ? (a.ids ? a.ids[slot] : slot) : 0;
     const cf* iq = a.iq + (size_t)(have ? sid : 0) * a.stream_stride;
-    const uint32_t n = have ? (a.counts ? a.counts[sid] : a.n_samples) : 0;
+    const uint32_t n = have ? (a.counts ? min(a.counts[sid], a.n_samples) : a.n_samples) : 0;
+    const uint32_t osr = a.osr, bwk = a.bw_k;
+    StreamView view;
+    view.iq = iq; view.n = n; view.comp = have && a.comp_cfo != nullptr; view.rate = 0.0f; view.offset = 0;
+    if (view.comp) {                                                          // phy.cpp:158-165
+        const float PI_F = 3.14159265358979323846f;
+        view.rate = __fdiv_rn(fx::fmul(-2.0f * PI_F, a.comp_cfo[sid]), fx::fmul((float)N, (float)osr));
+        view.offset = (int)roundf(a.comp_to[sid]);
+    }
 
     // state machine registers (thread 0 of the group)
     int state = ST_FRAMESYNC, prev_value = 0, freq_error = 0, fine_idx = 0, down = 0;
@@ -210,7 +238,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
     for (;;) {
         if (tid == 0) {
             ctl.pos = pos;
-            ctl.live = have && (unsigned long long)pos + 2ull * N <= n;       // LoRaDemod.cpp:148
+            ctl.live = have && (unsigned long long)pos + 2ull * N * osr <= n;  // LoRaDemod.cpp:148
             ctl.down = down;
             ctl.ft = fine_idx;
             ctl.fine_err = fine_err;
@@ -223,7 +251,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
         const float ferr = ctl.fine_err;
         const cf* chirp = ctl.down ? a.down : a.up;
         int ft = ctl.ft;
-        DetectOut d = sync_window<SF>(a, iq + wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, ftidx, red, redd,
+        DetectOut d = sync_window<SF>(a, view, wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, ftidx, red, redd,
                                       &ctl.ok);
         bool squelched = false, syncd = false, match0 = false;
         if (tid == 0 && live) {
@@ -231,7 +259,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
             squelched = d.snr < a.thresh;
             if (state == ST_FRAMESYNC) {                                       // :179-185
                 syncd = !squelched && (prev_value + 4) / 8 == 0;
-                match0 = (unsigned)(d.value + 4) / 8 == (a.sync >> 4);
+                match0 = (unsigned)(d.value + 4) / 8 == a.sync0;
                 if (syncd && match0) { ctl.need2 = 1; ctl.ft2 = ft; }
             }
         }
@@ -240,7 +268,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
         int value1 = 0;
         if (__syncthreads_or(need2)) {                                         // look ahead one window for sync word1 (:188-205)
             int ft2 = 0;                                                       // (a copy: _fineTuneIndex itself is not advanced)
-            DetectOut d1 = sync_window<SF>(a, iq + wpos + N, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
+            DetectOut d1 = sync_window<SF>(a, view, wpos + (uint32_t)N * osr, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
                                            ftidx, red, redd, &ctl.ok);
             if (tid == 0 && need2) { value1 = d1.value; d.findex = d1.findex; }
         }
@@ -248,9 +276,9 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
             uint32_t total = 0;
             switch (state) {
             case ST_FRAMESYNC: {
-                const bool match1 = need2 && (unsigned)(value1 + 4) / 8 == (a.sync & 0xfu);
+                const bool match1 = need2 && (unsigned)(value1 + 4) / 8 == a.sync1;
                 if (syncd && match0 && match1) { total = 2 * N; state = ST_DOWNCHIRP0; down = 1; cur_start = wpos; }
-                else if (!squelched) { total = (uint32_t)(N - d.value); fine_err = fx::fadd(fine_err, d.findex); }
+                else if (!squelched) { total = (uint32_t)(N - d.value / (int)bwk); fine_err = fx::fadd(fine_err, d.findex); }   // bw_k = 1: upstream
                 else { total = N; fine_err = 0.0f; fine_idx = 0; }
             } break;
             case ST_DOWNCHIRP0: {                                              // :240-250
@@ -264,7 +292,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
             } break;
             case ST_QUARTERCHIRP: {                                            // :273-283
                 state = ST_DATASYMBOLS;
-                total = (uint32_t)(N / 4 + freq_error / 2);
+                total = (uint32_t)(N / 4 + (freq_error / 2) / (int)bwk);
                 fine_err = fx::fadd(fine_err, (float)(freq_error / 2));
                 sym_count = 0;
             } break;
@@ -286,7 +314,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
                 }
             } break;
             }
-            pos = wpos + total;
+            pos = wpos + total * osr;
             prev_value = (int)(short)d.value;
         }
     }

@@ -100,6 +100,12 @@ void oracle_stream_tables(unsigned sf, ocplx* up, ocplx* down, ocplx* fine);
 long oracle_stream_demod(unsigned sf, unsigned sync, float thresh, unsigned mtu, const ocplx* iq, size_t n,
                          size_t max_frames, uint32_t* frame_start, int32_t* frame_err, int32_t* frame_nsym,
                          int16_t* symbols, uint32_t* end_pos);
+void oracle_stream_tables_bw(unsigned sf, unsigned bw_k, ocplx* up, ocplx* down, ocplx* fine);
+long oracle_stream_demod_ex(unsigned sf, unsigned osr, unsigned bw_k, unsigned sync, float thresh, unsigned mtu, const ocplx* iq,
+                            size_t n, size_t max_frames, uint32_t* frame_start, int32_t* frame_err, int32_t* frame_nsym,
+                            int16_t* symbols, uint32_t* end_pos);
+size_t oracle_frame_modulate_bw(const uint16_t* symbols, size_t n, ocplx* out, unsigned sf, unsigned ovs, unsigned sync,
+                                float ampl, unsigned padding, unsigned bw_k);
 /* Upstream transmitter frame format (external/LoRa-SDR/LoRaMod.cpp:109-238, ChirpGenerator.hpp:22-47). */
 size_t oracle_frame_samples(unsigned sf, unsigned ovs, size_t n_symbols, unsigned padding);
 size_t oracle_frame_modulate(const uint16_t* symbols, size_t n, ocplx* out, unsigned sf, unsigned ovs, unsigned sync,

@@ -271,7 +271,7 @@ class CpuPhy:
                     length=int(r), flags=fl.value)
 
     # ---- upstream streaming receiver (oracle restatement only) ----------------------------------
-    def stream_demod(self, iq, sf, sync=0x12, thresh=-30.0, mtu=256, max_frames=16):
+    def stream_demod(self, iq, sf, sync=0x12, thresh=-30.0, mtu=256, max_frames=16, osr=1, bw_k=1):
         assert not self.is_ref
         iq = np.ascontiguousarray(iq, dtype=np.complex64)
         start = np.zeros(max_frames, np.uint32)
@@ -279,28 +279,28 @@ class CpuPhy:
         nsym = np.zeros(max_frames, np.int32)
         sym = np.zeros((max_frames, mtu), np.int16)
         end = C.c_uint32(0)
-        f = self.fn("stream_demod", C.c_long, [C.c_uint, C.c_uint, C.c_float, C.c_uint, C.c_void_p, C.c_size_t, C.c_size_t,
-                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)])
-        n = f(sf, sync, thresh, mtu, iq.ctypes.data, iq.size, max_frames, start.ctypes.data, err.ctypes.data,
+        f = self.fn("stream_demod_ex", C.c_long, [C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_float, C.c_uint, C.c_void_p, C.c_size_t,
+                                                  C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)])
+        n = f(sf, osr, bw_k, sync, thresh, mtu, iq.ctypes.data, iq.size, max_frames, start.ctypes.data, err.ctypes.data,
               nsym.ctypes.data, sym.ctypes.data, C.byref(end))
         return int(n), start, err, nsym, sym, end.value
 
-    def stream_tables(self, sf):
+    def stream_tables(self, sf, bw_k=1):
         assert not self.is_ref
         N = 1 << sf
         up, down, fine = np.zeros(N, np.complex64), np.zeros(N, np.complex64), np.zeros(N * 128, np.complex64)
-        self.fn("stream_tables", None, [C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p])(sf, up.ctypes.data, down.ctypes.data,
-                                                                                     fine.ctypes.data)
+        self.fn("stream_tables_bw", None, [C.c_uint, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p])(sf, bw_k, up.ctypes.data,
+                                                                                                  down.ctypes.data, fine.ctypes.data)
         return up, down, fine
 
-    def frame_modulate(self, symbols, sf, ovs=1, sync=0x12, ampl=0.3, padding=1):
+    def frame_modulate(self, symbols, sf, ovs=1, sync=0x12, ampl=0.3, padding=1, bw_k=1):
         assert not self.is_ref
         symbols = np.ascontiguousarray(symbols, dtype=np.uint16)
         n = self.fn("frame_samples", C.c_size_t, [C.c_uint, C.c_uint, C.c_size_t, C.c_uint])(sf, ovs, symbols.size, padding)
         out = np.zeros(n, np.complex64)
-        f = self.fn("frame_modulate", C.c_size_t, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_uint, C.c_uint, C.c_uint,
-                                                   C.c_float, C.c_uint])
-        got = f(symbols.ctypes.data, symbols.size, out.ctypes.data, sf, ovs, sync, ampl, padding)
+        f = self.fn("frame_modulate_bw", C.c_size_t, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_uint, C.c_uint, C.c_uint,
+                                                      C.c_float, C.c_uint, C.c_uint])
+        got = f(symbols.ctypes.data, symbols.size, out.ctypes.data, sf, ovs, sync, ampl, padding, bw_k)
         assert got == n
         return out
 
