@@ -233,7 +233,7 @@ def also_stream(phy, lp, torch, peak, sf, gbytes=4.0, symbols=32, steps=3):
     return rec
 
 
-def also_stream_mixed(phy, lp, torch, peak, gbytes=3.0, symbols=24, steps=3):
+def also_stream_mixed(phy, lp, torch, peak, gbytes=6.0, symbols=24, steps=3):
     """BASELINE configs[3] shape: ONE batch of continuous streams that differ in SF (7..12), bandwidth (the reference's
     bw_scale semantics) and oversampling, frames in the upstream format back to back with a per-stream carrier offset,
     through lora_phy_cuda_detect_streams_ex (one launch per distinct (sf, bw, osr))."""
@@ -241,7 +241,7 @@ def also_stream_mixed(phy, lp, torch, peak, gbytes=3.0, symbols=24, steps=3):
     import numpy as np
     groups = [(sf, k, osr) for sf in range(7, 13) for (k, osr) in ((1, 1), (2, 1), (1, 2), (1, 4))]
     per_group = gbytes * 1e9 / 8 / len(groups)
-    n_row = 1 << 17
+    n_row = max((14 + symbols + 2 + 3) * (1 << sf) * osr + (1 << sf) * osr // 4 for sf, k, osr in groups)   # the longest frame fits a row
     g = torch.Generator(device=phy.device).manual_seed(0xC0FFEE)
     rows, sfs, bws, osrs, counts, want = [], [], [], [], [], []
     for sf, k, osr in groups:

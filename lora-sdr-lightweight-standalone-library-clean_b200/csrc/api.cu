@@ -81,6 +81,10 @@ struct lora_phy_cuda_ctx {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_h2d[2] = { nullptr, nullptr }, ev_done[2] = { nullptr, nullptr }, ev_start = nullptr;
     size_t host_chunk_bytes = (size_t)64 << 20;         // LORA_PHY_HOST_CHUNK_MB
+    // mixed stream batches: one launch per (sf, bandwidth, osr) group, each a small grid of sequential walkers -- the groups
+    // run side by side on these streams and join the context's stream at the end
+    cudaStream_t side[8] = {};
+    cudaEvent_t side_done[8] = {}, side_start = nullptr;
     std::recursive_mutex mu;                            // held for a whole entry point (staging buffers, scratch, err)
 };
 
@@ -209,6 +213,11 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
         if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
     }
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    for (int i = 0; i < 8; ++i) {
+        if (ctx->side_done[i]) cudaEventDestroy(ctx->side_done[i]);
+        if (ctx->side[i]) cudaStreamDestroy(ctx->side[i]);
+    }
+    if (ctx->side_start) cudaEventDestroy(ctx->side_start);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -811,7 +820,23 @@ static int detect_streams_common(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, ui
         }
         CK(cudaStreamSynchronize(ctx->stream));                    // the host vectors go out of scope below
     }
-    size_t off = 0;
+    if (!one_group && !ctx->side_start) {
+        CK(cudaEventCreateWithFlags(&ctx->side_start, cudaEventDisableTiming));
+        for (int i = 0; i < 8; ++i) {
+            CK(cudaStreamCreateWithFlags(&ctx->side[i], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&ctx->side_done[i], cudaEventDisableTiming));
+        }
+    }
+    for (auto& kv : groups) {                                       // tables first: building one synchronises the stream
+        cf* tab = nullptr;
+        int rc = sync_tables(ctx, (uint32_t)std::get<0>(kv.first), (uint32_t)std::get<1>(kv.first), &tab);
+        if (rc) return rc;
+    }
+    if (!one_group) {
+        CK(cudaEventRecord(ctx->side_start, ctx->stream));
+        for (int i = 0; i < 8; ++i) CK(cudaStreamWaitEvent(ctx->side[i], ctx->side_start, 0));
+    }
+    size_t off = 0, gi = 0;
     for (auto& kv : groups) {
         const uint32_t sf = (uint32_t)std::get<0>(kv.first), k = (uint32_t)std::get<1>(kv.first), osr = (uint32_t)std::get<2>(kv.first);
         cf* tab = nullptr;
@@ -831,9 +856,16 @@ static int detect_streams_common(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, ui
         { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
         a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
         a.n_frames = d_n_frames; a.end_pos = d_end_pos; a.ids = one_group ? nullptr : d_ids + off;
-        CK(lk::launch_stream_sync((int)sf, a, ctx->stream));
+        CK(lk::launch_stream_sync((int)sf, a, one_group ? ctx->stream : ctx->side[gi % 8]));
         ++ctx->launches;
         off += kv.second.size();
+        ++gi;
+    }
+    if (!one_group) {
+        for (int i = 0; i < 8; ++i) {
+            CK(cudaEventRecord(ctx->side_done[i], ctx->side[i]));
+            CK(cudaStreamWaitEvent(ctx->stream, ctx->side_done[i], 0));
+        }
     }
     return 0;
 }

@@ -104,7 +104,7 @@ __device__ __forceinline__ cf stream_sample(const StreamView& v, uint32_t m)
     return fx::cmul(x, fx::mk(cs, sn));
 }
 
-template <int SF>
+template <int SF, bool EX>
 __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const StreamView& view, uint32_t wpos, bool live,
                                                  const cf* __restrict__ chirp, int idx0, int* ft_out, float fine_err,
                                                  int tid, cf* buf0, cf* buf1, int& flip, int* ftidx, Peak* red,
@@ -158,7 +158,8 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
         const int i = tid + T * c;
         cf x = fx::mk(0.0f, 0.0f);
         if (live) {
-            x = fx::cmul(stream_sample(view, wpos + (uint32_t)i * a.osr), ldg_cf(chirp + i));   // osr > 1: phase 0 of every chip
+            // EX: oversampled and / or compensated stream (osr > 1: phase 0 of every chip); else the plain one-sample-per-chip load
+            x = fx::cmul(EX ? stream_sample(view, wpos + (uint32_t)i * a.osr) : ldg_cf(view.iq + wpos + i), ldg_cf(chirp + i));
             x = fx::cmul(x, ldg_cf(a.fine + ci[c]));
         }
         v[c] = x;
@@ -199,7 +200,7 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     return o;
 }
 
-template <int SF>
+template <int SF, bool EX>
 __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const StreamSyncArgs a)
 {
     using P = fx::Plan<SF>;
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
     const uint32_t sid = have ? (a.ids ? a.ids[slot] : slot) : 0;
     const cf* iq = a.iq + (size_t)(have ? sid : 0) * a.stream_stride;
     const uint32_t n = have ? (a.counts ? min(a.counts[sid], a.n_samples) : a.n_samples) : 0;
-    const uint32_t osr = a.osr, bwk = a.bw_k;
+    const uint32_t osr = EX ? a.osr : 1u, bwk = EX ? a.bw_k : 1u;
     StreamView view;
     view.iq = iq; view.n = n; view.comp = have && a.comp_cfo != nullptr; view.rate = 0.0f; view.offset = 0;
     if (view.comp) {                                                          // phy.cpp:158-165
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
         const float ferr = ctl.fine_err;
         const cf* chirp = ctl.down ? a.down : a.up;
         int ft = ctl.ft;
-        DetectOut d = sync_window<SF>(a, view, wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, ftidx, red, redd,
+        DetectOut d = sync_window<SF, EX>(a, view, wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, ftidx, red, redd,
                                       &ctl.ok);
         bool squelched = false, syncd = false, match0 = false;
         if (tid == 0 && live) {
@@ -268,7 +269,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
         int value1 = 0;
         if (__syncthreads_or(need2)) {                                         // look ahead one window for sync word1 (:188-205)
             int ft2 = 0;                                                       // (a copy: _fineTuneIndex itself is not advanced)
-            DetectOut d1 = sync_window<SF>(a, view, wpos + (uint32_t)N * osr, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
+            DetectOut d1 = sync_window<SF, EX>(a, view, wpos + (uint32_t)N * osr, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
                                            ftidx, red, redd, &ctl.ok);
             if (tid == 0 && need2) { value1 = d1.value; d.findex = d1.findex; }
         }
@@ -328,9 +329,15 @@ template <int SF>
 cudaError_t launch_sync_sf(const StreamSyncArgs& a, cudaStream_t stream)
 {
     using S = SyncSmem<SF>;
-    cudaFuncSetAttribute(stream_sync_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
+    const bool ex = a.osr != 1 || a.bw_k != 1 || a.comp_cfo != nullptr;
     const unsigned grid = (a.n_streams + S::G - 1) / S::G;
-    stream_sync_kernel<SF><<<grid, CTA_THREADS, S::bytes, stream>>>(a);
+    if (ex) {
+        cudaFuncSetAttribute(stream_sync_kernel<SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
+        stream_sync_kernel<SF, true><<<grid, CTA_THREADS, S::bytes, stream>>>(a);
+    } else {
+        cudaFuncSetAttribute(stream_sync_kernel<SF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
+        stream_sync_kernel<SF, false><<<grid, CTA_THREADS, S::bytes, stream>>>(a);
+    }
     return cudaGetLastError();
 }
 
