@@ -1,3 +1,12 @@
+// SPDX-License-Identifier: LGPL-2.1-or-later
+// Attribution: the algorithms, polynomial coefficients and tables below restate functions of the GNU C Library 2.39
+// (sysdeps/ieee754/flt-32/{s_sinf,s_cosf,s_sincosf,sincosf.h,e_logf,e_log10f,s_atanf,e_atan2f}.c, sysdeps/ieee754/dbl-64/
+// e_hypotf-style hypotf), Copyright (C) Free Software Foundation, Inc., distributed under the GNU Lesser General
+// Public License v2.1 or later; atanf/atan2f/log10f descend from fdlibm, Copyright (C) 1993 Sun Microsystems, Inc.
+// ("Permission to use, copy, modify, and distribute this software is freely granted, provided that this notice is
+// preserved").  This file is a derived work of that material and carries the same licence; it is third-party-derived,
+// not reference-derived (the reference only CALLS libm).
+//
 // glibc_math.cuh -- device restatements of the glibc 2.39 libm entry points the
 // reference's hot path resolves to (SURVEY.md section 1, L0 "Below" column):
 //
