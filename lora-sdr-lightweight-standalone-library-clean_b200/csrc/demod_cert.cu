@@ -29,6 +29,7 @@
 #include <cstdlib>
 #include "stream_common.cuh"
 #include "fft_fast.cuh"
+#include "fft_soa.cuh"
 #include "internal.h"
 
 namespace lk {
@@ -43,6 +44,22 @@ namespace lk {
 
 #ifndef CERT_TW0_SMEM_MAX_SF
 #define CERT_TW0_SMEM_MAX_SF 0                // pass-0 twiddles in shared memory up to this SF (A/B knob; registers measured faster)
+#endif
+
+#ifndef CERT_SOA_SF7
+#define CERT_SOA_SF7 1                        // SF7: struct-of-arrays packed transform (fft_soa.cuh); 0 = the AoS code of fft_fast.cuh (A/B)
+#endif
+
+#ifndef CERT_SOA_TW_SMEM
+#define CERT_SOA_TW_SMEM 0                    // SF7 SoA path: pass-0 twiddle pairs from shared memory instead of 32 registers (A/B knob)
+#endif
+
+#ifndef CERT_EARLY_REFILL
+#define CERT_EARLY_REFILL 0                   // warp pipelines: refill at the top of the step (needs an end-of-step __syncwarp), A/B knob
+#endif
+
+#ifndef CERT_L2_AHEAD
+#define CERT_L2_AHEAD 0                       // steps ahead of the walk that are pulled into L2 (0 = off); see the walk loop
 #endif
 
 constexpr int CERT_CAP = 512;                 // symbols per packet the fallback bitmap / symbol staging cover (255-byte payload
@@ -77,7 +94,7 @@ struct CertCfg {
     // pass-0 twiddles W_N^{tid*k}: a [16][T] table in shared memory for SF7-9 (15 conflict-free 64-bit loads per window
     // instead of 30 registers for the kernel's lifetime -- the loop is register-bound there), registers for SF10-12
     static constexpr bool TW0_SMEM = SF <= CERT_TW0_SMEM_MAX_SF;
-    static constexpr size_t tw0_bytes = TW0_SMEM ? (size_t)N * sizeof(cf) : 0;
+    static constexpr size_t tw0_bytes = (TW0_SMEM || (SF == 7 && CERT_SOA_SF7 && CERT_SOA_TW_SMEM)) ? (size_t)N * sizeof(cf) : 0;
     static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + 256;
     // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
     static constexpr int fit = (int)(((size_t)227 * 1024 / CERT_CTAS_PER_SM - 1024 - fixed_bytes) / stage_bytes);
@@ -205,6 +222,32 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             tw0[k] = fx::mk((float)cs, (float)sn);
         }
     }
+    constexpr bool SOA = SF == 7 && CERT_SOA_SF7 != 0;
+    fs::P2 twr[8], twi[8];                         // SOA: pass-0 twiddle pairs (W^{tid*2q}, W^{tid*(2q+1)})
+    constexpr bool SOA_TWS = SOA && CERT_SOA_TW_SMEM != 0;
+    unsigned long long* twp = reinterpret_cast<unsigned long long*>(smem_raw + C::tw0_off);   // [plane][q][t] pairs
+    if (SOA_TWS) {
+        for (int j = threadIdx.x; j < 64; j += CTA) {
+            const int q = j >> 3, t = j & 7;
+            double s0, c0, s1, c1;
+            sincospi(-2.0 * (double)((t * 2 * q) & (N - 1)) / (double)N, &s0, &c0);
+            sincospi(-2.0 * (double)((t * (2 * q + 1)) & (N - 1)) / (double)N, &s1, &c1);
+            twp[j] = fs::bits(fs::mk2((float)c0, (float)c1));
+            twp[64 + j] = fs::bits(fs::mk2((float)s0, (float)s1));
+        }
+    }
+    if (SOA && !SOA_TWS) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            double s0, c0, s1, c1;
+            sincospi(-2.0 * (double)((tid * 2 * q) & (N - 1)) / (double)N, &s0, &c0);
+            sincospi(-2.0 * (double)((tid * (2 * q + 1)) & (N - 1)) / (double)N, &s1, &c1);
+            twr[q] = fs::mk2((float)c0, (float)c1);
+            twi[q] = fs::mk2((float)s0, (float)s1);
+        }
+    }
+    const fs::P2 soa_s = fs::mk2(0.70710678118654752440f, 0.70710678118654752440f);
+    const fs::P2 soa_ns = fs::mk2(-0.70710678118654752440f, -0.70710678118654752440f);
     const int wr0 = F::wr_base(0, tid), rd0 = F::rd_base(0, tid);
     const int wr1 = NP == 3 ? F::wr_base(1, tid) : 0, rd1 = NP == 3 ? F::rd_base(1, tid) : 0;
     const int ir1 = NP == 3 ? F::i_rest(1, tid) : 0;
@@ -420,13 +463,29 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 // The slot refilled during this step is the one the PREVIOUS step consumed.  Its refill is issued after
                 // this step's first barrier: a thread that has reached that barrier has finished the previous step (its
                 // last generic-proxy store there is followed by fence.proxy.async), so no end-of-step barrier is needed.
-                auto refill = [&]() {
+                constexpr bool EARLY = CERT_EARLY_REFILL != 0 && DT <= 32;
+                auto refill_now = [&]() {
                     if (tid == 0) {
                         int stg = stage + (STAGES - 1);
                         if (stg >= STAGES) stg -= STAGES;
                         if (u + (STAGES - 1) < n_units) prefetch(s + (STAGES - 1) * GD, stg);
                     }
                 };
+                auto refill = [&]() { if (!EARLY) refill_now(); };
+                // The ring holds one or two steps per pipeline -- 64 KB in flight per SM with 16 warps, short of what the HBM
+                // latency-bandwidth product asks for (~100 KB per SM).  One lane therefore pulls the windows CERT_L2_AHEAD steps
+                // ahead (this packet's, or the first ones of the pipeline's next packet) into L2 with a bulk prefetch: no
+                // shared memory, nothing to wait for, and the ring's own copies then complete at L2 latency.
+                if (CERT_L2_AHEAD > 0 && lane == 0) {
+                    const uint32_t v = u + CERT_L2_AHEAD;
+                    const cf* src = nullptr;
+                    if (v < n_units) src = pkt + (size_t)v * GD * N;
+                    else if ((unsigned long long)pid + n_pipes < a.n_packets && v - n_units < n_units)
+                        src = pkt + (size_t)n_pipes * a.packet_stride + (size_t)(v - n_units) * GD * N;
+                    if (src) ptx::bulk_prefetch_l2(reinterpret_cast<const void*>(reinterpret_cast<uintptr_t>(src) & ~(uintptr_t)15),
+                                                   (unsigned)(GD * N * sizeof(cf)));
+                }
+                if (EARLY) refill_now();
                 const bool active = s < total;
                 if (!regular) {
                     const uint32_t base = shifted_base(s, (uint32_t)N, t_off, count);
@@ -451,6 +510,46 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 if (active) m = fmaxf(m, mw);
                 float en = (e0.x + e0.y) + (e1.x + e1.y);
 
+                unsigned key[16];
+#if defined(CERT_ABLATE)
+                // measurement-only build (tools/ablate_cert.sh, never the product): the walk without its transform -- what the
+                // streaming skeleton (ring, rotation, max / energy tracking, keys, reductions, bookkeeping) costs on its own
+#pragma unroll
+                for (int e = 0; e < 16; ++e) key[e] = key_of(ff::fnorm(v[e]), keymask, e);
+                if (false) {
+#else
+                if constexpr (SOA) {
+#endif
+                    // struct-of-arrays transform (fft_soa.cuh): every butterfly / twiddle / modulus op is packed over two points
+                    fs::P2 pr[8], pi[8];
+                    fs::pass0_r16(v, pr, pi, soa_s, soa_ns);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        if (SOA_TWS) fs::cmul(pr[q], pi[q], fs::from_bits(twp[8 * q + tid]), fs::from_bits(twp[64 + 8 * q + tid]));
+                        else fs::cmul(pr[q], pi[q], twr[q], twi[q]);
+                    }
+                    unsigned long long* ex = reinterpret_cast<unsigned long long*>(win);
+                    group_sync<T>();                           // every thread of the window has its raw samples
+                    refill();
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        ex[fs::sf7_wr(0, q) + tid] = fs::bits(pr[q]);
+                        ex[fs::SF7_PLANE + fs::sf7_wr(0, q) + tid] = fs::bits(pi[q]);
+                    }
+                    group_sync<T>();
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        pr[r] = fs::from_bits(ex[9 * tid + r]);
+                        pi[r] = fs::from_bits(ex[fs::SF7_PLANE + 9 * tid + r]);
+                    }
+                    fs::dft8(pr, pi, soa_s, soa_ns);
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        const fs::P2 q2 = fs::norm2(pr[r], pi[r]);
+                        key[r] = key_of(fs::lo(q2), keymask, r);          // bin 2 tid + 16 r
+                        key[r + 8] = key_of(fs::hi(q2), keymask, r + 8);  // bin 2 tid + 1 + 16 r
+                    }
+                } else {
                 // pass 0 in registers, twiddle, exchange(s) in the window's own slot
                 ff::dft16(v);
 #pragma unroll
@@ -485,9 +584,9 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 }
 
                 // |Y|^2 keyed with the register index in the low four mantissa bits; top key of the window
-                unsigned key[16];
 #pragma unroll
                 for (int e = 0; e < 16; ++e) key[e] = key_of(ff::fnorm(v[e]), keymask, e);
+                }
                 unsigned kloc = 0u;
 #pragma unroll
                 for (int e = 0; e < 16; e += 2) kloc = umax3(kloc, key[e], key[e + 1]);
@@ -510,6 +609,9 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 const float q1 = __uint_as_float(kmax & ~15u);
                 // tier 1: the top bin holds more than 3/4 of N*E (Parseval: every other bin is below half its modulus)
                 bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
+#if defined(CERT_ABLATE)
+                cert = true;
+#endif
                 // (a window that is the whole pipeline needs no vote: cert is uniform across it)
                 if (GD == 1 ? (!cert && active) : cany<DT>(!cert && active)) {
                     // tier 2: the true second maximum of the window.  Keys inside a thread are distinct (register index in
@@ -546,8 +648,9 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     if (kloc == kmax) {                                    // the lane that holds the top bin
                         if (cert) {
                             const unsigned e = kmax & 15u;
-                            const int idx = bin0 + ((e & 1u) ? F::bin_off(1) : 0) + ((e & 2u) ? F::bin_off(2) : 0) +
-                                            ((e & 4u) ? F::bin_off(4) : 0) + ((e & 8u) ? F::bin_off(8) : 0);
+                            const int idx = SOA ? fs::sf7_bin(tid, (int)(e & 7u), (int)(e >> 3))
+                                                : bin0 + ((e & 1u) ? F::bin_off(1) : 0) + ((e & 2u) ? F::bin_off(2) : 0) +
+                                                  ((e & 4u) ? F::bin_off(4) : 0) + ((e & 8u) ? F::bin_off(8) : 0);
                             if (have_sync && s < 2) ws.sw[s] = idx;
                             else ws.sym[have_sync ? s - 2 : s] = (uint16_t)idx;
                         } else {
@@ -556,6 +659,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     }
                 }
                 ptx::fence_proxy_async();                      // this thread's stores to the slot precede its next refill
+                if (EARLY) csync<DT>();
                 stage = stage + 1 == STAGES ? 0 : stage + 1;
             }
             csync<DT>();                                       // the last step's slot and staging cells are settled

@@ -85,6 +85,12 @@ __device__ __forceinline__ void sts_cf_sa(uint32_t dst, float x, float y)
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(dst), "f"(x), "f"(y) : "memory");
 }
 
+// hint: bring [src, src + bytes) into L2 (no shared memory, no completion to wait for); bytes multiple of 16, src 16-byte aligned
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src_gmem, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
+
 // bytes: multiple of 16; dst (shared) and src (global) 16-byte aligned
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, uint64_t* bar)
 {

@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <vector>
 #include "fft_fast.cuh"
+#include "fft_soa.cuh"
 
 using ff::cf;
 
@@ -147,9 +148,94 @@ static bool run(unsigned seed)
     return ok;
 }
 
+// The SF7 struct-of-arrays path (fft_soa.cuh): pass 0 on lanes (s_e, d_e), packed twiddle, pair exchange in two planes,
+// packed pass 1 -- same checks as above for a CTA of 32 windows x 8 threads with the kernel's window pitch.
+static bool run_soa7(unsigned seed)
+{
+    constexpr int N = 128, T = 8, CTA = 256, G = CTA / T, PITCH = ff::Plan<7>::pitch();
+    const double PI = 3.14159265358979323846;
+    bool ok = true;
+    int worst = 1;
+    srand(seed);
+    std::vector<std::complex<double>> x((size_t)G * N);
+    for (auto& z : x) z = { (double)rand() / RAND_MAX - 0.5, (double)rand() / RAND_MAX - 0.5 };
+    for (int i = 0; i < N; ++i) x[i] = std::polar(1.0, 2 * PI * 37.0 * i / N);
+    std::vector<fs::P2> R((size_t)G * T * 8), I((size_t)G * T * 8);
+    std::vector<fs::P2> sm((size_t)G * PITCH);
+    std::vector<int> written((size_t)G * PITCH, 0);
+    const fs::P2 S = fs::mk2(0.70710678118654752440f, 0.70710678118654752440f), NS = fs::mk2(-0.70710678118654752440f, -0.70710678118654752440f);
+    for (int g = 0; g < G; ++g)
+        for (int t = 0; t < T; ++t) {
+            cf y[16];
+            for (int c = 0; c < 16; ++c) y[c] = ff::mk((float)x[(size_t)g * N + t + T * c].real(), (float)x[(size_t)g * N + t + T * c].imag());
+            fs::P2 r[8], im[8];
+            fs::pass0_r16(y, r, im, S, NS);
+            for (int q = 0; q < 8; ++q) {
+                const double a0 = -2 * PI * (double)((t * 2 * q) % N) / N, a1 = -2 * PI * (double)((t * (2 * q + 1)) % N) / N;
+                fs::cmul(r[q], im[q], fs::mk2((float)cos(a0), (float)cos(a1)), fs::mk2((float)sin(a0), (float)sin(a1)));
+                R[((size_t)g * T + t) * 8 + q] = r[q];
+                I[((size_t)g * T + t) * 8 + q] = im[q];
+            }
+        }
+    for (int plane = 0; plane < 2; ++plane)
+        for (int q = 0; q < 8; ++q) {
+            std::vector<long> addr(CTA, -1);
+            for (int g = 0; g < G; ++g)
+                for (int t = 0; t < T; ++t) {
+                    const int a = plane * fs::SF7_PLANE + fs::sf7_wr(t, q);
+                    if (a >= PITCH || written[(size_t)g * PITCH + a]++) ok = false;
+                    addr[g * T + t] = (long)g * PITCH + a;
+                    sm[(size_t)g * PITCH + a] = (plane ? I : R)[((size_t)g * T + t) * 8 + q];
+                }
+            worst = std::max(worst, worst_conflict(addr));
+        }
+    double max_rel = 0.0;
+    for (int plane = 0; plane < 2; ++plane)
+        for (int r = 0; r < 8; ++r) {
+            std::vector<long> addr(CTA, -1);
+            for (int g = 0; g < G; ++g)
+                for (int t = 0; t < T; ++t) {
+                    const int a = plane * fs::SF7_PLANE + fs::sf7_rd(t, r);
+                    if (a >= PITCH || written[(size_t)g * PITCH + a] != 1) ok = false;
+                    written[(size_t)g * PITCH + a] = 2;
+                    addr[g * T + t] = (long)g * PITCH + a;
+                    (plane ? I : R)[((size_t)g * T + t) * 8 + r] = sm[(size_t)g * PITCH + a];
+                }
+            worst = std::max(worst, worst_conflict(addr));
+        }
+    for (int g = 0; g < G; ++g) {
+        std::vector<std::complex<double>> X(N);
+        std::vector<int> hit(N, 0);
+        double peak = 0.0;
+        for (int k = 0; k < N; ++k) {
+            std::complex<double> acc = 0;
+            for (int i = 0; i < N; ++i) acc += x[(size_t)g * N + i] * std::polar(1.0, -2 * PI * (double)((long)i * k % N) / N);
+            X[k] = acc;
+            peak = std::max(peak, std::abs(acc));
+        }
+        for (int t = 0; t < T; ++t) {
+            fs::P2 r[8], im[8];
+            for (int q = 0; q < 8; ++q) { r[q] = R[((size_t)g * T + t) * 8 + q]; im[q] = I[((size_t)g * T + t) * 8 + q]; }
+            fs::dft8(r, im, S, NS);
+            for (int q = 0; q < 8; ++q)
+                for (int lane = 0; lane < 2; ++lane) {
+                    const int bin = fs::sf7_bin(t, q, lane);
+                    if (bin < 0 || bin >= N || hit[bin]++) { ok = false; continue; }
+                    const std::complex<double> y(lane ? fs::hi(r[q]) : fs::lo(r[q]), lane ? fs::hi(im[q]) : fs::lo(im[q]));
+                    max_rel = std::max(max_rel, std::abs(y - X[bin]) / peak);
+                }
+        }
+    }
+    if (max_rel > 2e-6 || worst != 1) ok = false;
+    std::printf("{\"sf\": 7, \"layout\": \"soa pairs\", \"pitch\": %d, \"max_rel_err\": %.3g, \"worst_bank_conflict\": %d, \"match\": %s}\n", PITCH,
+                max_rel, worst, ok ? "true" : "false");
+    return ok;
+}
+
 int main()
 {
     bool ok = true;
+    ok &= run_soa7(7);
     ok &= run<7>(1);
     ok &= run<8>(2);
     ok &= run<9>(3);

@@ -37,3 +37,14 @@ def test_glibc_math_restatement():
     exe = compile_cpp("test_glibc_math", ["-lm"])
     r = subprocess.run([exe, "1031"], capture_output=True, text=True, timeout=600)   # ~4.2 M arguments per function
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_fft_fast_emulation():
+    """csrc/fft_fast.cuh and fft_soa.cuh (the certified path's throughput transform) emulated thread by thread: spectrum
+    within 2e-6 of a double DFT, every exchange address written once and read once inside the window slot, every 64-bit
+    access phase bank-conflict free, output bin map a permutation -- SF7 (both register layouts) to SF12."""
+    exe = compile_cpp("test_fft_fast_emulation", ["-lm"])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 7 and all(l["match"] and l["worst_bank_conflict"] == 1 for l in lines)

@@ -25,3 +25,11 @@ $NVCC $FLAGS -DLORA_ABLATE_FFT -DLORA_ABLATE_SINCOS -c "$C/demod_packet.cu" -o "
 $NVCC -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o "$OUT/liblora_neither.so" \
     "$OUT/demod_packet_neither.o" $(ls "$C"/build/*.o | grep -v '/demod_packet.o$')
 echo "built $OUT/liblora_neither.so"
+# certified demodulator (round 2): the walk without its transform (keys taken from the rotated samples, every window
+# counted as certified) -- the streaming skeleton's own cost at the product's occupancy
+for v in noxform; do
+  $NVCC $FLAGS -DCERT_ABLATE=1 -c "$C/demod_cert.cu" -o "$OUT/demod_cert_$v.o"
+  $NVCC -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o "$OUT/liblora_cert_$v.so" \
+      "$OUT/demod_cert_$v.o" $(ls "$C"/build/*.o | grep -v '/demod_cert.o$')
+  echo "built $OUT/liblora_cert_$v.so"
+done
