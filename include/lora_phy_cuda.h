@@ -162,6 +162,23 @@ long lora_phy_cuda_modulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cf
                                   const uint16_t* d_symbols, size_t symbol_stride,
                                   size_t symbols_per_packet, size_t n_packets,
                                   void* d_iq, size_t packet_stride);
+/* Allocation-free variant of lora_phy_cuda_modulate_batch.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same output bit for bit; the only difference is where the modulator keeps its
+ * per-chirp start phases: a static device array inside the library (4 MiB on every GPU that loads it, held until
+ * exit) instead of the context's growable buffer.  The call performs no cudaMalloc / cudaFree / allocating library
+ * routine.
+ *   limit   n_packets * (symbols_per_packet + 2) <= LORA_PHY_CUDA_STATIC_MAX_CHIRPS, else -E2BIG with
+ *           lora_phy_cuda_last_error() naming the limit (nothing is launched).
+ *   sharing every call on a device -- from any context or thread -- uses the SAME array: calls whose kernels may
+ *           overlap on the GPU (different streams, different contexts) race on it and must be ordered by the
+ *           caller.  The array keeps the previous call's contents; the modulator overwrites every entry it reads,
+ *           so nothing has to be cleared between calls.                                                          */
+#define LORA_PHY_CUDA_STATIC_MAX_CHIRPS 1048576u
+long lora_phy_cuda_modulate_batch_static(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
+                                         const uint16_t* d_symbols, size_t symbol_stride,
+                                         size_t symbols_per_packet, size_t n_packets,
+                                         void* d_iq, size_t packet_stride);
 long lora_phy_cuda_modulate_batch_host(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg,
                                        const uint16_t* h_symbols, size_t symbol_stride,
                                        size_t symbols_per_packet, size_t n_packets,

@@ -21,6 +21,7 @@ F_ONLY_PREPASS = 0x10
 F_ONLY_SYMBOLS = 0x20
 F_TWO_KERNEL = 0x80
 F_EXACT = 0x100
+STATIC_MAX_CHIRPS = 1 << 20        # LORA_PHY_CUDA_STATIC_MAX_CHIRPS
 
 
 class Cfg(C.Structure):
@@ -79,6 +80,7 @@ SIGNATURES = {
     "lora_phy_cuda_detect_batch": (C.c_int, [_vp, _u32, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_modulate_batch": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_modulate_batch_host": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
+    "lora_phy_cuda_modulate_batch_static": (C.c_long, [_vp, _cfgp, _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_tx_batch": (C.c_long, [_vp, _cfgp, C.POINTER(ChainCfg), _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_tx_batch_host": (C.c_long, [_vp, _cfgp, C.POINTER(ChainCfg), _vp, _sz, _sz, _sz, _vp, _sz]),
     "lora_phy_cuda_rx_batch": (C.c_int, [_vp, _cfgp, C.POINTER(ChainCfg), _vp, _sz, _sz, _sz, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
@@ -262,6 +264,14 @@ class LoraPhyCuda:
             iq = t.empty((P, n), dtype=t.complex64, device=self.device)
         self._check(self.lib.lora_phy_cuda_modulate_batch(self.h, C.byref(cfg), _ptr(symbols), symbols.stride(0), S, P,
                                                           _ptr(iq), iq.stride(0)))
+        return iq
+
+    def modulate_batch_static(self, cfg, symbols, iq):
+        """lora_phy_cuda_modulate_batch_static: allocation-free (static device scratch, at most STATIC_MAX_CHIRPS chirps
+        per call); the caller passes the output.  No counterpart in the reference."""
+        P, S = symbols.shape
+        self._check(self.lib.lora_phy_cuda_modulate_batch_static(self.h, C.byref(cfg), _ptr(symbols), symbols.stride(0), S, P,
+                                                                 _ptr(iq), iq.stride(0)))
         return iq
 
     def modulate_frames_batch(self, cfg, symbols, padding=1, iq=None):

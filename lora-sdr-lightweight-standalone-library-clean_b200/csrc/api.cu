@@ -577,6 +577,42 @@ long lora_phy_cuda_modulate_batch(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cf
     return (long)produced;
 }
 
+// Allocation-free variant (no counterpart in the reference; include/lora_phy_cuda.h): the phases live in modcodes.cu's
+// static device array, nothing here or below allocates.
+long lora_phy_cuda_modulate_batch_static(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, const uint16_t* d_symbols,
+                                         size_t symbol_stride, size_t spp_sym, size_t n_packets, void* d_iq,
+                                         size_t packet_stride)
+{
+    int rc = check_cfg(ctx, cfg);
+    if (rc) return rc;
+    if ((!d_symbols && spp_sym && n_packets) || (!d_iq && n_packets)) return fail(ctx, -EINVAL, "NULL buffer");
+    if (spp_sym > symbol_stride && n_packets > 1) return fail(ctx, -EINVAL, "symbols_per_packet exceeds symbol_stride");
+    const size_t produced = (spp_sym + 2) * ((size_t)1 << cfg->sf) * cfg->osr;
+    if (produced > packet_stride) return fail(ctx, -ERANGE, "packet_stride smaller than (symbols+2)*N*osr");
+    if (!n_packets) return (long)produced;
+    if (n_packets > 0xffffffffull || spp_sym > 0xfffffffdull ||
+        n_packets > (size_t)LORA_PHY_CUDA_STATIC_MAX_CHIRPS / (spp_sym + 2))
+        return fail(ctx, -E2BIG, "modulate_batch_static: n_packets * (symbols_per_packet + 2) exceeds "
+                                 "LORA_PHY_CUDA_STATIC_MAX_CHIRPS (1048576); split the batch or use lora_phy_cuda_modulate_batch");
+    CtxGuard g(ctx);
+    float* phases = nullptr;
+    cudaError_t e = lk::mod_static_scratch(&phases);          // cudaGetSymbolAddress, once per device, this device current
+    if (e != cudaSuccess) return fail(ctx, -EIO, "cudaGetSymbolAddress(static modulator scratch)", e);
+    lk::ModArgs a;
+    a.symbols = d_symbols; a.symbol_stride = symbol_stride; a.symbols_per_packet = (uint32_t)spp_sym;
+    a.n_packets = (uint32_t)n_packets; a.iq = static_cast<cf*>(d_iq); a.packet_stride = packet_stride;
+    a.sf = (int)cfg->sf; a.osr = cfg->osr; a.bw_scale = (float)cfg->bw_hz / 125000.0f;
+    a.amplitude = cfg->amplitude; a.sync = cfg->sync_word & 0xff;
+    a.phase_scratch = phases;
+    a.frame = 0; a.padding = 0;
+    a.channel = lk::McChannel{};
+    unsigned launches = 0;
+    e = lk::launch_modulate(a, ctx->sm_count, ctx->stream, &launches);
+    ctx->launches += launches;
+    if (e != cudaSuccess) return fail(ctx, -EIO, "modulator launch (static scratch)", e);
+    return (long)produced;
+}
+
 long lora_phy_cuda_frame_samples(uint32_t sf, uint32_t osr, size_t n_symbols, uint32_t padding_symbols)
 {
     if (sf < 5 || sf > 12 || osr == 0 || osr > 8) return -EINVAL;

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include "../../include/lora_phy_cuda.h"
 #include "fft_exact.cuh"
 #include "mc_noise.cuh"
 
@@ -58,6 +59,10 @@ struct ModArgs {
 // chirps per packet: shipped framing n+2; upstream frame 10 up + 2 sync + 2 down + quarter down + n data
 __host__ __device__ inline uint32_t mod_chirps(const ModArgs& a) { return a.symbols_per_packet + (a.frame ? 15u : 2u); }
 cudaError_t launch_modulate(const ModArgs& a, int sm_count, cudaStream_t stream, unsigned* launches);
+// allocation-free variant's scratch: a static device array of this many chirp phases (modcodes.cu); the device address
+// of it on the CURRENT device (cudaGetSymbolAddress, cached per device)
+constexpr size_t MOD_STATIC_MAX_CHIRPS = LORA_PHY_CUDA_STATIC_MAX_CHIRPS;
+cudaError_t mod_static_scratch(float** out);
 cudaError_t launch_dechirp(cf* iq, size_t packet_stride, uint32_t samples_per_packet, uint32_t n_packets,
                            const cf* table, uint32_t table_len, cudaStream_t stream);
 cudaError_t launch_encode(const uint8_t* payload, size_t payload_stride, uint32_t payload_len, uint32_t n_packets,

@@ -5,6 +5,7 @@
 //   lora_encode/decode   src/phy/LoRaEncoder.cpp:6-18, src/phy/LoRaDecoder.cpp:7-21
 //   decode CRC check     src/phy/phy.cpp:252-259, LoRaCodes.hpp:69-105
 //   compensate_offsets   src/phy/phy.cpp:150-180
+#include <mutex>
 #include "internal.h"
 #include "glibc_math.cuh"
 #include "mc_noise.cuh"
@@ -198,6 +199,34 @@ cudaError_t launch_modulate(const ModArgs& a, int sm_count, cudaStream_t stream,
     mod_emit_kernel<<<need < max_ctas ? (unsigned)need : max_ctas, EMIT_WARPS * 32, 0, stream>>>(a);
     ++*launches;
     return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free modulator (lora_phy_cuda_modulate_batch_static): the per-chirp start phases go to a file-scope device
+// array instead of the context's growable buffer.  Every GPU that loads the library holds the array (4 MiB) until exit.
+// In host code `g_mod_phase_static` is only a host-side stand-in for the symbol, NOT a device address: the address the
+// kernels get comes from cudaGetSymbolAddress, asked once per device with that device current.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_mod_phase_static[MOD_STATIC_MAX_CHIRPS];
+
+cudaError_t mod_static_scratch(float** out)
+{
+    static std::mutex mu;
+    static float* addr[64] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        float* p = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_mod_phase_static);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return cudaSuccess;
 }
 
 // ------------------------------------------------------------------------------------------
