@@ -168,7 +168,8 @@ def time_demod(phy, lp, torch, cfg, iq, out, steps, warmup):
     c1 = phy.cert_stats()
     ms = sum(a.elapsed_time(b) for a, b in evs) / steps
     return ms, {"windows": (c1[0] - c0[0]) // steps, "fallback_windows": (c1[1] - c0[1]) // steps,
-                "second_estimates": (c1[2] - c0[2]) // steps, "rewalked_packets": (c1[3] - c0[3]) // steps}
+                "second_estimates": (c1[2] - c0[2]) // steps, "rewalked_packets": (c1[3] - c0[3]) // steps,
+                "pruned_windows": (c1[4] - c0[4]) // steps}
 
 
 def also_demod(phy, lp, torch, peak, name, sf, L, P, raw=False, gains=False, exact=False, steps=3):
@@ -459,7 +460,8 @@ def run_ours(args, wl):
                 "packets_per_step": Pe, "h2d_gbs_per_rank": h2d_all},
         "gpu_launches": launches,
         "certified": {"windows": cert1[0] - cert0[0], "fallback_windows": cert1[1] - cert0[1],
-                      "second_estimates": cert1[2] - cert0[2], "rewalked_packets": cert1[3] - cert0[3]},
+                      "second_estimates": cert1[2] - cert0[2], "rewalked_packets": cert1[3] - cert0[3],
+                      "pruned_windows": cert1[4] - cert0[4]},
         "clocks": sampler.summary(),
     }
     if not args.no_cpu and world == 1:

@@ -71,6 +71,7 @@ SIGNATURES = {
     "lora_phy_cuda_set_stream": (C.c_int, [_vp, _vp]),
     "lora_phy_cuda_synchronize": (C.c_int, [_vp]),
     "lora_phy_cuda_cert_stats": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "lora_phy_cuda_cert_stats_ex": (C.c_int, [_vp, C.POINTER(C.c_uint64), _sz]),
     "lora_phy_cuda_demodulate_batch": (C.c_int, [_vp, _cfgp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_demodulate_batch_host": (C.c_int, [_vp, _cfgp, _vp, _sz, _vp, _sz, _sz, _vp, _sz, _vp, _vp, _vp, _vp]),
     "lora_phy_cuda_estimate_offsets_batch": (C.c_int, [_vp, _cfgp, _vp, _sz, _vp, _sz, _sz, _vp, _vp]),
@@ -172,9 +173,10 @@ class LoraPhyCuda:
         self._check(self.lib.lora_phy_cuda_synchronize(self.h))
 
     def cert_stats(self):
-        """(windows, fallback_windows, second_estimates, rewalked_packets) of the certified demodulator so far."""
-        out = (C.c_uint64 * 4)()
-        self._check(self.lib.lora_phy_cuda_cert_stats(self.h, out))
+        """(windows, fallback_windows, second_estimates, rewalked_packets, pruned_windows) of the certified demodulator
+        so far."""
+        out = (C.c_uint64 * 5)()
+        self._check(self.lib.lora_phy_cuda_cert_stats_ex(self.h, out, 5))
         return tuple(int(x) for x in out)
 
     def set_stream(self, stream_handle):

@@ -73,7 +73,7 @@ struct lora_phy_cuda_ctx {
     lk::McChannel mc_channel = {};                      // set by awgn_roundtrip around its modulate call (fused channel)
     size_t mc_scratch_bytes = (size_t)4 << 30;           // IQ bytes per Monte-Carlo chunk (LORA_PHY_MC_SCRATCH_MB)
     DevBuf lfsr;                                         // dewhitening byte table of the coding chain (chain.cu)
-    unsigned long long* cert_stats = nullptr;           // [4] counters of the certified demodulator (demod_cert.cu)
+    unsigned long long* cert_stats = nullptr;           // [8] counters of the certified demodulator (demod_cert.cu)
     DevBuf d_in, d_out, d_aux;                          // host-variant staging on the device
     PinBuf h_in, h_out;
     // host-variant pipeline (demodulate_batch_host): the batch is cut into chunks, chunk k+1 crosses PCIe on copy_stream
@@ -179,8 +179,8 @@ int lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device)
         }
         ctx->launches += 2;
     }
-    if (cudaMalloc(&ctx->cert_stats, 4 * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMemsetAsync(ctx->cert_stats, 0, 4 * sizeof(unsigned long long), ctx->stream) != cudaSuccess) {
+    if (cudaMalloc(&ctx->cert_stats, 8 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemsetAsync(ctx->cert_stats, 0, 8 * sizeof(unsigned long long), ctx->stream) != cudaSuccess) {
         lora_phy_cuda_destroy(ctx);
         return -EIO;
     }
@@ -244,6 +244,15 @@ int lora_phy_cuda_cert_stats(lora_phy_cuda_ctx* ctx, uint64_t out[4])
     CtxGuard g(ctx);
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaMemcpy(out, ctx->cert_stats, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int lora_phy_cuda_cert_stats_ex(lora_phy_cuda_ctx* ctx, uint64_t* out, size_t n)
+{
+    if (!ctx || !out || n > 8) return -EINVAL;
+    CtxGuard g(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(out, ctx->cert_stats, n * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return 0;
 }
 

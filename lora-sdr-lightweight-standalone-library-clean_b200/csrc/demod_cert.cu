@@ -30,6 +30,7 @@
 #include "stream_common.cuh"
 #include "fft_fast.cuh"
 #include "fft_soa.cuh"
+#include "fft_prune.cuh"
 #include "internal.h"
 
 namespace lk {
@@ -58,6 +59,10 @@ namespace lk {
 #define CERT_EARLY_REFILL 0                   // warp pipelines: refill at the top of the step (needs an end-of-step __syncwarp), A/B knob
 #endif
 
+#ifndef CERT_PRUNE
+#define CERT_PRUNE 1                          // pruned transform (fft_prune.cuh) first, full transform for windows that fail tier 1; 0 = A/B
+#endif
+
 #ifndef CERT_L2_AHEAD
 #define CERT_L2_AHEAD 0                       // steps ahead of the walk that are pulled into L2 (0 = off); see the walk loop
 #endif
@@ -76,6 +81,10 @@ struct CertShared {                           // one per pipeline
     EstSymC est[2];
     int sw[2];
     float bc_rate; int bc_toff;
+    int k0;                                   // pruned transform: bin class chosen by the window's first thread
+    int fail_seq;                             //   bumped when a pruned window fails tier 1 (multi-warp windows; read one step later)
+    int tcnt;                                 //   warps of the window that have published their top bin
+    unsigned tq[8]; int tbin[8]; float te[8]; //   per warp: top |Y|^2 bits, its bin, energy of the warp's samples
     unsigned fb[CERT_CAP / 32];               // windows that failed certification
     uint16_t sym[CERT_CAP];                   // data symbols of the packet, flushed in one coalesced run
 };
@@ -95,7 +104,13 @@ struct CertCfg {
     // instead of 30 registers for the kernel's lifetime -- the loop is register-bound there), registers for SF10-12
     static constexpr bool TW0_SMEM = SF <= CERT_TW0_SMEM_MAX_SF;
     static constexpr size_t tw0_bytes = (TW0_SMEM || (SF == 7 && CERT_SOA_SF7 && CERT_SOA_TW_SMEM)) ? (size_t)N * sizeof(cf) : 0;
-    static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + 256;
+    // pruned transform: stage factors of the lane transform [4][32], W_R^j [8], W_N^j (SF7 only: its pass-0 twiddles live
+    // in the struct-of-arrays layout), and for multi-warp windows the T-entry meeting buffer of every pipeline
+    using PR = fp::Prune<SF>;
+    static constexpr size_t pr_tws = 0, pr_wr = 4 * 32 * sizeof(cf), pr_twn = pr_wr + 8 * sizeof(cf);
+    static constexpr size_t pr_ub = pr_twn + (SF == 7 ? (size_t)N * sizeof(cf) : 0);
+    static constexpr size_t pr_bytes = CERT_PRUNE ? pr_ub + (PR::R > 1 ? (size_t)DOMS * T * sizeof(cf) : 0) : 0;
+    static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + pr_bytes + 256;
     // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
     static constexpr int fit = (int)(((size_t)227 * 1024 / CERT_CTAS_PER_SM - 1024 - fixed_bytes) / stage_bytes);
     static constexpr int STAGES = fit >= 3 ? 3 : 2;
@@ -105,7 +120,8 @@ struct CertCfg {
     static constexpr size_t tw1_off = (red_off + red_bytes + 15) & ~(size_t)15;
     static constexpr size_t tw0_off = (tw1_off + (size_t)F::TW1_SIZE * sizeof(cf) + 15) & ~(size_t)15;
     static constexpr size_t ws_off = (tw0_off + tw0_bytes + 15) & ~(size_t)15;
-    static constexpr size_t bytes = ws_off + (size_t)DOMS * sizeof(CertShared);
+    static constexpr size_t pr_off = (ws_off + (size_t)DOMS * sizeof(CertShared) + 15) & ~(size_t)15;
+    static constexpr size_t bytes = pr_off + pr_bytes;
 };
 
 struct RedCell { unsigned key; float e; unsigned m1; unsigned m2; };      // per warp, multi-warp windows only
@@ -246,6 +262,38 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             twi[q] = fs::mk2((float)s0, (float)s1);
         }
     }
+    // pruned transform (fft_prune.cuh): tables and this thread's cross-warp twiddle W_T^{lane * warp}
+    using PR = fp::Prune<SF>;
+    constexpr bool PRUNE = CERT_PRUNE != 0;
+    cf* pr_tws = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_tws);
+    cf* pr_wr = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_wr);
+    cf* pr_twn = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_twn);
+    cf* pr_ub = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_ub) + (PR::R > 1 ? (size_t)dom * T : 0);
+    cf pr_twc = fx::mk(1.0f, 0.0f);
+    if (PRUNE) {
+        for (int j = threadIdx.x; j < PR::STAGES_TW * PR::W; j += CTA) {
+            double sn, cs;
+            sincospi(-2.0 * (double)PR::stage_exp(j / PR::W, j % PR::W) / (double)PR::W, &sn, &cs);
+            pr_tws[j] = fx::mk((float)cs, (float)sn);
+        }
+        for (int j = threadIdx.x; j < 8; j += CTA) {
+            double sn, cs;
+            sincospi(-2.0 * (double)(j & (PR::R - 1)) / (double)PR::R, &sn, &cs);
+            pr_wr[j] = fx::mk((float)cs, (float)sn);
+        }
+        if (SF == 7)
+            for (int j = threadIdx.x; j < N; j += CTA) {
+                double sn, cs;
+                sincospi(-2.0 * (double)j / (double)N, &sn, &cs);
+                pr_twn[j] = fx::mk((float)cs, (float)sn);
+            }
+        if (PR::R > 1) {
+            double sn, cs;
+            sincospi(-2.0 * (double)PR::cross_exp(tid >> 5, tid & 31) / (double)T, &sn, &cs);
+            pr_twc = fx::mk((float)cs, (float)sn);
+        }
+        if (lane == 0) { ws.k0 = 0; ws.fail_seq = 0; ws.tcnt = 0; }
+    }
     const fs::P2 soa_s = fs::mk2(0.70710678118654752440f, 0.70710678118654752440f);
     const fs::P2 soa_ns = fs::mk2(-0.70710678118654752440f, -0.70710678118654752440f);
     const int wr0 = F::wr_base(0, tid), rd0 = F::rd_base(0, tid);
@@ -261,6 +309,12 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
     const uint32_t n_pipes = gridDim.x * C::DOMS;
     float pred_max = 0.0f;                         // max-abs of the last packet this pipeline saw
     unsigned st_windows = 0, st_fallback = 0, st_est2 = 0, st_rewalk = 0;      // per-thread statistics, summed at the end
+    unsigned st_pruned = 0;
+    // pruned-transform policy, uniform over the pipeline: after a window fails tier 1 the next `skip` steps go straight
+    // to the full transform; the back-off doubles on every failed retry (noisy traffic settles on the full transform
+    // with a vanishing number of retries) and clears on success
+    unsigned pr_skip = 0, pr_backoff = 0;
+    int pr_seen = 0;
 
     for (uint32_t pid = blockIdx.x * C::DOMS + dom; pid < a.n_packets; pid += n_pipes) {
         const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
@@ -440,6 +494,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             // (t_off == 0, the usual case) has window s at sample s*N with the packet's own parity.
             float m = 0.0f;
             bool suspicious = false;
+            const bool fast_pkt = Kc < 0.0078125f;             // tier 1 available at all (pruned windows have no tier 2)
             const bool regular = t_off == 0;
             const uint32_t slot0 = ptx::smem_u32(slots) + (uint32_t)(gq * C::PITCH * sizeof(cf));
             const uint32_t bar0 = ptx::smem_u32(full);
@@ -510,13 +565,130 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 if (active) m = fmaxf(m, mw);
                 float en = (e0.x + e0.y) + (e1.x + e1.y);
 
+                bool refilled = false;
+                auto refill_once = [&]() { if (!refilled) { refill(); refilled = true; } };
+                const bool fast = PRUNE && pr_skip == 0 && fast_pkt;
+                bool pr_failed = false;
+                if (PRUNE && fast) {
+                    // ---- pruned transform (fft_prune.cuh): pass 0, the tone's bin class, one value per thread ------------
+                    ff::dft16(v);
+                    int k0 = 0;
+                    if (T <= 32 || (tid >> 5) == 0) {
+                        // the window's first thread ranks its 16 outputs by |re| + |im| (any choice is safe, see the header)
+                        unsigned kb = 0u;
+#pragma unroll
+                        for (int e = 0; e < 16; e += 2)
+                            kb = umax3(kb, key_of(fabsf(v[e].x) + fabsf(v[e].y), keymask, e),
+                                       key_of(fabsf(v[e + 1].x) + fabsf(v[e + 1].y), keymask, e + 1));
+                        if (T <= 32) k0 = __shfl_sync(0xffffffffu, (int)(kb & 15u), (int)(threadIdx.x & 31u) & ~(T - 1));
+                        else if (tid == 0) ws.k0 = (int)(kb & 15u);
+                    }
+                    if (T > 32) {
+                        group_sync<T>();                       // k0 visible; every thread of the window has its raw samples
+                        k0 = ws.k0;
+                        const int fsq = ws.fail_seq;           // verdict of the previous pruned step, published before this barrier
+                        if (fsq != pr_seen) { pr_seen = fsq; pr_failed = true; }
+                    } else {
+                        __syncwarp();
+                    }
+                    refill_once();
+                    cf sel = v[0], tw = fx::mk(1.0f, 0.0f);
+                    switch (k0) {
+#define CERT_PICK(K) case K: sel = v[K]; if (!SOA) tw = tw0[K]; break;
+                        CERT_PICK(1) CERT_PICK(2) CERT_PICK(3) CERT_PICK(4) CERT_PICK(5) CERT_PICK(6) CERT_PICK(7) CERT_PICK(8)
+                        CERT_PICK(9) CERT_PICK(10) CERT_PICK(11) CERT_PICK(12) CERT_PICK(13) CERT_PICK(14) CERT_PICK(15)
+#undef CERT_PICK
+                        default: break;
+                    }
+                    if (SOA) tw = pr_twn[(tid * k0) & (N - 1)];
+                    cf cval = ff::fcmul(sel, tw);
+                    if (PR::R > 1) {
+                        // T > 32: warp ka forms its output of the R-point transform across the window's warps
+                        pr_ub[tid] = cval;
+                        group_sync<T>();
+                        const int ka = tid >> 5, l5 = tid & 31;
+                        cf acc = pr_ub[l5];
+#pragma unroll
+                        for (int w = 1; w < PR::R; ++w) {
+                            const cf t = ff::fcmul(pr_ub[l5 + 32 * w], pr_wr[(w * ka) & (PR::R - 1)]);
+                            acc = ff::add(acc, t);
+                        }
+                        cval = ff::fcmul(acc, pr_twc);
+                    }
+                    const int lw = tid & (PR::W - 1);
+                    const cf yv = fp::lane_dft<SF>(cval, lw, pr_tws);
+                    const unsigned qb = __float_as_uint(ff::fnorm(yv));       // >= +0, or NaN (sorts above everything)
+                    unsigned qmax = qb;
+#pragma unroll
+                    for (int off = PR::W / 2; off > 0; off >>= 1) {
+                        qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
+                        en += __shfl_xor_sync(0xffffffffu, en, off);
+                    }
+                    if (PR::R == 1) {
+                        const float q1 = __uint_as_float(qmax);
+                        const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
+                        if (active) {
+                            if (!cert && !(en < 1.0e30f)) suspicious = true;
+                            if (qb == qmax) {                                  // the lane that holds the top bin (unique when certified)
+                                if (cert) {
+                                    const int idx = k0 + 16 * (int)(__brev((unsigned)lw) >> (32 - PR::LW));
+                                    if (have_sync && s < 2) ws.sw[s] = idx;
+                                    else ws.sym[have_sync ? s - 2 : s] = (uint16_t)idx;
+                                } else {
+                                    atomicOr(&ws.fb[s >> 5], 1u << (s & 31));
+                                }
+                            }
+                            if (tid == 0 && cert) ++st_pruned;
+                        }
+                        pr_failed = __any_sync(0xffffffffu, active && !cert) != 0;
+                    } else {
+                        // every warp publishes its top bin; the last one to arrive decides for the window
+                        const unsigned ball = __ballot_sync(0xffffffffu, qb == qmax);
+                        if ((threadIdx.x & 31u) == 0u) {
+                            const int ka = tid >> 5;
+                            const int lt = __ffs((int)ball) - 1;
+                            ws.tq[ka] = qmax;
+                            ws.tbin[ka] = k0 + 16 * (ka + PR::R * (int)(__brev((unsigned)lt) >> (32 - PR::LW)));
+                            ws.te[ka] = en;
+                            __threadfence_block();
+                            const int ticket = atomicAdd(&ws.tcnt, 1);
+                            if (ticket == PR::R - 1) {
+                                __threadfence_block();
+                                ws.tcnt = 0;
+                                unsigned bq = 0u; int bb = 0; float et = 0.0f;
+#pragma unroll
+                                for (int w = 0; w < PR::R; ++w) {
+                                    const unsigned qw = ws.tq[w];
+                                    et += ws.te[w];
+                                    if (qw > bq) { bq = qw; bb = ws.tbin[w]; }
+                                }
+                                const float q1 = __uint_as_float(bq);
+                                const bool cert = (q1 > tier1 * et) && (et < 1.0e30f) && (q1 >= 8.3e-25f);
+                                if (active) {
+                                    if (cert) {
+                                        if (have_sync && s < 2) ws.sw[s] = bb;
+                                        else ws.sym[have_sync ? s - 2 : s] = (uint16_t)bb;
+                                        ++st_pruned;
+                                    } else {
+                                        if (!(et < 1.0e30f)) suspicious = true;
+                                        atomicOr(&ws.fb[s >> 5], 1u << (s & 31));
+                                        ws.fail_seq = ws.fail_seq + 1;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                } else {
                 unsigned key[16];
 #if defined(CERT_ABLATE)
-                // measurement-only build (tools/ablate_cert.sh, never the product): the walk without its transform -- what the
+                // measurement-only build (tools/ablate.sh, never the product): the walk without its transform -- what the
                 // streaming skeleton (ring, rotation, max / energy tracking, keys, reductions, bookkeeping) costs on its own
+                if constexpr (true) {
+                    group_sync<T>();
+                    refill_once();
 #pragma unroll
-                for (int e = 0; e < 16; ++e) key[e] = key_of(ff::fnorm(v[e]), keymask, e);
-                if (false) {
+                    for (int e = 0; e < 16; ++e) key[e] = key_of(ff::fnorm(v[e]), keymask, e);
+                } else if constexpr (SOA) {
 #else
                 if constexpr (SOA) {
 #endif
@@ -658,6 +830,12 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                         }
                     }
                 }
+                if (pr_skip) --pr_skip;
+                }                                              // full transform
+                if (PRUNE && fast) {
+                    if (pr_failed) { pr_backoff = min(2u * pr_backoff + 16u, 4096u); pr_skip = pr_backoff; }
+                    else pr_backoff = 0u;
+                }
                 ptx::fence_proxy_async();                      // this thread's stores to the slot precede its next refill
                 if (EARLY) csync<DT>();
                 stage = stage + 1 == STAGES ? 0 : stage + 1;
@@ -771,6 +949,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
         if (st_fallback) atomicAdd(a.cert_stats + 1, (unsigned long long)st_fallback);
         if (lane == 0 && st_est2) atomicAdd(a.cert_stats + 2, (unsigned long long)st_est2);
         if (lane == 0 && st_rewalk) atomicAdd(a.cert_stats + 3, (unsigned long long)st_rewalk);
+        if (st_pruned) atomicAdd(a.cert_stats + 4, (unsigned long long)st_pruned);
     }
 }
 

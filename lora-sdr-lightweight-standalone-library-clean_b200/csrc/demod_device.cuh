@@ -54,7 +54,7 @@ struct DemodArgs {
     float* time_offset;
     int32_t* status;
     int force_exact;              // LORA_PHY_CUDA_F_EXACT: the certified kernel replays the exact chain for every window
-    unsigned long long* cert_stats;   // [4] windows walked, windows replayed exactly, second estimates, re-walked packets
+    unsigned long long* cert_stats;   // [8] windows walked, windows replayed exactly, second estimates, re-walked packets, windows settled by the pruned transform
 };
 
 __device__ __forceinline__ cf ldg_cf(const cf* p)
