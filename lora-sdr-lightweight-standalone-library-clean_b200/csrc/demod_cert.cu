@@ -108,7 +108,7 @@ struct CertCfg {
     // in the struct-of-arrays layout), and for multi-warp windows the T-entry meeting buffer of every pipeline
     using PR = fp::Prune<SF>;
     static constexpr size_t pr_tws = 0, pr_wr = 4 * 32 * sizeof(cf), pr_twn = pr_wr + 8 * sizeof(cf);
-    static constexpr size_t pr_ub = pr_twn + (SF == 7 ? (size_t)N * sizeof(cf) : 0);
+    static constexpr size_t pr_ub = pr_twn + (SF <= 8 ? (size_t)N * sizeof(cf) : 0);
     static constexpr size_t pr_bytes = CERT_PRUNE ? pr_ub + (PR::R > 1 ? (size_t)DOMS * T * sizeof(cf) : 0) : 0;
     static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + pr_bytes + 256;
     // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             sincospi(-2.0 * (double)(j & (PR::R - 1)) / (double)PR::R, &sn, &cs);
             pr_wr[j] = fx::mk((float)cs, (float)sn);
         }
-        if (SF == 7)
+        if (SF <= 8)
             for (int j = threadIdx.x; j < N; j += CTA) {
                 double sn, cs;
                 sincospi(-2.0 * (double)j / (double)N, &sn, &cs);
@@ -593,14 +593,27 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     }
                     refill_once();
                     cf sel = v[0], tw = fx::mk(1.0f, 0.0f);
+                    constexpr bool TW_TABLE = SOA || T < 32;   // several windows per warp: k0 differs between lanes -> no branch
+                    if (T < 32) {
+                        // binary select tree on the bits of k0 (30 selects), twiddle from the W_N table
+                        const bool b0 = (k0 & 1) != 0, b1 = (k0 & 2) != 0, b2 = (k0 & 4) != 0, b3 = (k0 & 8) != 0;
+                        cf t8[8], t4[4], t2[2];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) t8[j] = fx::mk(b0 ? v[2 * j + 1].x : v[2 * j].x, b0 ? v[2 * j + 1].y : v[2 * j].y);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) t4[j] = fx::mk(b1 ? t8[2 * j + 1].x : t8[2 * j].x, b1 ? t8[2 * j + 1].y : t8[2 * j].y);
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) t2[j] = fx::mk(b2 ? t4[2 * j + 1].x : t4[2 * j].x, b2 ? t4[2 * j + 1].y : t4[2 * j].y);
+                        sel = fx::mk(b3 ? t2[1].x : t2[0].x, b3 ? t2[1].y : t2[0].y);
+                    } else
                     switch (k0) {
-#define CERT_PICK(K) case K: sel = v[K]; if (!SOA) tw = tw0[K]; break;
+#define CERT_PICK(K) case K: sel = v[K]; if (!TW_TABLE) tw = tw0[K]; break;
                         CERT_PICK(1) CERT_PICK(2) CERT_PICK(3) CERT_PICK(4) CERT_PICK(5) CERT_PICK(6) CERT_PICK(7) CERT_PICK(8)
                         CERT_PICK(9) CERT_PICK(10) CERT_PICK(11) CERT_PICK(12) CERT_PICK(13) CERT_PICK(14) CERT_PICK(15)
 #undef CERT_PICK
                         default: break;
                     }
-                    if (SOA) tw = pr_twn[(tid * k0) & (N - 1)];
+                    if (TW_TABLE) tw = pr_twn[(tid * k0) & (N - 1)];
                     cf cval = ff::fcmul(sel, tw);
                     if (PR::R > 1) {
                         // T > 32: warp ka forms its output of the R-point transform across the window's warps
