@@ -63,6 +63,11 @@ namespace lk {
 #define CERT_PRUNE 1                          // pruned transform (fft_prune.cuh) first, full transform for windows that fail tier 1; 0 = A/B
 #endif
 
+#ifndef CERT_GEOM
+#define CERT_GEOM 1                           // single-warp windows without downchirp / window tables: the pruned transform works on
+                                              // the RAW samples (rotation folded into a per-packet geometric ratio); 0 = A/B
+#endif
+
 #ifndef CERT_L2_AHEAD
 #define CERT_L2_AHEAD 0                       // steps ahead of the walk that are pulled into L2 (0 = off); see the walk loop
 #endif
@@ -85,6 +90,7 @@ struct CertShared {                           // one per pipeline
     int fail_seq;                             //   bumped when a pruned window fails tier 1 (multi-warp windows; read one step later)
     int tcnt;                                 //   warps of the window that have published their top bin
     unsigned tq[8]; int tbin[8]; float te[8]; //   per warp: top |Y|^2 bits, its bin, energy of the warp's samples
+    alignas(16) cf hp[64];                             //   geometric variant: [k0][m] = (G w_k0)^(2^m), G = exp(j rate T), w = W16 (per packet)
     unsigned fb[CERT_CAP / 32];               // windows that failed certification
     uint16_t sym[CERT_CAP];                   // data symbols of the packet, flushed in one coalesced run
 };
@@ -108,7 +114,8 @@ struct CertCfg {
     // in the struct-of-arrays layout), and for multi-warp windows the T-entry meeting buffer of every pipeline
     using PR = fp::Prune<SF>;
     static constexpr size_t pr_tws = 0, pr_wr = 4 * 32 * sizeof(cf), pr_twn = pr_wr + 8 * sizeof(cf);
-    static constexpr size_t pr_ub = pr_twn + (SF <= 8 ? (size_t)N * sizeof(cf) : 0);
+    static constexpr size_t pr_w16 = pr_twn + (SF <= 9 ? (size_t)N * sizeof(cf) : 0);       // W16^j, 16 entries
+    static constexpr size_t pr_ub = pr_w16 + 16 * sizeof(cf);
     static constexpr size_t pr_bytes = CERT_PRUNE ? pr_ub + (PR::R > 1 ? (size_t)DOMS * T * sizeof(cf) : 0) : 0;
     static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + pr_bytes + 256;
     // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
@@ -268,6 +275,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
     cf* pr_tws = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_tws);
     cf* pr_wr = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_wr);
     cf* pr_twn = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_twn);
+    cf* pr_w16 = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_w16);
     cf* pr_ub = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_ub) + (PR::R > 1 ? (size_t)dom * T : 0);
     cf pr_twc = fx::mk(1.0f, 0.0f);
     if (PRUNE) {
@@ -281,7 +289,12 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             sincospi(-2.0 * (double)(j & (PR::R - 1)) / (double)PR::R, &sn, &cs);
             pr_wr[j] = fx::mk((float)cs, (float)sn);
         }
-        if (SF <= 8)
+        for (int j = threadIdx.x; j < 16; j += CTA) {
+            double sn, cs;
+            sincospi(-2.0 * (double)j / 16.0, &sn, &cs);
+            pr_w16[j] = fx::mk((float)cs, (float)sn);
+        }
+        if (SF <= 9)
             for (int j = threadIdx.x; j < N; j += CTA) {
                 double sn, cs;
                 sincospi(-2.0 * (double)j / (double)N, &sn, &cs);
@@ -469,18 +482,47 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             }
 
             // ---- per-packet factors f_c = scale * [down_i] * exp(j*rate*i) * [w_i], i = tid + T*c ------------------
+            constexpr bool GEOM = PRUNE && CERT_GEOM != 0 && !EXTRA && T <= 32;
             cf f[16];
+            bool f_ready = false;
+            auto make_f = [&]() {
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                const int i = tid + T * c;
-                float ph = fx::fmul(rate, (float)i);
-                ph = __fmaf_rn(-6.283185307179586f, rintf(ph * 0.15915494309189535f), ph);      // into [-pi, pi]
+                for (int c = 0; c < 16; ++c) {
+                    const int i = tid + T * c;
+                    float ph = fx::fmul(rate, (float)i);
+                    ph = __fmaf_rn(-6.283185307179586f, rintf(ph * 0.15915494309189535f), ph);      // into [-pi, pi]
+                    float sn, cs;
+                    __sincosf(ph, &sn, &cs);
+                    cf r = fx::mk(cs * scale, sn * scale);
+                    if (EXTRA && a.down) r = ff::fcmul(ldg_cf(a.down + i), r);
+                    if (EXTRA && a.window) { const float w = __ldg(a.window + i); r = fx::mk(r.x * w, r.y * w); }
+                    f[c] = r;
+                }
+                f_ready = true;
+            };
+            // Geometric variant: f_c = F_tid * G^c with F_tid = scale exp(j rate tid), G = exp(j rate T), so the bin class k0
+            // of the pruned transform is sum_c r_c h^c, h = G W16^k0 -- a polynomial in the RAW samples.  Per packet: F_tid
+            // (one sin/cos.approx, <= 9u), G^(1,2,4,8) in double on four lanes (rate T m is exact: T m is a power of two),
+            // and the table hp[k0][m] = G^(2^m) W16^(k0 2^m) (one float complex product: <= 3.5u each).
+            cf geo_f = fx::mk(scale, 0.0f), geo_g1 = fx::mk(1.0f, 0.0f);
+            if (GEOM) {
+                float ph = fx::fmul(rate, (float)tid);
                 float sn, cs;
-                __sincosf(ph, &sn, &cs);
-                cf r = fx::mk(cs * scale, sn * scale);
-                if (EXTRA && a.down) r = ff::fcmul(ldg_cf(a.down + i), r);
-                if (EXTRA && a.window) { const float w = __ldg(a.window + i); r = fx::mk(r.x * w, r.y * w); }
-                f[c] = r;
+                __sincosf(ph, &sn, &cs);                                   // |rate tid| < 2 pi / 16
+                geo_f = fx::mk(cs * scale, sn * scale);
+                double ds = 0.0, dc = 1.0;
+                if (lane < 4) sincos((double)rate * (double)(T << lane), &ds, &dc);
+                const float gx = (float)dc, gy = (float)ds;
+                geo_g1 = fx::mk(__shfl_sync(0xffffffffu, gx, 0), __shfl_sync(0xffffffffu, gy, 0));
+#pragma unroll
+                for (int h2 = 0; h2 < 2; ++h2) {
+                    const int e = lane + 32 * h2, k = e >> 2, mi = e & 3;          // entry [k][mi]
+                    const cf g = fx::mk(__shfl_sync(0xffffffffu, gx, mi), __shfl_sync(0xffffffffu, gy, mi));
+                    ws.hp[e] = ff::fcmul(g, pr_w16[(k << mi) & 15]);
+                }
+                __syncwarp();
+            } else {
+                make_f();
             }
             // certification constant: K = u * (C0 + |start|max + 2|rate|N); accepted iff d^2 > 16 K^2 (N E) q1
             const float start_max = fabsf(rate) * ((float)total * (float)N + fabsf((float)t_off)) * 1.01f;
@@ -551,9 +593,94 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 cf* win = slots + (size_t)stage * C::SLOT + (size_t)gq * C::PITCH;
                 const cf* raw = win + roff;
 
+                const bool fast = PRUNE && pr_skip == 0 && fast_pkt;
+                bool pr_failed = false;
+                bool refilled = false;
+                auto refill_once = [&]() { if (!refilled) { refill(); refilled = true; } };
                 cf v[16];
                 float mw = 0.0f;
                 cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);                   // (sum re^2, sum im^2), two chains
+                float en;
+                if (GEOM && fast) {
+                    // ---- pruned transform on the raw samples (geometric variant, single-warp windows) ---------------------
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) {
+                        const cf r = raw[T * c];
+                        mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                 // running max-abs (LoRaDemod.cpp:61-68)
+                        if (c & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
+                        v[c] = r;
+                    }
+                    if (active) m = fmaxf(m, mw);
+                    // energy of the rotated samples: |f_c| = scale up to the rounding of sin^2 + cos^2 (a hair of head-room)
+                    en = ((e0.x + e0.y) + (e1.x + e1.y)) * (scale * scale) * 1.000002f;
+                    // bin class: the phase step between neighbouring samples of a thread, 2 pi (bin mod 16) / 16 after the
+                    // rotation's own step G; four pairs per thread, summed over the window
+                    cf z = fx::mk(0.0f, 0.0f);
+#pragma unroll
+                    for (int c = 0; c < 16; c += 4) {
+                        z.x = ff::fma_(v[c + 1].x, v[c].x, z.x); z.x = ff::fma_(v[c + 1].y, v[c].y, z.x);
+                        z.y = ff::fma_(v[c + 1].y, v[c].x, z.y); z.y = ff::fma_(-v[c + 1].x, v[c].y, z.y);
+                    }
+#pragma unroll
+                    for (int off = PR::W / 2; off > 0; off >>= 1) {
+                        z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
+                        z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
+                    }
+                    __syncwarp();
+                    refill_once();
+                    z = ff::fcmul(z, geo_g1);
+                    int k0;
+                    {   // nearest multiple of 22.5 degrees, by octant folding (an inexact answer only costs a failed test)
+                        const float ax = fabsf(z.x), ay = fabsf(z.y);
+                        const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
+                        int q = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
+                        if (ay > ax) q = 4 - q;
+                        if (z.x < 0.0f) q = 8 - q;
+                        if (z.y < 0.0f) q = 16 - q;
+                        k0 = q & 15;
+                    }
+                    // sum_c r_c h^c by halving: four levels of complex multiply-adds with h^8, h^4, h^2, h
+                    const float4 hA = *reinterpret_cast<const float4*>(&ws.hp[4 * k0]);          // h, h^2
+                    const float4 hB = *reinterpret_cast<const float4*>(&ws.hp[4 * k0 + 2]);      // h^4, h^8
+                    const cf h1 = fx::mk(hA.x, hA.y), h2 = fx::mk(hA.z, hA.w), h4 = fx::mk(hB.x, hB.y), h8 = fx::mk(hB.z, hB.w);
+                    auto cma = [](cf acc, cf a, cf w) {                   // acc + a * w: four fused multiply-adds
+                        return fx::mk(ff::fma_(-a.y, w.y, ff::fma_(a.x, w.x, acc.x)), ff::fma_(a.y, w.x, ff::fma_(a.x, w.y, acc.y)));
+                    };
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) v[c] = cma(v[c], v[c + 8], h8);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) v[c] = cma(v[c], v[c + 4], h4);
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) v[c] = cma(v[c], v[c + 2], h2);
+                    const cf pv = cma(v[0], v[1], h1);
+                    const cf cval = ff::fcmul(ff::fcmul(pv, pr_twn[(tid * k0) & (N - 1)]), geo_f);
+                    const int lw = tid & (PR::W - 1);
+                    const cf yv = fp::lane_dft<SF>(cval, lw, pr_tws);
+                    const unsigned qb = __float_as_uint(ff::fnorm(yv));       // >= +0, or NaN (sorts above everything)
+                    unsigned qmax = qb;
+#pragma unroll
+                    for (int off = PR::W / 2; off > 0; off >>= 1) {
+                        qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
+                        en += __shfl_xor_sync(0xffffffffu, en, off);
+                    }
+                    const float q1 = __uint_as_float(qmax);
+                    const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
+                    if (active) {
+                        if (!cert && !(en < 1.0e30f)) suspicious = true;
+                        if (qb == qmax) {                                  // the lane that holds the top bin (unique when certified)
+                            if (cert) {
+                                const int idx = k0 + 16 * (int)(__brev((unsigned)lw) >> (32 - PR::LW));
+                                if (have_sync && s < 2) ws.sw[s] = idx;
+                                else ws.sym[have_sync ? s - 2 : s] = (uint16_t)idx;
+                            } else {
+                                atomicOr(&ws.fb[s >> 5], 1u << (s & 31));
+                            }
+                        }
+                        if (tid == 0 && cert) ++st_pruned;
+                    }
+                    pr_failed = __any_sync(0xffffffffu, active && !cert) != 0;
+                } else {
+                if (GEOM && !f_ready) make_f();
 #pragma unroll
                 for (int c = 0; c < 16; ++c) {
                     const cf r = raw[T * c];
@@ -563,12 +690,8 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     v[c] = y;
                 }
                 if (active) m = fmaxf(m, mw);
-                float en = (e0.x + e0.y) + (e1.x + e1.y);
+                en = (e0.x + e0.y) + (e1.x + e1.y);
 
-                bool refilled = false;
-                auto refill_once = [&]() { if (!refilled) { refill(); refilled = true; } };
-                const bool fast = PRUNE && pr_skip == 0 && fast_pkt;
-                bool pr_failed = false;
                 if (PRUNE && fast) {
                     // ---- pruned transform (fft_prune.cuh): pass 0, the tone's bin class, one value per thread ------------
                     ff::dft16(v);
@@ -845,6 +968,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 }
                 if (pr_skip) --pr_skip;
                 }                                              // full transform
+                }                                              // rotated samples (not the geometric variant)
                 if (PRUNE && fast) {
                     if (pr_failed) { pr_backoff = min(2u * pr_backoff + 16u, 4096u); pr_skip = pr_backoff; }
                     else pr_backoff = 0u;
