@@ -68,6 +68,11 @@ namespace lk {
                                               // the RAW samples (rotation folded into a per-packet geometric ratio); 0 = A/B
 #endif
 
+#ifndef CERT_GEOM_MAX_T
+#define CERT_GEOM_MAX_T 32                    // widest window (threads) that takes the geometric variant: measured slower at SF12 (T = 256),
+                                              // level at SF10 / SF11; multi-warp windows keep pass 0 + first-thread class
+#endif
+
 #ifndef CERT_L2_AHEAD
 #define CERT_L2_AHEAD 0                       // steps ahead of the walk that are pulled into L2 (0 = off); see the walk loop
 #endif
@@ -90,6 +95,7 @@ struct CertShared {                           // one per pipeline
     int fail_seq;                             //   bumped when a pruned window fails tier 1 (multi-warp windows; read one step later)
     int tcnt;                                 //   warps of the window that have published their top bin
     unsigned tq[8]; int tbin[8]; float te[8]; //   per warp: top |Y|^2 bits, its bin, energy of the warp's samples
+    int tk0[8];                               //   per warp: the bin class it transformed (all must agree)
     alignas(16) cf hp[64];                             //   geometric variant: [k0][m] = (G w_k0)^(2^m), G = exp(j rate T), w = W16 (per packet)
     unsigned fb[CERT_CAP / 32];               // windows that failed certification
     uint16_t sym[CERT_CAP];                   // data symbols of the packet, flushed in one coalesced run
@@ -116,7 +122,7 @@ struct CertCfg {
     static constexpr size_t pr_tws = 0, pr_wr = 4 * 32 * sizeof(cf), pr_twn = pr_wr + 8 * sizeof(cf);
     static constexpr size_t pr_w16 = pr_twn + (SF <= 9 ? (size_t)N * sizeof(cf) : 0);       // W16^j, 16 entries
     static constexpr size_t pr_ub = pr_w16 + 16 * sizeof(cf);
-    static constexpr size_t pr_bytes = CERT_PRUNE ? pr_ub + (PR::R > 1 ? (size_t)DOMS * T * sizeof(cf) : 0) : 0;
+    static constexpr size_t pr_bytes = CERT_PRUNE ? pr_ub + (PR::R > 1 ? (size_t)DOMS * 2 * T * sizeof(cf) : 0) : 0;   // two buffers: steps alternate
     static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + pr_bytes + 256;
     // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
     static constexpr int fit = (int)(((size_t)227 * 1024 / CERT_CTAS_PER_SM - 1024 - fixed_bytes) / stage_bytes);
@@ -276,7 +282,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
     cf* pr_wr = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_wr);
     cf* pr_twn = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_twn);
     cf* pr_w16 = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_w16);
-    cf* pr_ub = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_ub) + (PR::R > 1 ? (size_t)dom * T : 0);
+    cf* pr_ub = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_ub) + (PR::R > 1 ? (size_t)dom * 2 * T : 0);
     cf pr_twc = fx::mk(1.0f, 0.0f);
     if (PRUNE) {
         for (int j = threadIdx.x; j < PR::STAGES_TW * PR::W; j += CTA) {
@@ -482,7 +488,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
             }
 
             // ---- per-packet factors f_c = scale * [down_i] * exp(j*rate*i) * [w_i], i = tid + T*c ------------------
-            constexpr bool GEOM = PRUNE && CERT_GEOM != 0 && !EXTRA && T <= 32;
+            constexpr bool GEOM = PRUNE && CERT_GEOM != 0 && !EXTRA && T <= CERT_GEOM_MAX_T;
             cf f[16];
             bool f_ready = false;
             auto make_f = [&]() {
@@ -510,17 +516,19 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 float sn, cs;
                 __sincosf(ph, &sn, &cs);                                   // |rate tid| < 2 pi / 16
                 geo_f = fx::mk(cs * scale, sn * scale);
-                double ds = 0.0, dc = 1.0;
-                if (lane < 4) sincos((double)rate * (double)(T << lane), &ds, &dc);
-                const float gx = (float)dc, gy = (float)ds;
-                geo_g1 = fx::mk(__shfl_sync(0xffffffffu, gx, 0), __shfl_sync(0xffffffffu, gy, 0));
+                if (lane < 32) {                                           // the pipeline's first warp
+                    double ds = 0.0, dc = 1.0;
+                    if (lane < 4) sincos((double)rate * (double)(T << lane), &ds, &dc);
+                    const float gx = (float)dc, gy = (float)ds;
 #pragma unroll
-                for (int h2 = 0; h2 < 2; ++h2) {
-                    const int e = lane + 32 * h2, k = e >> 2, mi = e & 3;          // entry [k][mi]
-                    const cf g = fx::mk(__shfl_sync(0xffffffffu, gx, mi), __shfl_sync(0xffffffffu, gy, mi));
-                    ws.hp[e] = ff::fcmul(g, pr_w16[(k << mi) & 15]);
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const int e = lane + 32 * h2, k = e >> 2, mi = e & 3;      // entry [k][mi]
+                        const cf g = fx::mk(__shfl_sync(0xffffffffu, gx, mi), __shfl_sync(0xffffffffu, gy, mi));
+                        ws.hp[e] = ff::fcmul(g, pr_w16[(k << mi) & 15]);
+                    }
                 }
-                __syncwarp();
+                csync<DT>();
+                geo_g1 = ws.hp[0];                                         // G itself (W16^0 = 1)
             } else {
                 make_f();
             }
@@ -601,152 +609,147 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 float mw = 0.0f;
                 cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);                   // (sum re^2, sum im^2), two chains
                 float en;
-                if (GEOM && fast) {
-                    // ---- pruned transform on the raw samples (geometric variant, single-warp windows) ---------------------
+                if (!(GEOM && fast)) {
+                    // rotated samples: the full transform and the pruned transform of the variants with tables
+                    if (GEOM && !f_ready) make_f();
 #pragma unroll
                     for (int c = 0; c < 16; ++c) {
                         const cf r = raw[T * c];
                         mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                 // running max-abs (LoRaDemod.cpp:61-68)
+                        const cf y = ff::fcmul(r, f[c]);
+                        if (c & 1) e1 = ff::sqacc(e1, y); else e0 = ff::sqacc(e0, y);  // one packed FMA per sample
+                        v[c] = y;
+                    }
+                    en = (e0.x + e0.y) + (e1.x + e1.y);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) {
+                        const cf r = raw[T * c];
+                        mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));
                         if (c & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
                         v[c] = r;
                     }
-                    if (active) m = fmaxf(m, mw);
                     // energy of the rotated samples: |f_c| = scale up to the rounding of sin^2 + cos^2 (a hair of head-room)
                     en = ((e0.x + e0.y) + (e1.x + e1.y)) * (scale * scale) * 1.000002f;
-                    // bin class: the phase step between neighbouring samples of a thread, 2 pi (bin mod 16) / 16 after the
-                    // rotation's own step G; four pairs per thread, summed over the window
-                    cf z = fx::mk(0.0f, 0.0f);
-#pragma unroll
-                    for (int c = 0; c < 16; c += 4) {
-                        z.x = ff::fma_(v[c + 1].x, v[c].x, z.x); z.x = ff::fma_(v[c + 1].y, v[c].y, z.x);
-                        z.y = ff::fma_(v[c + 1].y, v[c].x, z.y); z.y = ff::fma_(-v[c + 1].x, v[c].y, z.y);
-                    }
-#pragma unroll
-                    for (int off = PR::W / 2; off > 0; off >>= 1) {
-                        z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
-                        z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
-                    }
-                    __syncwarp();
-                    refill_once();
-                    z = ff::fcmul(z, geo_g1);
-                    int k0;
-                    {   // nearest multiple of 22.5 degrees, by octant folding (an inexact answer only costs a failed test)
-                        const float ax = fabsf(z.x), ay = fabsf(z.y);
-                        const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
-                        int q = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
-                        if (ay > ax) q = 4 - q;
-                        if (z.x < 0.0f) q = 8 - q;
-                        if (z.y < 0.0f) q = 16 - q;
-                        k0 = q & 15;
-                    }
-                    // sum_c r_c h^c by halving: four levels of complex multiply-adds with h^8, h^4, h^2, h
-                    const float4 hA = *reinterpret_cast<const float4*>(&ws.hp[4 * k0]);          // h, h^2
-                    const float4 hB = *reinterpret_cast<const float4*>(&ws.hp[4 * k0 + 2]);      // h^4, h^8
-                    const cf h1 = fx::mk(hA.x, hA.y), h2 = fx::mk(hA.z, hA.w), h4 = fx::mk(hB.x, hB.y), h8 = fx::mk(hB.z, hB.w);
-                    auto cma = [](cf acc, cf a, cf w) {                   // acc + a * w: four fused multiply-adds
-                        return fx::mk(ff::fma_(-a.y, w.y, ff::fma_(a.x, w.x, acc.x)), ff::fma_(a.y, w.x, ff::fma_(a.x, w.y, acc.y)));
-                    };
-#pragma unroll
-                    for (int c = 0; c < 8; ++c) v[c] = cma(v[c], v[c + 8], h8);
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) v[c] = cma(v[c], v[c + 4], h4);
-#pragma unroll
-                    for (int c = 0; c < 2; ++c) v[c] = cma(v[c], v[c + 2], h2);
-                    const cf pv = cma(v[0], v[1], h1);
-                    const cf cval = ff::fcmul(ff::fcmul(pv, pr_twn[(tid * k0) & (N - 1)]), geo_f);
-                    const int lw = tid & (PR::W - 1);
-                    const cf yv = fp::lane_dft<SF>(cval, lw, pr_tws);
-                    const unsigned qb = __float_as_uint(ff::fnorm(yv));       // >= +0, or NaN (sorts above everything)
-                    unsigned qmax = qb;
-#pragma unroll
-                    for (int off = PR::W / 2; off > 0; off >>= 1) {
-                        qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
-                        en += __shfl_xor_sync(0xffffffffu, en, off);
-                    }
-                    const float q1 = __uint_as_float(qmax);
-                    const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
-                    if (active) {
-                        if (!cert && !(en < 1.0e30f)) suspicious = true;
-                        if (qb == qmax) {                                  // the lane that holds the top bin (unique when certified)
-                            if (cert) {
-                                const int idx = k0 + 16 * (int)(__brev((unsigned)lw) >> (32 - PR::LW));
-                                if (have_sync && s < 2) ws.sw[s] = idx;
-                                else ws.sym[have_sync ? s - 2 : s] = (uint16_t)idx;
-                            } else {
-                                atomicOr(&ws.fb[s >> 5], 1u << (s & 31));
-                            }
-                        }
-                        if (tid == 0 && cert) ++st_pruned;
-                    }
-                    pr_failed = __any_sync(0xffffffffu, active && !cert) != 0;
-                } else {
-                if (GEOM && !f_ready) make_f();
-#pragma unroll
-                for (int c = 0; c < 16; ++c) {
-                    const cf r = raw[T * c];
-                    mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                     // running max-abs (LoRaDemod.cpp:61-68)
-                    const cf y = ff::fcmul(r, f[c]);
-                    if (c & 1) e1 = ff::sqacc(e1, y); else e0 = ff::sqacc(e0, y);      // one packed FMA per sample
-                    v[c] = y;
                 }
                 if (active) m = fmaxf(m, mw);
-                en = (e0.x + e0.y) + (e1.x + e1.y);
 
                 if (PRUNE && fast) {
-                    // ---- pruned transform (fft_prune.cuh): pass 0, the tone's bin class, one value per thread ------------
-                    ff::dft16(v);
+                    // ---- pruned transform (fft_prune.cuh): the tone's bin class k0, then ONE value per thread -----------------
                     int k0 = 0;
-                    if (T <= 32 || (tid >> 5) == 0) {
-                        // the window's first thread ranks its 16 outputs by |re| + |im| (any choice is safe, see the header)
-                        unsigned kb = 0u;
+                    cf cval;
+                    if (GEOM) {
+                        // Geometric variant, on the raw samples.  Bin class: the phase step between neighbouring samples of a
+                        // thread is 2 pi (bin mod 16) / 16 once the rotation's own step G is added; four pairs per thread,
+                        // summed over the warp.  (Every warp of a multi-warp window decides for itself -- a tone gives them
+                        // all the same answer -- and the choices are compared before anything is accepted.)
+                        cf z = fx::mk(0.0f, 0.0f);
 #pragma unroll
-                        for (int e = 0; e < 16; e += 2)
-                            kb = umax3(kb, key_of(fabsf(v[e].x) + fabsf(v[e].y), keymask, e),
-                                       key_of(fabsf(v[e + 1].x) + fabsf(v[e + 1].y), keymask, e + 1));
-                        if (T <= 32) k0 = __shfl_sync(0xffffffffu, (int)(kb & 15u), (int)(threadIdx.x & 31u) & ~(T - 1));
-                        else if (tid == 0) ws.k0 = (int)(kb & 15u);
+                        for (int c = 0; c < 16; c += 4) {
+                            z.x = ff::fma_(v[c + 1].x, v[c].x, z.x); z.x = ff::fma_(v[c + 1].y, v[c].y, z.x);
+                            z.y = ff::fma_(v[c + 1].y, v[c].x, z.y); z.y = ff::fma_(-v[c + 1].x, v[c].y, z.y);
+                        }
+#pragma unroll
+                        for (int off = PR::W / 2; off > 0; off >>= 1) {
+                            z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
+                            z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
+                        }
+                        if (T <= 32) { __syncwarp(); refill_once(); }
+                        z = ff::fcmul(z, geo_g1);
+                        {   // nearest multiple of 22.5 degrees, by octant folding (an inexact answer only costs a failed test)
+                            const float ax = fabsf(z.x), ay = fabsf(z.y);
+                            const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
+                            int q = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
+                            if (ay > ax) q = 4 - q;
+                            if (z.x < 0.0f) q = 8 - q;
+                            if (z.y < 0.0f) q = 16 - q;
+                            k0 = q & 15;
+                        }
+                        // sum_c r_c h^c, h = G W16^k0, by halving: four levels of complex multiply-adds with h^8, h^4, h^2, h
+                        const float4 hA = *reinterpret_cast<const float4*>(&ws.hp[4 * k0]);          // h, h^2
+                        const float4 hB = *reinterpret_cast<const float4*>(&ws.hp[4 * k0 + 2]);      // h^4, h^8
+                        const cf h1 = fx::mk(hA.x, hA.y), h2 = fx::mk(hA.z, hA.w), h4 = fx::mk(hB.x, hB.y), h8 = fx::mk(hB.z, hB.w);
+                        auto cma = [](cf acc, cf a, cf w) {               // acc + a * w: four fused multiply-adds
+                            return fx::mk(ff::fma_(-a.y, w.y, ff::fma_(a.x, w.x, acc.x)), ff::fma_(a.y, w.x, ff::fma_(a.x, w.y, acc.y)));
+                        };
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) v[c] = cma(v[c], v[c + 8], h8);
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) v[c] = cma(v[c], v[c + 4], h4);
+#pragma unroll
+                        for (int c = 0; c < 2; ++c) v[c] = cma(v[c], v[c + 2], h2);
+                        const cf pv = cma(v[0], v[1], h1);
+                        cf tw = fx::mk(1.0f, 0.0f);
+                        if (T <= 32) {
+                            tw = pr_twn[(tid * k0) & (N - 1)];
+                        } else {
+                            switch (k0) {                                  // uniform over the warp
+#define CERT_PICK(K) case K: tw = tw0[K]; break;
+                                CERT_PICK(1) CERT_PICK(2) CERT_PICK(3) CERT_PICK(4) CERT_PICK(5) CERT_PICK(6) CERT_PICK(7) CERT_PICK(8)
+                                CERT_PICK(9) CERT_PICK(10) CERT_PICK(11) CERT_PICK(12) CERT_PICK(13) CERT_PICK(14) CERT_PICK(15)
+#undef CERT_PICK
+                                default: break;
+                            }
+                        }
+                        cval = ff::fcmul(ff::fcmul(pv, tw), geo_f);
+                    } else {
+                        // Variants with downchirp / window tables: pass 0 on the rotated samples, class from the window's first
+                        // thread (its 16 outputs ranked by |re| + |im|), that output times its pass-0 twiddle
+                        ff::dft16(v);
+                        if (T <= 32 || (tid >> 5) == 0) {
+                            unsigned kb = 0u;
+#pragma unroll
+                            for (int e = 0; e < 16; e += 2)
+                                kb = umax3(kb, key_of(fabsf(v[e].x) + fabsf(v[e].y), keymask, e),
+                                           key_of(fabsf(v[e + 1].x) + fabsf(v[e + 1].y), keymask, e + 1));
+                            if (T <= 32) k0 = __shfl_sync(0xffffffffu, (int)(kb & 15u), (int)(threadIdx.x & 31u) & ~(T - 1));
+                            else if (tid == 0) ws.k0 = (int)(kb & 15u);
+                        }
+                        if (T > 32) {
+                            group_sync<T>();                   // k0 visible; every thread of the window has its raw samples
+                            k0 = ws.k0;
+                        } else {
+                            __syncwarp();
+                        }
+                        refill_once();
+                        cf sel = v[0], tw = fx::mk(1.0f, 0.0f);
+                        constexpr bool TW_TABLE = T < 32;      // several windows per warp: k0 differs between lanes -> no branch
+                        if (T < 32) {
+                            // binary select tree on the bits of k0 (30 selects), twiddle from the W_N table
+                            const bool b0 = (k0 & 1) != 0, b1 = (k0 & 2) != 0, b2 = (k0 & 4) != 0, b3 = (k0 & 8) != 0;
+                            cf t8[8], t4[4], t2[2];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) t8[j] = fx::mk(b0 ? v[2 * j + 1].x : v[2 * j].x, b0 ? v[2 * j + 1].y : v[2 * j].y);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) t4[j] = fx::mk(b1 ? t8[2 * j + 1].x : t8[2 * j].x, b1 ? t8[2 * j + 1].y : t8[2 * j].y);
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) t2[j] = fx::mk(b2 ? t4[2 * j + 1].x : t4[2 * j].x, b2 ? t4[2 * j + 1].y : t4[2 * j].y);
+                            sel = fx::mk(b3 ? t2[1].x : t2[0].x, b3 ? t2[1].y : t2[0].y);
+                        } else
+                        switch (k0) {
+#define CERT_PICK(K) case K: sel = v[K]; tw = tw0[K]; break;
+                            CERT_PICK(1) CERT_PICK(2) CERT_PICK(3) CERT_PICK(4) CERT_PICK(5) CERT_PICK(6) CERT_PICK(7) CERT_PICK(8)
+                            CERT_PICK(9) CERT_PICK(10) CERT_PICK(11) CERT_PICK(12) CERT_PICK(13) CERT_PICK(14) CERT_PICK(15)
+#undef CERT_PICK
+                            default: break;
+                        }
+                        if (TW_TABLE) tw = pr_twn[(tid * k0) & (N - 1)];
+                        cval = ff::fcmul(sel, tw);
                     }
-                    if (T > 32) {
-                        group_sync<T>();                       // k0 visible; every thread of the window has its raw samples
-                        k0 = ws.k0;
+                    if (PR::R > 1) {
+                        // T > 32: warp ka forms its output of the R-point transform across the window's warps.  Two meeting
+                        // buffers, alternating: a warp may start the next step while another still reads this one.
+                        cf* ub = pr_ub + (u & 1u) * T;
+                        ub[tid] = cval;
+                        group_sync<T>();
+                        refill_once();
                         const int fsq = ws.fail_seq;           // verdict of the previous pruned step, published before this barrier
                         if (fsq != pr_seen) { pr_seen = fsq; pr_failed = true; }
-                    } else {
-                        __syncwarp();
-                    }
-                    refill_once();
-                    cf sel = v[0], tw = fx::mk(1.0f, 0.0f);
-                    constexpr bool TW_TABLE = SOA || T < 32;   // several windows per warp: k0 differs between lanes -> no branch
-                    if (T < 32) {
-                        // binary select tree on the bits of k0 (30 selects), twiddle from the W_N table
-                        const bool b0 = (k0 & 1) != 0, b1 = (k0 & 2) != 0, b2 = (k0 & 4) != 0, b3 = (k0 & 8) != 0;
-                        cf t8[8], t4[4], t2[2];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) t8[j] = fx::mk(b0 ? v[2 * j + 1].x : v[2 * j].x, b0 ? v[2 * j + 1].y : v[2 * j].y);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) t4[j] = fx::mk(b1 ? t8[2 * j + 1].x : t8[2 * j].x, b1 ? t8[2 * j + 1].y : t8[2 * j].y);
-#pragma unroll
-                        for (int j = 0; j < 2; ++j) t2[j] = fx::mk(b2 ? t4[2 * j + 1].x : t4[2 * j].x, b2 ? t4[2 * j + 1].y : t4[2 * j].y);
-                        sel = fx::mk(b3 ? t2[1].x : t2[0].x, b3 ? t2[1].y : t2[0].y);
-                    } else
-                    switch (k0) {
-#define CERT_PICK(K) case K: sel = v[K]; if (!TW_TABLE) tw = tw0[K]; break;
-                        CERT_PICK(1) CERT_PICK(2) CERT_PICK(3) CERT_PICK(4) CERT_PICK(5) CERT_PICK(6) CERT_PICK(7) CERT_PICK(8)
-                        CERT_PICK(9) CERT_PICK(10) CERT_PICK(11) CERT_PICK(12) CERT_PICK(13) CERT_PICK(14) CERT_PICK(15)
-#undef CERT_PICK
-                        default: break;
-                    }
-                    if (TW_TABLE) tw = pr_twn[(tid * k0) & (N - 1)];
-                    cf cval = ff::fcmul(sel, tw);
-                    if (PR::R > 1) {
-                        // T > 32: warp ka forms its output of the R-point transform across the window's warps
-                        pr_ub[tid] = cval;
-                        group_sync<T>();
                         const int ka = tid >> 5, l5 = tid & 31;
-                        cf acc = pr_ub[l5];
+                        cf acc = ub[l5];
 #pragma unroll
                         for (int w = 1; w < PR::R; ++w) {
-                            const cf t = ff::fcmul(pr_ub[l5 + 32 * w], pr_wr[(w * ka) & (PR::R - 1)]);
+                            const cf t = ff::fcmul(ub[l5 + 32 * w], pr_wr[(w * ka) & (PR::R - 1)]);
                             acc = ff::add(acc, t);
                         }
                         cval = ff::fcmul(acc, pr_twc);
@@ -786,20 +789,23 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                             ws.tq[ka] = qmax;
                             ws.tbin[ka] = k0 + 16 * (ka + PR::R * (int)(__brev((unsigned)lt) >> (32 - PR::LW)));
                             ws.te[ka] = en;
+                            ws.tk0[ka] = k0;
                             __threadfence_block();
                             const int ticket = atomicAdd(&ws.tcnt, 1);
                             if (ticket == PR::R - 1) {
                                 __threadfence_block();
                                 ws.tcnt = 0;
                                 unsigned bq = 0u; int bb = 0; float et = 0.0f;
+                                bool agree = true;                 // every warp transformed the same bin class
 #pragma unroll
                                 for (int w = 0; w < PR::R; ++w) {
                                     const unsigned qw = ws.tq[w];
                                     et += ws.te[w];
+                                    agree = agree && ws.tk0[w] == k0;
                                     if (qw > bq) { bq = qw; bb = ws.tbin[w]; }
                                 }
                                 const float q1 = __uint_as_float(bq);
-                                const bool cert = (q1 > tier1 * et) && (et < 1.0e30f) && (q1 >= 8.3e-25f);
+                                const bool cert = agree && (q1 > tier1 * et) && (et < 1.0e30f) && (q1 >= 8.3e-25f);
                                 if (active) {
                                     if (cert) {
                                         if (have_sync && s < 2) ws.sw[s] = bb;
@@ -968,7 +974,6 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 }
                 if (pr_skip) --pr_skip;
                 }                                              // full transform
-                }                                              // rotated samples (not the geometric variant)
                 if (PRUNE && fast) {
                     if (pr_failed) { pr_backoff = min(2u * pr_backoff + 16u, 4096u); pr_skip = pr_backoff; }
                     else pr_backoff = 0u;
