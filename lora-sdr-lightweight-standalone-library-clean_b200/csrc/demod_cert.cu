@@ -609,9 +609,10 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 float mw = 0.0f;
                 cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);                   // (sum re^2, sum im^2), two chains
                 float en;
-                if (!(GEOM && fast)) {
+                auto load_rotated = [&]() {
                     // rotated samples: the full transform and the pruned transform of the variants with tables
                     if (GEOM && !f_ready) make_f();
+                    e0 = fx::mk(0.0f, 0.0f); e1 = fx::mk(0.0f, 0.0f);
 #pragma unroll
                     for (int c = 0; c < 16; ++c) {
                         const cf r = raw[T * c];
@@ -621,7 +622,13 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                         v[c] = y;
                     }
                     en = (e0.x + e0.y) + (e1.x + e1.y);
-                } else {
+                };
+                // the full transform runs when the pruned one is not tried -- or, for single-warp windows, when it has just
+                // failed: the raw samples are still in the slot (the pruned transform never writes there)
+                bool full = !(PRUNE && fast);
+                if (PRUNE && fast && !GEOM) {
+                    load_rotated();
+                } else if (PRUNE && fast) {
 #pragma unroll
                     for (int c = 0; c < 16; ++c) {
                         const cf r = raw[T * c];
@@ -632,9 +639,8 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     // energy of the rotated samples: |f_c| = scale up to the rounding of sin^2 + cos^2 (a hair of head-room)
                     en = ((e0.x + e0.y) + (e1.x + e1.y)) * (scale * scale) * 1.000002f;
                 }
-                if (active) m = fmaxf(m, mw);
-
                 if (PRUNE && fast) {
+                    if (active) m = fmaxf(m, mw);
                     // ---- pruned transform (fft_prune.cuh): the tone's bin class k0, then ONE value per thread -----------------
                     int k0 = 0;
                     cf cval;
@@ -768,18 +774,15 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                         const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
                         if (active) {
                             if (!cert && !(en < 1.0e30f)) suspicious = true;
-                            if (qb == qmax) {                                  // the lane that holds the top bin (unique when certified)
-                                if (cert) {
-                                    const int idx = k0 + 16 * (int)(__brev((unsigned)lw) >> (32 - PR::LW));
-                                    if (have_sync && s < 2) ws.sw[s] = idx;
-                                    else ws.sym[have_sync ? s - 2 : s] = (uint16_t)idx;
-                                } else {
-                                    atomicOr(&ws.fb[s >> 5], 1u << (s & 31));
-                                }
+                            if (qb == qmax && cert) {                          // the lane that holds the top bin (unique when certified)
+                                const int idx = k0 + 16 * (int)(__brev((unsigned)lw) >> (32 - PR::LW));
+                                if (have_sync && s < 2) ws.sw[s] = idx;
+                                else ws.sym[have_sync ? s - 2 : s] = (uint16_t)idx;
                             }
-                            if (tid == 0 && cert) ++st_pruned;
                         }
                         pr_failed = __any_sync(0xffffffffu, active && !cert) != 0;
+                        if (pr_failed) full = true;                            // same step, full transform (tier 1 / tier 2)
+                        else if (tid == 0 && active) ++st_pruned;
                     } else {
                         // every warp publishes its top bin; the last one to arrive decides for the window
                         const unsigned ball = __ballot_sync(0xffffffffu, qb == qmax);
@@ -820,7 +823,10 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                             }
                         }
                     }
-                } else {
+                }
+                if (full) {
+                load_rotated();
+                if (active) m = fmaxf(m, mw);
                 unsigned key[16];
 #if defined(CERT_ABLATE)
                 // measurement-only build (tools/ablate.sh, never the product): the walk without its transform -- what the
@@ -844,7 +850,7 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     }
                     unsigned long long* ex = reinterpret_cast<unsigned long long*>(win);
                     group_sync<T>();                           // every thread of the window has its raw samples
-                    refill();
+                    refill_once();
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
                         ex[fs::sf7_wr(0, q) + tid] = fs::bits(pr[q]);
@@ -872,11 +878,11 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 // read its own samples from, unless the window sits one entry later (odd alignment): no barrier needed first.
                 constexpr bool OWN = F::stride(0, SF - 1) == (1 << (SF - 1));
                 const bool pre_sync = !OWN || roff != tid;
-                if (pre_sync) { group_sync<T>(); refill(); }  // every thread of the window has its raw samples
+                if (pre_sync) { group_sync<T>(); refill_once(); }  // every thread of the window has its raw samples
 #pragma unroll
                 for (int e = 0; e < 16; ++e) win[wr0 + F::wr_off(0, e)] = v[e];
                 group_sync<T>();
-                if (!pre_sync) refill();
+                if (!pre_sync) refill_once();
 #pragma unroll
                 for (int e = 0; e < 16; ++e) v[e] = win[rd0 + F::rd_off(0, e)];
                 F::butterflies(1, v);
