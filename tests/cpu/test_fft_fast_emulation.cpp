@@ -16,6 +16,7 @@
 #include <vector>
 #include "fft_fast.cuh"
 #include "fft_soa.cuh"
+#include "fft_prune.cuh"
 
 using ff::cf;
 
@@ -232,9 +233,125 @@ static bool run_soa7(unsigned seed)
     return ok;
 }
 
+// The pruned transform (fft_prune.cuh): for a random bin class k0, the value chain of demod_cert.cu's pruned step --
+// pass 0 output k0 (or, geometric variant, sum_c r_c h^c on the raw samples with the rotation folded into h), pass-0
+// twiddle, [T > 32: R-point sum across warps + W_T twiddle], radix-2 lane transform with the stage table -- replayed
+// lane by lane with shuffles modelled as array reads.  Every bin of the class must match the double DFT of the
+// rotated samples and the bin map must cover the class exactly once.
+template <int SF>
+static bool run_prune(unsigned seed, bool geometric)
+{
+    using P = ff::Plan<SF>;
+    using Q = fp::Prune<SF>;
+    constexpr int N = P::N, T = P::T, W = Q::W, R = Q::R, LW = Q::LW;
+    const double PI = 3.14159265358979323846;
+    bool ok = true;
+    srand(seed);
+    const double rate = -2 * PI * 0.37 / N;                          // the walk's rotation exp(j rate i)
+    std::vector<std::complex<double>> x(N), y(N);
+    for (int i = 0; i < N; ++i) {
+        x[i] = { (double)rand() / RAND_MAX - 0.5, (double)rand() / RAND_MAX - 0.5 };
+        y[i] = x[i] * std::polar(1.0, rate * i);
+    }
+    std::vector<cf> tws((size_t)(LW > 1 ? LW - 1 : 1) * W);
+    for (int s = 0; s + 1 < LW; ++s)
+        for (int l = 0; l < W; ++l) {
+            const double a = -2 * PI * Q::stage_exp(s, l) / W;
+            tws[(size_t)s * W + l] = ff::mk((float)cos(a), (float)sin(a));
+        }
+    double max_rel = 0.0;
+    for (int k0 = 0; k0 < 16; ++k0) {
+        std::vector<cf> val(T);
+        for (int tid = 0; tid < T; ++tid) {
+            cf v[16];
+            cf pv;
+            if (geometric) {
+                // h = G W16^k0, G = exp(j rate T); powers as the kernel builds them (float products of accurate factors)
+                cf hp[4];
+                for (int m = 0; m < 4; ++m) {
+                    const double ga = rate * (double)(T << m), wa = -2 * PI * (double)((k0 << m) & 15) / 16.0;
+                    hp[m] = ff::fcmul(ff::mk((float)cos(ga), (float)sin(ga)), ff::mk((float)cos(wa), (float)sin(wa)));
+                }
+                for (int c = 0; c < 16; ++c) v[c] = ff::mk((float)x[tid + T * c].real(), (float)x[tid + T * c].imag());
+                auto cma = [](cf acc, cf a, cf w) {
+                    return ff::mk(ff::fma_(-a.y, w.y, ff::fma_(a.x, w.x, acc.x)), ff::fma_(a.y, w.x, ff::fma_(a.x, w.y, acc.y)));
+                };
+                for (int c = 0; c < 8; ++c) v[c] = cma(v[c], v[c + 8], hp[3]);
+                for (int c = 0; c < 4; ++c) v[c] = cma(v[c], v[c + 4], hp[2]);
+                for (int c = 0; c < 2; ++c) v[c] = cma(v[c], v[c + 2], hp[1]);
+                pv = cma(v[0], v[1], hp[0]);
+                pv = ff::fcmul(pv, ff::mk((float)cos(rate * tid), (float)sin(rate * tid)));      // F_tid (scale 1)
+            } else {
+                for (int c = 0; c < 16; ++c) v[c] = ff::mk((float)y[tid + T * c].real(), (float)y[tid + T * c].imag());
+                ff::dft16(v);
+                pv = v[k0];
+            }
+            const double a = -2 * PI * (double)P::tw0_exp(tid, k0) / N;
+            val[tid] = ff::fcmul(pv, ff::mk((float)cos(a), (float)sin(a)));
+        }
+        // cross-warp stage
+        std::vector<cf> c(T);
+        for (int tid = 0; tid < T; ++tid) {
+            if (R == 1) { c[tid] = val[tid]; continue; }
+            const int ka = tid >> 5, l = tid & 31;
+            cf acc = val[l];
+            for (int w = 1; w < R; ++w) {
+                const double a = -2 * PI * (double)Q::sum_exp(ka, w) / R;
+                acc = ff::add(acc, ff::fcmul(val[l + 32 * w], ff::mk((float)cos(a), (float)sin(a))));
+            }
+            const double a = -2 * PI * (double)Q::cross_exp(ka, l) / T;
+            c[tid] = ff::fcmul(acc, ff::mk((float)cos(a), (float)sin(a)));
+        }
+        // lane transform: stage s pairs lane l with l ^ h
+        for (int s = 0; s < LW; ++s) {
+            const int h = Q::half(s);
+            std::vector<cf> nx(T);
+            for (int tid = 0; tid < T; ++tid) {
+                const int l = tid & (W - 1);
+                const cf o = c[tid ^ h];
+                const bool upper = (l & h) != 0;
+                const cf own = upper ? ff::mk(-c[tid].x, -c[tid].y) : c[tid];
+                cf r = ff::add(o, own);
+                if (s != LW - 1) r = ff::fcmul(r, tws[(size_t)s * W + l]);
+                nx[tid] = r;
+            }
+            c.swap(nx);
+        }
+        // compare with the double DFT of the rotated samples; the map must hit every bin of the class once
+        std::vector<int> hit(N, 0);
+        double peak = 0.0;
+        std::vector<std::complex<double>> X(N);
+        for (int k = k0; k < N; k += 16) {
+            std::complex<double> acc = 0;
+            for (int i = 0; i < N; ++i) acc += y[i] * std::polar(1.0, -2 * PI * (double)((long)i * k % N) / N);
+            X[k] = acc;
+        }
+        for (int i = 0; i < N; ++i) peak += std::abs(y[i]);
+        for (int tid = 0; tid < T; ++tid) {
+            const int bin = Q::bin(k0, tid >> 5 & (R - 1), tid & (W - 1));
+            if (bin < 0 || bin >= N || (bin & 15) != k0 || hit[bin]++) { ok = false; continue; }
+            max_rel = std::max(max_rel, std::abs(std::complex<double>(c[tid].x, c[tid].y) - X[bin]) / peak);
+        }
+        for (int k = k0; k < N; k += 16) if (hit[k] != 1) ok = false;
+    }
+    // per-bin error against sum |y_i| (the certificate's unit): the budget for "our side" is 96 * 2^-24 = 5.7e-6
+    if (max_rel > 2e-6) ok = false;
+    std::printf("{\"sf\": %d, \"layout\": \"pruned %s\", \"lanes\": %d, \"warps\": %d, \"max_err_over_sum_abs\": %.3g, \"worst_bank_conflict\": 1, \"match\": %s}\n",
+                SF, geometric ? "geometric" : "pass0", W, R, max_rel, ok ? "true" : "false");
+    return ok;
+}
+
 int main()
 {
     bool ok = true;
+    ok &= run_prune<7>(11, true);
+    ok &= run_prune<8>(12, true);
+    ok &= run_prune<9>(13, true);
+    ok &= run_prune<7>(14, false);
+    ok &= run_prune<10>(15, false);
+    ok &= run_prune<11>(16, false);
+    ok &= run_prune<12>(17, false);
+    ok &= run_prune<12>(18, true);
     ok &= run_soa7(7);
     ok &= run<7>(1);
     ok &= run<8>(2);

@@ -42,9 +42,12 @@ def test_glibc_math_restatement():
 def test_fft_fast_emulation():
     """csrc/fft_fast.cuh and fft_soa.cuh (the certified path's throughput transform) emulated thread by thread: spectrum
     within 2e-6 of a double DFT, every exchange address written once and read once inside the window slot, every 64-bit
-    access phase bank-conflict free, output bin map a permutation -- SF7 (both register layouts) to SF12."""
+    access phase bank-conflict free, output bin map a permutation -- SF7 (both register layouts) to SF12; and the pruned
+    transform of fft_prune.cuh (pass-0 and geometric variants, single- and multi-warp windows): every bin of every class
+    against the double DFT, bin map covering each class exactly once."""
     exe = compile_cpp("test_fft_fast_emulation", ["-lm"])
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
-    assert len(lines) == 7 and all(l["match"] and l["worst_bank_conflict"] == 1 for l in lines)
+    assert len(lines) == 15 and all(l["match"] and l["worst_bank_conflict"] == 1 for l in lines)
+    assert sum("pruned" in l.get("layout", "") for l in lines) == 8

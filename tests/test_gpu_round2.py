@@ -362,6 +362,49 @@ def test_certified_fallbacks_fire(phy, lp, oracle):
     print("golden detection inputs: %d windows, %d replayed" % (c1[0] - c0[0], c1[1] - c0[1]))
 
 
+@pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
+def test_pruned_transform_policy_over_snr_and_sync_words(phy, lp, oracle, sf):
+    """The pruned transform (one bin class, accepted by the Parseval test) and its hand-over to the full transform:
+    packets whose per-sample SNR steps from clean to -6 dB and back, sync words that put the reference's carrier
+    correction anywhere between 0 and 1 bin (0x88: half a bin, where the top bin holds less than 3/4 of the energy and
+    the pruned test must refuse), two tones in different bin classes.  Every packet equals the oracle; the counters
+    show both outcomes."""
+    rng = np.random.default_rng(900 + sf)
+    N = 1 << sf
+    S = 10 if sf <= 9 else (6 if sf < 12 else 4)
+    down = oracle.gen_chirp(N, 1, N, 0.0, True, 1.0, 0.0, 1.0)[0]
+    rows = []
+    snrs = [None, 20.0, 10.0, 6.0, 3.0, 0.0, -6.0, None, 6.0, None]
+    for snr in snrs:
+        for sync in (0x12, 0x34, 0x88, 0xF1):
+            syms = rng.integers(0, N, S - 2).astype(np.uint16)
+            d = (oracle.lora_modulate(syms, sf, 1, 125000, 1.0, sync).reshape(-1, N) * down[None, :]).astype(np.complex64).ravel()
+            if snr is not None:
+                sg = np.float32(10 ** (-snr / 20) / np.sqrt(2))
+                d = (d + sg * (rng.standard_normal(d.size) + 1j * rng.standard_normal(d.size))).astype(np.complex64)
+            rows.append(d)
+    two = rows[0].copy()                                          # a second tone of 0.8x in another class on top of window 3
+    two[3 * N:4 * N] += (0.8 * np.exp(2j * np.pi * ((int(rng.integers(0, N)) | 1) ^ 6) * np.arange(N) / N)).astype(np.complex64)
+    rows.append(two)
+    iq = np.stack(rows)
+    c0 = phy.cert_stats()
+    check_legacy(phy, lp, oracle, iq, sf, 1, 0)
+    c1 = phy.cert_stats()
+    windows, replayed, pruned = c1[0] - c0[0], c1[1] - c0[1], c1[4] - c0[4]
+    assert windows >= iq.shape[0] * S
+    assert 0 < pruned < windows, (windows, pruned)
+    print("sf%d: %d windows, %d settled by the pruned transform, %d replayed exactly" % (sf, windows, pruned, replayed))
+    # the same batch, clean packets only: everything but the half-bin sync word is settled by the pruned transform
+    clean = np.stack([r for r, k in zip(rows, [sn for sn in snrs for _ in range(4)]) if k is None])
+    c0 = phy.cert_stats()
+    check_legacy(phy, lp, oracle, clean, sf, 1, 0)
+    c1 = phy.cert_stats()
+    assert c1[4] - c0[4] >= (c1[0] - c0[0]) // 2
+    # single-warp windows hand a refused window to the full transform in the same step; multi-warp windows replay it
+    # exactly and back off (a bounded number of retries)
+    assert c1[1] == c0[1] if sf <= 9 else c1[1] - c0[1] <= (c1[0] - c0[0]) // 4
+
+
 def test_every_kernel_family_small_cases():
     """tools/sanitize_driver.py (written for compute-sanitizer, which is closed on this pool) as a plain run: every kernel
     family on ragged / oversized / odd-aligned / loud / noise-only inputs must complete without a CUDA error."""
