@@ -39,6 +39,11 @@ namespace lk {
 #define CERT_CTAS_PER_SM 2
 #endif
 
+#ifndef CERT_CTAS_SMALL
+#define CERT_CTAS_SMALL CERT_CTAS_PER_SM      // resident CTAs per SM for SF7-9 (with CERT_CTA_SMALL: the occupancy A/B knob)
+#endif
+constexpr int cert_ctas(int sf) { return sf <= 9 ? CERT_CTAS_SMALL : CERT_CTAS_PER_SM; }
+
 #ifndef CERT_CTA_SMALL
 #define CERT_CTA_SMALL 256                    // threads per CTA for SF7-9 (a window is at most one warp there: any multiple of 32)
 #endif
@@ -71,6 +76,11 @@ namespace lk {
 #ifndef CERT_GEOM_MAX_T
 #define CERT_GEOM_MAX_T 32                    // widest window (threads) that takes the geometric variant: measured slower at SF12 (T = 256),
                                               // level at SF10 / SF11; multi-warp windows keep pass 0 + first-thread class
+#endif
+
+#ifndef CERT_ONE_LEADER
+#define CERT_ONE_LEADER 0                     // 1: lane 0 issues the bulk copies of all the warp's windows in a row -- measured SLOWER (SF7 4845 -> 4051 GB/s):
+                                              // the diverged leaders compute their addresses in parallel and only the copy itself goes through the elect loop
 #endif
 
 #ifndef CERT_L2_AHEAD
@@ -125,7 +135,8 @@ struct CertCfg {
     static constexpr size_t pr_bytes = CERT_PRUNE ? pr_ub + (PR::R > 1 ? (size_t)DOMS * 2 * T * sizeof(cf) : 0) : 0;   // two buffers: steps alternate
     static constexpr size_t fixed_bytes = (size_t)DOMS * sizeof(CertShared) + red_bytes + (size_t)F::TW1_SIZE * sizeof(cf) + tw0_bytes + pr_bytes + 256;
     // as many ring stages as fit CERT_CTAS_PER_SM CTAs into the 227 KB of an SM, at most 3
-    static constexpr int fit = (int)(((size_t)227 * 1024 / CERT_CTAS_PER_SM - 1024 - fixed_bytes) / stage_bytes);
+    static constexpr int fit = (int)(((size_t)227 * 1024 / cert_ctas(SF) - 1024 - fixed_bytes) / stage_bytes);
+    static_assert(fit >= 2, "the ring needs two stages");
     static constexpr int STAGES = fit >= 3 ? 3 : 2;
     static constexpr size_t slot_bytes = stage_bytes * STAGES;
     static constexpr size_t bar_off = slot_bytes;
@@ -200,7 +211,7 @@ __device__ __forceinline__ float cert_scan_max(const cf* __restrict__ pkt, uint3
 }
 
 template <int SF, bool EXTRA, int CTA>
-__global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const DemodArgs a)
+__global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const DemodArgs a)
 {
     using C = CertCfg<SF, CTA>;
     using P = fx::Plan<SF>;
@@ -557,9 +568,27 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                     ptx::mbar_arrive_sa(bar0 + 8u * (uint32_t)stg);
                 }
             };
-            if (tid == 0) {
+            constexpr bool ONE_LEADER = CERT_ONE_LEADER != 0 && GD > 1;
+            const uint32_t slotb = ptx::smem_u32(slots);
+            auto prefetch_step = [&](uint32_t s_first, int stg) {    // lane 0 only: the GD windows of one step
+#pragma unroll
+                for (int g = 0; g < GD; ++g) {
+                    const uint32_t sp = s_first + (uint32_t)g;
+                    if (sp < total) {
+                        const uint32_t base = regular ? sp * (uint32_t)N : shifted_base(sp, (uint32_t)N, t_off, count);
+                        fetch_window_sa<N>(slotb + (uint32_t)(g * C::PITCH * sizeof(cf)) + (uint32_t)stg * SLOT_B, pkt + base,
+                                           bar0 + 8u * (uint32_t)stg);
+                    } else {
+                        ptx::mbar_arrive_sa(bar0 + 8u * (uint32_t)stg);
+                    }
+                }
+            };
+            if (ONE_LEADER ? lane == 0 : tid == 0) {
                 int stg = stage;
-                for (uint32_t u = 0; u < (uint32_t)(STAGES - 1) && u < n_units; ++u) { prefetch(u * GD + gq, stg); stg = stg + 1 == STAGES ? 0 : stg + 1; }
+                for (uint32_t u = 0; u < (uint32_t)(STAGES - 1) && u < n_units; ++u) {
+                    if (ONE_LEADER) prefetch_step(u * GD, stg); else prefetch(u * GD + gq, stg);
+                    stg = stg + 1 == STAGES ? 0 : stg + 1;
+                }
             }
             uint32_t s = (uint32_t)gq;                              // this window's symbol; += GD per step
             int roff = (odd_pkt ? 1 : 0) + tid;
@@ -570,10 +599,13 @@ __global__ void __launch_bounds__(CTA, CERT_CTAS_PER_SM) demod_cert_kernel(const
                 // last generic-proxy store there is followed by fence.proxy.async), so no end-of-step barrier is needed.
                 constexpr bool EARLY = CERT_EARLY_REFILL != 0 && DT <= 32;
                 auto refill_now = [&]() {
-                    if (tid == 0) {
+                    if (ONE_LEADER ? lane == 0 : tid == 0) {
                         int stg = stage + (STAGES - 1);
                         if (stg >= STAGES) stg -= STAGES;
-                        if (u + (STAGES - 1) < n_units) prefetch(s + (STAGES - 1) * GD, stg);
+                        if (u + (STAGES - 1) < n_units) {
+                            if (ONE_LEADER) prefetch_step(s + (STAGES - 1) * GD, stg);       // lane 0: s is the step's first symbol
+                            else prefetch(s + (STAGES - 1) * GD, stg);
+                        }
                     }
                 };
                 auto refill = [&]() { if (!EARLY) refill_now(); };
@@ -1114,7 +1146,7 @@ static cudaError_t launch_cert_sf(const DemodArgs& a, int sm_count, cudaStream_t
         cudaFuncSetAttribute(demod_cert_kernel<SF, true, CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
         attr_done[dev & 63].store(true, std::memory_order_release);
     }
-    const unsigned max_ctas = (unsigned)sm_count * CERT_CTAS_PER_SM;      // persistent grid: every CTA resident
+    const unsigned max_ctas = (unsigned)sm_count * cert_ctas(SF);         // persistent grid: every CTA resident
     const unsigned need = (a.n_packets + C::DOMS - 1) / C::DOMS;
     const unsigned grid = need < max_ctas ? need : max_ctas;
     if (extra) demod_cert_kernel<SF, true, CTA><<<grid, CTA, C::bytes, stream>>>(a);
