@@ -74,8 +74,7 @@ constexpr int cert_ctas(int sf) { return sf <= 9 ? CERT_CTAS_SMALL : CERT_CTAS_P
 #endif
 
 #ifndef CERT_GEOM_MAX_T
-#define CERT_GEOM_MAX_T 32                    // widest window (threads) that takes the geometric variant: measured slower at SF12 (T = 256),
-                                              // level at SF10 / SF11; multi-warp windows keep pass 0 + first-thread class
+#define CERT_GEOM_MAX_T 256                   // widest window (threads) that takes the geometric variant (A/B knob)
 #endif
 
 #ifndef CERT_ONE_LEADER
@@ -681,20 +680,20 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
                         // thread is 2 pi (bin mod 16) / 16 once the rotation's own step G is added; four pairs per thread,
                         // summed over the warp.  (Every warp of a multi-warp window decides for itself -- a tone gives them
                         // all the same answer -- and the choices are compared before anything is accepted.)
-                        cf z = fx::mk(0.0f, 0.0f);
+                        if (T <= 32 || (tid >> 5) == 0) {              // multi-warp windows: the first warp decides
+                            cf z = fx::mk(0.0f, 0.0f);
 #pragma unroll
-                        for (int c = 0; c < 16; c += 4) {
-                            z.x = ff::fma_(v[c + 1].x, v[c].x, z.x); z.x = ff::fma_(v[c + 1].y, v[c].y, z.x);
-                            z.y = ff::fma_(v[c + 1].y, v[c].x, z.y); z.y = ff::fma_(-v[c + 1].x, v[c].y, z.y);
-                        }
+                            for (int c = 0; c < 16; c += 4) {
+                                z.x = ff::fma_(v[c + 1].x, v[c].x, z.x); z.x = ff::fma_(v[c + 1].y, v[c].y, z.x);
+                                z.y = ff::fma_(v[c + 1].y, v[c].x, z.y); z.y = ff::fma_(-v[c + 1].x, v[c].y, z.y);
+                            }
 #pragma unroll
-                        for (int off = PR::W / 2; off > 0; off >>= 1) {
-                            z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
-                            z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
-                        }
-                        if (T <= 32) { __syncwarp(); refill_once(); }
-                        z = ff::fcmul(z, geo_g1);
-                        {   // nearest multiple of 22.5 degrees, by octant folding (an inexact answer only costs a failed test)
+                            for (int off = PR::W / 2; off > 0; off >>= 1) {
+                                z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
+                                z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
+                            }
+                            z = ff::fcmul(z, geo_g1);
+                            // nearest multiple of 22.5 degrees, by octant folding (an inexact answer only costs a failed test)
                             const float ax = fabsf(z.x), ay = fabsf(z.y);
                             const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
                             int q = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
@@ -702,7 +701,15 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
                             if (z.x < 0.0f) q = 8 - q;
                             if (z.y < 0.0f) q = 16 - q;
                             k0 = q & 15;
+                            if (T > 32 && tid == 0) ws.k0 = k0;
                         }
+                        if (T <= 32) {
+                            __syncwarp();
+                        } else {
+                            group_sync<T>();                   // k0 visible; every thread of the window has its raw samples
+                            k0 = ws.k0;
+                        }
+                        refill_once();
                         // sum_c r_c h^c, h = G W16^k0, by halving: four levels of complex multiply-adds with h^8, h^4, h^2, h
                         const float4 hA = *reinterpret_cast<const float4*>(&ws.hp[4 * k0]);          // h, h^2
                         const float4 hB = *reinterpret_cast<const float4*>(&ws.hp[4 * k0 + 2]);      // h^4, h^8
