@@ -90,7 +90,8 @@ int  lora_phy_cuda_synchronize(lora_phy_cuda_ctx* ctx);
  * were redone after a max-abs misprediction, out[3] packets walked a second time.  No reference counterpart.       */
 int  lora_phy_cuda_cert_stats(lora_phy_cuda_ctx* ctx, uint64_t out[4]);
 /* The same counters and the later ones, n <= 8 of them: out[4] windows settled by the pruned transform (one bin class,
- * accepted by the Parseval test) without running the full one; out[5..7] reserved (zero).  No reference counterpart. */
+ * accepted by the Parseval test) without running the full one; out[5] packets the streaming first pass (SF10-12) handed
+ * to the certified kernel with every symbol still open; out[6..7] reserved (zero).  No reference counterpart.            */
 int  lora_phy_cuda_cert_stats_ex(lora_phy_cuda_ctx* ctx, uint64_t* out, size_t n);
 
 /* ---- demodulator: K1 + K2a ------------------------------------------------------------- */

@@ -173,10 +173,10 @@ class LoraPhyCuda:
         self._check(self.lib.lora_phy_cuda_synchronize(self.h))
 
     def cert_stats(self):
-        """(windows, fallback_windows, second_estimates, rewalked_packets, pruned_windows) of the certified demodulator
-        so far."""
-        out = (C.c_uint64 * 5)()
-        self._check(self.lib.lora_phy_cuda_cert_stats_ex(self.h, out, 5))
+        """(windows, fallback_windows, second_estimates, rewalked_packets, pruned_windows, lean_flagged_packets) of the
+        certified demodulator so far."""
+        out = (C.c_uint64 * 6)()
+        self._check(self.lib.lora_phy_cuda_cert_stats_ex(self.h, out, 6))
         return tuple(int(x) for x in out)
 
     def set_stream(self, stream_handle):

@@ -66,6 +66,7 @@ struct lora_phy_cuda_ctx {
     SfTables tab[13];
     std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
     DevBuf state, phases, tmp;                          // PacketState[], modulator phases, compensate scratch
+    DevBuf flag, pmax;                                  // lean route: one byte / one max-abs per packet (handed to the certified kernel)
     cf* sync_tab[3][13] = {};                            // stream detector tables per (bandwidth scale, sf): up | down | fine
     DevBuf txrx[3];                                      // tx/rx pipelines: symbols, status, host-variant results
     DevBuf mc[8];                                        // Monte-Carlo driver: payload, tx symbols, IQ, rx symbols, status+sync, decoded, len, flags
@@ -205,7 +206,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
     ctx->lfsr.release();
     for (auto& b : ctx->mc) b.release();
     for (auto& b : ctx->txrx) b.release();
-    ctx->state.release(); ctx->phases.release(); ctx->tmp.release();
+    ctx->state.release(); ctx->phases.release(); ctx->tmp.release(); ctx->flag.release(); ctx->pmax.release();
     ctx->d_in.release(); ctx->d_out.release(); ctx->d_aux.release();
     ctx->h_in.release(); ctx->h_out.release();
     for (int i = 0; i < 2; ++i) {
@@ -326,8 +327,37 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.time_offset = d_to;
     a.status = d_status;
     a.force_exact = 0;
+    a.unit_scale = 0; a.skip_sync = 0; a.flagged = nullptr; a.only_flagged = nullptr; a.pmax = nullptr;
     a.cert_stats = ctx->cert_stats;
     unsigned launches = 0;
+    // SF10-12, pre-dechirped IQ (the cfg-3 shape): three launches.  (1) the exact two-symbol estimator alone, assuming the
+    // packet needs no 1/max normalisation; (2) the streaming pruned transform, one warp per packet (demod_lean.cu), which
+    // checks that assumption and flags every packet it cannot settle; (3) the certified kernel over the flagged packets.
+    static const bool lean_off = getenv("LORA_PHY_NO_LEAN") != nullptr;
+    if (!lean_off && !(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&
+        lk::lean_supported((int)cfg->sf, a) && lk::cert_supported((int)cfg->sf, a)) {
+        CK(ctx->flag.reserve(n_packets));
+        CK(ctx->pmax.reserve(n_packets * sizeof(float)));
+        CK(cudaMemsetAsync(ctx->flag.p, 0, n_packets, ctx->stream));
+        lk::DemodArgs p = a;
+        p.unit_scale = 1; p.skip_sync = 1; p.est_uniform = 2;
+        cudaError_t e = lk::launch_demod((int)cfg->sf, p, ctx->sm_count, ctx->stream, true, false, &launches);
+        if (e != cudaSuccess) return fail(ctx, -EIO, "estimator launch", e);
+        p = a;
+        p.flagged = static_cast<uint8_t*>(ctx->flag.p);
+        p.pmax = static_cast<float*>(ctx->pmax.p);
+        e = lk::launch_demod_lean((int)cfg->sf, p, ctx->sm_count, ctx->stream);
+        ++launches;
+        if (e != cudaSuccess) return fail(ctx, -EIO, "lean demodulator launch", e);
+        p = a;
+        p.only_flagged = static_cast<const uint8_t*>(ctx->flag.p);
+        p.pmax = static_cast<float*>(ctx->pmax.p);
+        e = lk::launch_demod_cert((int)cfg->sf, p, ctx->sm_count, ctx->stream);
+        ++launches;
+        ctx->launches += launches;
+        if (e != cudaSuccess) return fail(ctx, -EIO, "certified demodulator launch", e);
+        return 0;
+    }
     // default: one launch, one pipeline per packet, margin-certified throughput transform with exact replay of the
     // windows that cannot be proven (demod_cert.cu)
     if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&

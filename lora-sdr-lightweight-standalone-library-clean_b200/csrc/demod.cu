@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) prepass_kernel(const DemodArgs
         // -- 1. max-abs scan (legacy path only) : LoRaDemod.cpp:61-68 --
         PacketState st; st.scale = 1.0f; st.rate = 0.0f; st.t_off = 0; st.flags = 0;
         int status = 0;
-        if (a.mode == MODE_LEGACY) {
+        if (a.mode == MODE_LEGACY && !a.unit_scale) {
             float m = 0.0f;
             const bool vec = ((reinterpret_cast<uintptr_t>(pkt) & 15) == 0);
             if (vec) {
@@ -177,9 +177,11 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) prepass_kernel(const DemodArgs
         // -- 3. sync symbols and bookkeeping : LoRaDemod.cpp:166-196 --
         const bool have_sync = total >= 2;
         int sw[2] = { 0, 0 };
+        if (!a.skip_sync) {
 #pragma unroll
-        for (uint32_t s = 0; s < 2; ++s)
-            sw[s] = demod_symbol<SF, false>(a, pkt, count, s, run && have_sync, st, tid, buf0, buf1, flip, red);
+            for (uint32_t s = 0; s < 2; ++s)
+                sw[s] = demod_symbol<SF, false>(a, pkt, count, s, run && have_sync, st, tid, buf0, buf1, flip, red);
+        }
         if (tid == 0 && active) {
             if (run) {
                 if (a.state) a.state[pid] = st;

@@ -346,6 +346,8 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
     int pr_seen = 0;
 
     for (uint32_t pid = blockIdx.x * C::DOMS + dom; pid < a.n_packets; pid += n_pipes) {
+        const int lean_flag = a.only_flagged ? (int)a.only_flagged[pid] : 1;
+        if (lean_flag == 0) continue;                                   // third pass of the lean route: flagged packets only
         const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
         const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
         const uint32_t total = count / (uint32_t)N;
@@ -384,6 +386,16 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
         int t_off = 0, t_off_walk = 0;
         bool walked = false;
         const bool odd_pkt = window_is_odd(pkt);
+        // Lean route, flag 2: the streaming pass has settled every symbol with the rate of a unit-scale estimate and found
+        // the packet's max-abs above 1.  Its decisions are scale-invariant (as a finished walk's are, see below), so this
+        // pass only repeats the two exact estimator symbols with the true scale -- cfo / time_offset bit for bit -- and
+        // keeps the lean symbols when t_off is unchanged and the rate moved by no more than the budgeted tolerance.
+        bool verify_only = lean_flag == 2 && legacy && !all_exact;
+        if (verify_only) {
+            const PacketState ps = a.state[pid];
+            walked = true; rate_walk = ps.rate; t_off_walk = ps.t_off;
+            use_max = a.pmax[pid]; known = true;
+        }
 
 #pragma unroll 1
         for (int attempt = 0; attempt < 3 && !(flags & PS_SKIP); ++attempt) {
@@ -485,13 +497,14 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
             have_metrics = true;
 
             if (!(use_max < 3.0e38f)) all_exact = true;        // 1/inf == 0 wipes the packet: nothing is scale-invariant there
-            if (all_exact) break;
+            if (all_exact) { verify_only = false; break; }
             if (walked) {
                 // second estimate after a max-abs misprediction: the finished walk is scale-invariant, so it stands when
                 // it used the same window bases and a rate within the tolerance its certification margin budgeted
                 if (lane == 0) ++st_est2;
                 const bool same = t_off == t_off_walk && fabsf(fx::fsub(rate, rate_walk)) * (float)N <= CERT_RATE_TOL;
                 if (same) break;
+                verify_only = false;                           // lean symbols do not stand: this pass walks the packet
                 if (lane == 0) ++st_rewalk;
                 if (lane < CERT_CAP / 32) ws.fb[lane] = 0u;
                 csync<DT>();
@@ -1112,7 +1125,7 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
 
         // ---- bookkeeping: LoRaDemod.cpp:166-196; the packet's symbols leave in one coalesced run ----------------------
         csync<DT>();
-        if (run) {
+        if (run && !verify_only) {
             const uint32_t n_stage = n_data < (uint32_t)CERT_CAP ? n_data : (uint32_t)CERT_CAP;
             for (uint32_t i = lane; i < n_stage; i += DT) out_sym[i] = ws.sym[i];
         }
@@ -1122,7 +1135,7 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
                 if (a.cfo) a.cfo[pid] = cfo;
                 if (a.time_offset) a.time_offset[pid] = toff;
             }
-            if (a.sync) {
+            if (a.sync && !verify_only) {
                 const unsigned shift = SF > 4 ? SF - 4 : 0;
                 a.sync[pid] = (run && have_sync) ? (uint8_t)((((ws.sw[0] >> shift) & 0xf) << 4) | ((ws.sw[1] >> shift) & 0xf)) : 0;
             }

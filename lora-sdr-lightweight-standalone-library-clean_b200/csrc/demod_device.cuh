@@ -53,6 +53,13 @@ struct DemodArgs {
     float* cfo;
     float* time_offset;
     int32_t* status;
+    int unit_scale;               // prepass: assume no 1/max normalisation is needed (no max-abs scan); the lean pass checks
+    int skip_sync;                // prepass: leave the two sync symbols to a later pass
+    uint8_t* flagged;             // lean pass (demod_lean.cu): packets it hands to the certified kernel
+    const uint8_t* only_flagged;  // certified kernel: skip packets whose byte is 0 (nullptr = every packet); 2 = the lean pass
+                                  // settled every symbol but the packet's max-abs (pmax) exceeds 1: redo the estimator with the
+                                  // true scale, and keep the lean symbols if rate / t_off stay within the certified tolerance
+    float* pmax;                  // lean pass: max-abs of the packets it marks 2
     int force_exact;              // LORA_PHY_CUDA_F_EXACT: the certified kernel replays the exact chain for every window
     unsigned long long* cert_stats;   // [8] windows walked, windows replayed exactly, second estimates, re-walked packets, windows settled by the pruned transform
 };

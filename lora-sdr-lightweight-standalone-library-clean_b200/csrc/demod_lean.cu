@@ -1,0 +1,370 @@
+// demod_lean.cu -- first pass of the three-launch demodulator for SF10-12 (lora_demodulate, LoRaDemod.cpp:50-197):
+// the pruned transform of fft_prune.cuh as a STREAMING kernel, one warp per packet, 4 KB of IQ per step.
+//
+// Why a kernel of its own: in demod_cert.cu a 1024..4096-point window is held by 2..8 warps (16 samples per thread, the
+// layout its full transform needs), so every window costs barriers and only 2-8 windows are in flight per SM; that kernel
+// is latency-bound at ~0.7 of the HBM rate for SF11 / SF12.  The pruned transform does not need the window in registers:
+// with f_c = F_tid G^c ("geometric variant") the class-k0 output of pass 0 is a POLYNOMIAL in the raw samples,
+//     V_t[k0] = F_t * sum_c r_{t + T c} h^c,   h = G W16^k0,  T = N / 16 = 32 R,
+// which a warp can accumulate while the window streams past in R = N / 512 chunks of 512 samples: lane l keeps R complex
+// accumulators (t = l + 32 j), each chunk adds 16 / R terms to each of them (halving levels inside the chunk, one
+// multiply-add with the running power h^(c0) to join).  At the end of the window the lane holds the R inputs of the
+// cross-warp stage of fft_prune.cuh itself: an R-point DFT in registers, the W_T twiddles, R lane transforms, top bin.
+// No shared-memory exchange, no barrier, 2-3 x 4 KB of ring per warp.
+//
+// Division of labour (api.cu):
+//   1. prepass_kernel (demod.cu, unit_scale): the exact two-symbol estimator -> cfo, time_offset, rate, t_off per packet.
+//      It assumes the packet needs no 1/max normalisation (LoRaDemod.cpp:61-78), which only this pass can check.
+//   2. THIS kernel: every window of every "regular" packet (t_off == 0, whole symbols, 16-byte aligned, finite) through
+//      the pruned transform and the tier-1 Parseval test of demod_cert.cu, tracking the max-abs.  The first window that
+//      is refused -- or any irregularity -- FLAGS the packet (1) and abandons it.  A packet settled completely whose
+//      max-abs exceeds 1 is flagged 2: its symbols stand (the decisions are scale-invariant) if the estimator, redone
+//      with the true scale, keeps t_off and moves the rate by no more than the tolerance the proof budgets.
+//   3. demod_cert_kernel over the flagged packets only: flag 1 = the whole packet again (full transform, tier 2, exact
+//      replay, normalisation), every output rewritten; flag 2 = the two exact estimator symbols with the true scale ->
+//      cfo / time_offset, and the rate check (a failed check turns it into flag 1).
+// Symbols, sync word, status, cfo, time_offset are bit-exact either way: accepted windows carry demod_cert.cu's proof
+// (same constants, same budget: DESIGN.md section 5), everything else is the old path.
+#include <atomic>
+#include "stream_common.cuh"
+#include "fft_fast.cuh"
+#include "fft_prune.cuh"
+#include "internal.h"
+
+namespace lk {
+
+#ifndef LEAN_CTA
+#define LEAN_CTA 128
+#endif
+#ifndef LEAN_CTAS_PER_SM
+#define LEAN_CTAS_PER_SM 4
+#endif
+#ifndef LEAN_STAGES
+#define LEAN_STAGES 2
+#endif
+
+constexpr float LEAN_U = 5.9604644775390625e-08f;
+constexpr float LEAN_C0 = 384.0f;                 // CERT_C0 of demod_cert.cu (same budget)
+constexpr int LEAN_CHUNK = 512;                   // samples per step: 4 KB
+
+template <int SF>
+struct LeanCfg {
+    static constexpr int N = 1 << SF, T = N / 16, R = N / LEAN_CHUNK;      // R = T / 32 accumulators per lane
+    static constexpr int CP = 16 / R;                                     // terms per accumulator and chunk
+    static constexpr int LV = CP == 8 ? 3 : CP == 4 ? 2 : 1;              // halving levels inside a chunk
+    static constexpr int WARPS = LEAN_CTA / 32;
+    static constexpr size_t ring_bytes = (size_t)WARPS * LEAN_STAGES * LEAN_CHUNK * sizeof(cf);
+    static constexpr size_t bar_off = ring_bytes;
+    static constexpr size_t tws_off = (bar_off + (size_t)WARPS * LEAN_STAGES * 8 + 15) & ~(size_t)15;   // [4][32] lane-stage factors
+    static constexpr size_t twl_off = tws_off + 4 * 32 * sizeof(cf);                                   // W_N^e, e < 512
+    static constexpr size_t tw32_off = twl_off + 512 * sizeof(cf);                                     // W_N^(32 e), e < 128
+    static constexpr size_t twx_off = tw32_off + 128 * sizeof(cf);                                     // W_T^(l ka), [ka][l]
+    static constexpr size_t w16_off = twx_off + (size_t)R * 32 * sizeof(cf);                           // W16^j
+    static constexpr size_t hp_off = w16_off + 16 * sizeof(cf);                                        // per warp: [k0][4] powers of h
+    static constexpr size_t g32_off = hp_off + (size_t)WARPS * 64 * sizeof(cf);                        // per warp: G32^j, j < 8
+    static constexpr size_t bytes = g32_off + (size_t)WARPS * 8 * sizeof(cf);
+};
+
+__device__ __forceinline__ cf lean_cma(cf acc, cf a, cf w)            // acc + a * w: four fused multiply-adds
+{
+    return fx::mk(ff::fma_(-a.y, w.y, ff::fma_(a.x, w.x, acc.x)), ff::fma_(a.y, w.x, ff::fma_(a.x, w.y, acc.y)));
+}
+
+template <int SF>
+__global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(const DemodArgs a)
+{
+    using C = LeanCfg<SF>;
+    using PR = fp::Prune<SF>;
+    constexpr int N = C::N, T = C::T, R = C::R, CP = C::CP, LV = C::LV, S = LEAN_STAGES;
+    static_assert(R >= 2 && R <= 8, "streaming variant: SF10..SF12");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, l = threadIdx.x & 31;
+    cf* ring = reinterpret_cast<cf*>(smem_raw) + (size_t)warp * S * LEAN_CHUNK;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::bar_off) + warp * S;
+    cf* tws = reinterpret_cast<cf*>(smem_raw + C::tws_off);
+    cf* twl = reinterpret_cast<cf*>(smem_raw + C::twl_off);
+    cf* tw32 = reinterpret_cast<cf*>(smem_raw + C::tw32_off);
+    cf* twx = reinterpret_cast<cf*>(smem_raw + C::twx_off);
+    cf* w16 = reinterpret_cast<cf*>(smem_raw + C::w16_off);
+    cf* hp = reinterpret_cast<cf*>(smem_raw + C::hp_off) + warp * 64;
+    cf* g32 = reinterpret_cast<cf*>(smem_raw + C::g32_off) + warp * 8;
+
+    if (l == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) ptx::mbar_init(&full[s], 1);
+        ptx::fence_mbar_init();
+    }
+    for (int j = threadIdx.x; j < PR::STAGES_TW * 32; j += LEAN_CTA) {
+        double sn, cs;
+        sincospi(-2.0 * (double)PR::stage_exp(j / 32, j % 32) / 32.0, &sn, &cs);
+        tws[j] = fx::mk((float)cs, (float)sn);
+    }
+    for (int j = threadIdx.x; j < 512; j += LEAN_CTA) {
+        double sn, cs;
+        sincospi(-2.0 * (double)j / (double)N, &sn, &cs);
+        twl[j] = fx::mk((float)cs, (float)sn);
+    }
+    for (int j = threadIdx.x; j < 128; j += LEAN_CTA) {
+        double sn, cs;
+        sincospi(-2.0 * (double)((32 * j) & (N - 1)) / (double)N, &sn, &cs);
+        tw32[j] = fx::mk((float)cs, (float)sn);
+    }
+    for (int j = threadIdx.x; j < R * 32; j += LEAN_CTA) {
+        double sn, cs;
+        sincospi(-2.0 * (double)PR::cross_exp(j / 32, j % 32) / (double)T, &sn, &cs);
+        twx[j] = fx::mk((float)cs, (float)sn);
+    }
+    for (int j = threadIdx.x; j < 16; j += LEAN_CTA) {
+        double sn, cs;
+        sincospi(-2.0 * (double)j / 16.0, &sn, &cs);
+        w16[j] = fx::mk((float)cs, (float)sn);
+    }
+    __syncthreads();
+
+    const uint32_t ring0 = ptx::smem_u32(ring), bar0 = ptx::smem_u32(full);
+    int stage = 0;
+    unsigned phase_bits = 0;
+    unsigned st_pruned = 0, st_flagged = 0;
+    const uint32_t n_warps = gridDim.x * C::WARPS;
+
+    for (uint32_t pid = blockIdx.x * C::WARPS + warp; pid < a.n_packets; pid += n_warps) {
+        const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
+        const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
+        const uint32_t total = count / (uint32_t)N;
+        const PacketState st = a.state[pid];
+        // regular packets only; everything else is the third pass's (it repeats the estimator with the right scale)
+        bool ok = st.flags == 0 && st.t_off == 0 && total >= 2 && count == total * (uint32_t)N &&
+                  (reinterpret_cast<uintptr_t>(pkt) & 15) == 0;
+        const float rate = st.rate;
+        const float start_max = fabsf(rate) * ((float)total * (float)N) * 1.01f;
+        const float Kc = LEAN_U * (LEAN_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
+        ok = ok && Kc < 0.0078125f;                            // tier 1 available (demod_cert.cu)
+        if (!ok) {
+            if (l == 0) { a.flagged[pid] = 1; ++st_flagged; }
+            continue;
+        }
+        const float tier1 = 0.75f * (float)N;
+
+        // ---- per packet: F_l = exp(j rate l); G^(1,2,4,8) (G = exp(j rate T)) and G32^j (exp(j rate 32 j)) in double;
+        //      hp[k0][m] = G^(2^m) W16^(k0 2^m) ------------------------------------------------------------------------
+        cf geo_f;
+        {
+            float sn, cs;
+            __sincosf(fx::fmul(rate, (float)l), &sn, &cs);     // |rate l| < 2 pi / 128
+            geo_f = fx::mk(cs, sn);
+            double ds = 0.0, dc = 1.0;
+            if (l < 4) sincos((double)rate * (double)(T << l), &ds, &dc);
+            else if (l < 12) sincos((double)rate * (double)(32 * (l - 4)), &ds, &dc);
+            const float gx = (float)dc, gy = (float)ds;
+            if (l >= 4 && l < 12) g32[l - 4] = fx::mk(gx, gy);
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {
+                const int e = l + 32 * h2, k = e >> 2, mi = e & 3;
+                const cf g = fx::mk(__shfl_sync(0xffffffffu, gx, mi), __shfl_sync(0xffffffffu, gy, mi));
+                hp[e] = ff::fcmul(g, w16[(k << mi) & 15]);
+            }
+            __syncwarp();
+        }
+        const cf geo_g1 = hp[0];
+
+        // ---- the stream: total * R chunks of 4 KB, contiguous ------------------------------------------------------------
+        const uint32_t n_chunks = total * (uint32_t)R;
+        auto issue = [&](uint32_t g, int stg) {                // lane 0
+            ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, LEAN_CHUNK * sizeof(cf));
+            ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_CHUNK * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK,
+                             LEAN_CHUNK * sizeof(cf), bar0 + 8u * (uint32_t)stg);
+        };
+        if (l == 0) {
+            int stg = stage;
+            for (uint32_t g = 0; g < (uint32_t)(S - 1) && g < n_chunks; ++g) { issue(g, stg); stg = stg + 1 == S ? 0 : stg + 1; }
+        }
+        float mmax = 0.0f;
+        int sw0 = 0, sw1 = 0;
+        bool bad = false;
+        uint32_t g = 0;
+#pragma unroll 1
+        for (uint32_t s = 0; s < total && !bad; ++s) {
+            cf acc[R];
+            cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
+            cf hq = fx::mk(1.0f, 0.0f);
+            cf h1 = hq, h2 = hq, h4 = hq, hs = hq;
+            int k0 = 0;
+#pragma unroll
+            for (int q = 0; q < R; ++q, ++g) {
+                __syncwarp();                                  // every lane has finished the slot that is refilled now
+                if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
+                    int stg = stage + (S - 1);
+                    if (stg >= S) stg -= S;
+                    issue(g + (uint32_t)(S - 1), stg);
+                }
+                ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+                const cf* raw = ring + (size_t)stage * LEAN_CHUNK + l;
+                cf v[16];
+                float mw = 0.0f;
+#pragma unroll
+                for (int m = 0; m < 16; ++m) {
+                    const cf r = raw[32 * m];
+                    mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                     // LoRaDemod.cpp:61-68
+                    if (m & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
+                    v[m] = r;
+                }
+                mmax = fmaxf(mmax, mw);
+                if (q == 0) {
+                    // bin class from the phase step between samples T apart (m and m + R), four pairs per lane
+                    cf z = fx::mk(0.0f, 0.0f);
+#pragma unroll
+                    for (int m = 0; m < 4; ++m) {
+                        const cf p1 = v[m + R], p0 = v[m];
+                        z.x = ff::fma_(p1.x, p0.x, z.x); z.x = ff::fma_(p1.y, p0.y, z.x);
+                        z.y = ff::fma_(p1.y, p0.x, z.y); z.y = ff::fma_(-p1.x, p0.y, z.y);
+                    }
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) {
+                        z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
+                        z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
+                    }
+                    z = ff::fcmul(z, geo_g1);
+                    const float ax = fabsf(z.x), ay = fabsf(z.y);
+                    const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
+                    int qq = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
+                    if (ay > ax) qq = 4 - qq;
+                    if (z.x < 0.0f) qq = 8 - qq;
+                    if (z.y < 0.0f) qq = 16 - qq;
+                    k0 = qq & 15;
+                    const float4 hA = *reinterpret_cast<const float4*>(&hp[4 * k0]);
+                    const float4 hB = *reinterpret_cast<const float4*>(&hp[4 * k0 + 2]);
+                    h1 = fx::mk(hA.x, hA.y); h2 = fx::mk(hA.z, hA.w); h4 = fx::mk(hB.x, hB.y);
+                    hs = LV == 3 ? fx::mk(hB.z, hB.w) : (LV == 2 ? h4 : h2);           // h^(16 / R): the chunk's step
+                }
+                // inside the chunk: accumulator j gets sum_{c' < CP} v[j + R c'] h^c' by halving
+                if (LV >= 3) {
+#pragma unroll
+                    for (int i = 0; i < 4 * R; ++i) v[i] = lean_cma(v[i], v[i + 4 * R], h4);
+                }
+                if (LV >= 2) {
+#pragma unroll
+                    for (int i = 0; i < 2 * R; ++i) v[i] = lean_cma(v[i], v[i + 2 * R], h2);
+                }
+#pragma unroll
+                for (int i = 0; i < R; ++i) v[i] = lean_cma(v[i], v[i + R], h1);
+                if (q == 0) {
+#pragma unroll
+                    for (int j = 0; j < R; ++j) acc[j] = v[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < R; ++j) acc[j] = lean_cma(acc[j], v[j], hq);
+                }
+                hq = q == 0 ? hs : ff::fcmul(hq, hs);
+                stage = stage + 1 == S ? 0 : stage + 1;
+            }
+            // ---- end of the window: thread t = l + 32 j holds acc[j]; twiddle exp(j t theta), theta = rate - 2 pi k0 / N ----
+            const cf el = ff::fcmul(geo_f, twl[l * k0]);                               // F_l W_N^(l k0)
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                cf u = ff::fcmul(acc[j], el);
+                if (j > 0) u = ff::fcmul(u, ff::fcmul(g32[j], tw32[j * k0]));          // G32^j W_N^(32 j k0)
+                acc[j] = u;
+            }
+            // R-point DFT across the window's warps-that-were (natural order), cross twiddle, R lane transforms
+            if (R == 2) ff::dft2(acc[0], acc[1]);
+            if (R == 4) ff::dft4(acc[0], acc[1], acc[2], acc[3]);
+            if (R == 8) ff::dft8(acc[0], acc[1], acc[2], acc[3], acc[4], acc[5], acc[6], acc[7]);
+#pragma unroll
+            for (int ka = 1; ka < R; ++ka) acc[ka] = ff::fcmul(acc[ka], twx[ka * 32 + l]);
+#pragma unroll
+            for (int sgi = 0; sgi < 5; ++sgi) {
+                const int h = 16 >> sgi;
+                const bool last = sgi == 4;
+                const cf tw = last ? fx::mk(1.0f, 0.0f) : tws[sgi * 32 + l];
+#pragma unroll
+                for (int ka = 0; ka < R; ++ka) acc[ka] = fp::lane_stage(acc[ka], h, (l & h) != 0, tw, last);
+            }
+            unsigned qb = 0u;
+            int kab = 0;
+#pragma unroll
+            for (int ka = 0; ka < R; ++ka) {
+                const unsigned qv = __float_as_uint(ff::fnorm(acc[ka]));              // >= +0, or NaN (sorts above everything)
+                if (qv > qb) { qb = qv; kab = ka; }
+            }
+            unsigned qmax = qb;
+            float en = ((e0.x + e0.y) + (e1.x + e1.y)) * 1.000002f;
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
+                en += __shfl_xor_sync(0xffffffffu, en, off);
+            }
+            const float q1 = __uint_as_float(qmax);
+            const unsigned ball = __ballot_sync(0xffffffffu, qb == qmax);
+            const int src = __ffs((int)ball) - 1;
+            const int idx = __shfl_sync(0xffffffffu, k0 + 16 * (kab + R * (int)(__brev((unsigned)l) >> 27)), src);
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, off));
+            // accepted iff the top bin holds 3/4 of N E (tier 1 of demod_cert.cu).  The decision does not depend on the 1/max
+            // normalisation the estimator pass assumed away (positive scale; the rate it changes is checked by the third
+            // pass); NaN samples are invisible to fmaxf but poison E, an infinite max wipes the packet in the reference
+            const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f) && (mmax < 3.0e38f);
+            if (!cert) { bad = true; break; }
+            if (s == 0) sw0 = idx;
+            else if (s == 1) sw1 = idx;
+            else if (l == 0) a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
+        }
+        if (bad) {
+            // abandon the packet: consume the copies still in flight so that the ring's phases stay consistent
+            const uint32_t end = min(n_chunks, g + (uint32_t)(S - 1));
+            for (; g < end; ++g) {
+                ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                phase_bits ^= 1u << stage;
+                stage = stage + 1 == S ? 0 : stage + 1;
+            }
+            __syncwarp();
+        }
+        if (bad) {
+            if (l == 0) { a.flagged[pid] = 1; ++st_flagged; }
+        } else if (l == 0) {
+            st_pruned += total;
+            if (mmax > 1.0f) { a.pmax[pid] = mmax; a.flagged[pid] = 2; }       // LoRaDemod.cpp:69-78: the estimator needs the scale
+            if (a.sync) a.sync[pid] = (uint8_t)((((sw0 >> (SF - 4)) & 0xf) << 4) | ((sw1 >> (SF - 4)) & 0xf));
+            if (a.status) a.status[pid] = (int)(total - 2);
+        }
+    }
+    if (a.cert_stats && l == 0) {
+        if (st_pruned) { atomicAdd(a.cert_stats + 0, (unsigned long long)st_pruned); atomicAdd(a.cert_stats + 4, (unsigned long long)st_pruned); }
+        if (st_flagged) atomicAdd(a.cert_stats + 5, (unsigned long long)st_flagged);
+    }
+}
+
+template <int SF>
+static cudaError_t launch_lean_sf(const DemodArgs& a, int sm_count, cudaStream_t stream)
+{
+    using C = LeanCfg<SF>;
+    static std::atomic<bool> attr_done[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
+        cudaFuncSetAttribute(demod_lean_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        attr_done[dev & 63].store(true, std::memory_order_release);
+    }
+    const unsigned max_ctas = (unsigned)sm_count * LEAN_CTAS_PER_SM;      // persistent grid
+    const unsigned need = (a.n_packets + C::WARPS - 1) / C::WARPS;
+    demod_lean_kernel<SF><<<need < max_ctas ? need : max_ctas, LEAN_CTA, C::bytes, stream>>>(a);
+    return cudaGetLastError();
+}
+
+bool lean_supported(int sf, const DemodArgs& a)
+{
+    return sf >= 10 && sf <= 12 && a.osr == 1 && a.mode == MODE_LEGACY && !a.window && !a.down && !a.no_scratch &&
+           !a.force_exact && (unsigned long long)a.samples_per_packet < 0xf0000000ull;
+}
+
+cudaError_t launch_demod_lean(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream)
+{
+    switch (sf) {
+    case 10: return launch_lean_sf<10>(a, sm_count, stream);
+    case 11: return launch_lean_sf<11>(a, sm_count, stream);
+    case 12: return launch_lean_sf<12>(a, sm_count, stream);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+} // namespace lk

@@ -47,6 +47,10 @@ cudaError_t launch_build_tables(int sf, cf* tw, cf* ct, int ct_size, float* hann
 cudaError_t launch_build_chirp(int sf, int osr, float bw_scale, cf* out /* N*osr */, cudaStream_t stream);
 int compact_size_of(int sf);
 
+// demod_lean.cu: streaming pruned first pass (SF10-12); see api.cu for the three-launch route
+bool lean_supported(int sf, const DemodArgs& a);
+cudaError_t launch_demod_lean(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
+
 // modcodes.cu
 struct ModArgs {
     const uint16_t* symbols; size_t symbol_stride; uint32_t symbols_per_packet; uint32_t n_packets;

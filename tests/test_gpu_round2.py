@@ -11,6 +11,7 @@
 * the round-1 advisor cases: a per-packet count above samples_per_packet, a batch that starts 8 bytes into an
   allocation.
 """
+import ctypes
 import errno
 import os
 
@@ -403,6 +404,59 @@ def test_pruned_transform_policy_over_snr_and_sync_words(phy, lp, oracle, sf):
     # single-warp windows hand a refused window to the full transform in the same step; multi-warp windows replay it
     # exactly and back off (a bounded number of retries)
     assert c1[1] == c0[1] if sf <= 9 else c1[1] - c0[1] <= (c1[0] - c0[0]) // 4
+
+
+@pytest.mark.parametrize("sf", [10, 11, 12])
+def test_lean_route_hands_over_what_it_cannot_settle(phy, lp, oracle, sf):
+    """SF10-12, pre-dechirped IQ: estimator pass, streaming pruned pass, certified pass over the flagged packets.  Quiet and
+    loud clean packets (max-abs above 1: the estimator is redone with the true scale, the symbols stand), noisy ones
+    (handed over whole), NaN / Inf samples, a packet that ends in a partial symbol, one that starts 8 bytes into a
+    16-byte unit: every output equals the oracle, and the counters show all three outcomes."""
+    rng = np.random.default_rng(1200 + sf)
+    N = 1 << sf
+    S = 5
+    down = oracle.gen_chirp(N, 1, N, 0.0, True, 1.0, 0.0, 1.0)[0]
+
+    def pkt(amp, noise=0.0, sync=0x12):
+        syms = rng.integers(0, N, S - 2).astype(np.uint16)
+        d = (oracle.lora_modulate(syms, sf, 1, 125000, amp, sync).reshape(-1, N) * down[None, :]).astype(np.complex64).ravel()
+        if noise:
+            d = (d + np.float32(noise) * (rng.standard_normal(d.size) + 1j * rng.standard_normal(d.size))).astype(np.complex64)
+        return d
+
+    rows = [pkt(0.5), pkt(1.0), pkt(1.7), pkt(33.0), pkt(0.9, 0.02), pkt(1.0, 0.9), pkt(0.7, 2.0), pkt(0.25, sync=0x88),
+            pkt(1.3), pkt(0.8)]
+    rows[8][2 * N + 17] = np.complex64(complex(np.nan, 0.0))
+    rows[9][3 * N + 5] = np.complex64(complex(np.inf, 1.0))
+    iq = np.stack(rows)
+    counts = np.full(len(rows), S * N, np.uint32)
+    counts[0] = S * N - 3                                          # partial last symbol: not a regular packet
+    c0 = phy.cert_stats()
+    with np.errstate(all="ignore"):
+        check_legacy(phy, lp, oracle, iq, sf, 1, 0, counts=counts)
+    c1 = phy.cert_stats()
+    assert c1[4] - c0[4] >= 3 * S and c1[5] - c0[5] >= 4, (c0, c1)
+    # the same rows one sample (8 bytes) into the allocation: no 16-byte alignment, the certified kernel takes them all
+    big = np.zeros((len(rows), S * N + 2), np.complex64)
+    flat = big.ravel()
+    dev = to_dev(phy, flat)
+    view = dev[1:1 + len(rows) * (S * N + 2) - 1]
+    host = np.zeros(len(rows) * (S * N + 2) - 1, np.complex64)
+    for p, r in enumerate(rows):
+        host[p * (S * N + 2):p * (S * N + 2) + S * N] = r
+    view.copy_(to_dev(phy, host))
+    cfg = lp.make_cfg(sf)
+    out = phy.alloc_demod_outputs(len(rows), S - 2)
+    rc = phy.lib.lora_phy_cuda_demodulate_batch(phy.h, ctypes.byref(cfg), view.data_ptr(), S * N + 2, None, S * N, len(rows),
+                                                out["symbols"].data_ptr(), out["symbols"].stride(0), out["sync"].data_ptr(),
+                                                out["cfo"].data_ptr(), out["time_offset"].data_ptr(), out["status"].data_ptr())
+    assert rc == 0
+    phy.synchronize()
+    with np.errstate(all="ignore"):
+        for p, r in enumerate(rows):
+            n, s_ref, sync, cfo, to = oracle.lora_demodulate(r, sf, 1, 0, 1)
+            assert int(out["status"][p]) == n
+            assert np.array_equal(out["symbols"][p, :n].cpu().numpy(), s_ref) and int(out["sync"][p]) == sync
 
 
 def test_every_kernel_family_small_cases():
