@@ -330,9 +330,9 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.unit_scale = 0; a.skip_sync = 0; a.flagged = nullptr; a.only_flagged = nullptr; a.pmax = nullptr;
     a.cert_stats = ctx->cert_stats;
     unsigned launches = 0;
-    // SF10-12, pre-dechirped IQ (the cfg-3 shape): three launches.  (1) the exact two-symbol estimator alone, assuming the
-    // packet needs no 1/max normalisation; (2) the streaming pruned transform, one warp per packet (demod_lean.cu), which
-    // checks that assumption and flags every packet it cannot settle; (3) the certified kernel over the flagged packets.
+    // SF10-12, pre-dechirped IQ (the cfg-3 shape): two launches.  (1) demod_lean.cu: the exact two-symbol estimator by
+    // teams of warps, then the streaming pruned transform with one warp per packet; it flags every packet it cannot
+    // settle; (2) the certified kernel over the flagged packets.
     static const bool lean_off = getenv("LORA_PHY_NO_LEAN") != nullptr;
     if (!lean_off && !(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&
         lk::lean_supported((int)cfg->sf, a) && lk::cert_supported((int)cfg->sf, a)) {
@@ -340,9 +340,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
         CK(ctx->pmax.reserve(n_packets * sizeof(float)));
         CK(cudaMemsetAsync(ctx->flag.p, 0, n_packets, ctx->stream));
         lk::DemodArgs p = a;
-        p.unit_scale = 1; p.skip_sync = 1; p.est_uniform = 2;
-        cudaError_t e = lk::launch_demod((int)cfg->sf, p, ctx->sm_count, ctx->stream, true, false, &launches);
-        if (e != cudaSuccess) return fail(ctx, -EIO, "estimator launch", e);
+        cudaError_t e;
         p = a;
         p.flagged = static_cast<uint8_t*>(ctx->flag.p);
         p.pmax = static_cast<float*>(ctx->pmax.p);

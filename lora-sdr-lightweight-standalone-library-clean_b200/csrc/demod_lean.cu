@@ -34,10 +34,10 @@
 namespace lk {
 
 #ifndef LEAN_CTA
-#define LEAN_CTA 128
+#define LEAN_CTA 256
 #endif
 #ifndef LEAN_CTAS_PER_SM
-#define LEAN_CTAS_PER_SM 4
+#define LEAN_CTAS_PER_SM 2
 #endif
 #ifndef LEAN_STAGES
 #define LEAN_STAGES 2
@@ -62,7 +62,10 @@ struct LeanCfg {
     static constexpr size_t w16_off = twx_off + (size_t)R * 32 * sizeof(cf);                           // W16^j
     static constexpr size_t hp_off = w16_off + 16 * sizeof(cf);                                        // per warp: [k0][4] powers of h
     static constexpr size_t g32_off = hp_off + (size_t)WARPS * 64 * sizeof(cf);                        // per warp: G32^j, j < 8
-    static constexpr size_t bytes = g32_off + (size_t)WARPS * 8 * sizeof(cf);
+    static constexpr size_t cell_off = g32_off + (size_t)WARPS * 8 * sizeof(cf);                       // per warp: LeanTeamCell (48 B)
+    static constexpr size_t est_off = cell_off + (size_t)WARPS * 48;                                   // per team: two LeanEst (16 B slots)
+    static constexpr size_t red_off = est_off + (size_t)WARPS * 2 * 16;                                // Peak[8] of the exact estimator
+    static constexpr size_t bytes = red_off + 8 * 8;
 };
 
 __device__ __forceinline__ cf lean_cma(cf acc, cf a, cf w)            // acc + a * w: four fused multiply-adds
@@ -70,16 +73,29 @@ __device__ __forceinline__ cf lean_cma(cf acc, cf a, cf w)            // acc + a
     return fx::mk(ff::fma_(-a.y, w.y, ff::fma_(a.x, w.x, acc.x)), ff::fma_(a.y, w.x, ff::fma_(a.x, w.y, acc.y)));
 }
 
+struct LeanTeamCell {       // one per warp: what the team's estimator phase hands to / takes from the warp's stream
+    float rate; int t_off; int ok; float used_max;          // estimate for the packet about to be streamed
+    int vpid; float vmax; float vrate; int vtoff;           // request: redo packet vpid's estimate with max-abs vmax
+    float pred;                                             // max-abs the next estimate should assume (the warp's last packet's)
+    int pad[3];
+};
+struct LeanEst { int idx; float fi; float phase; };
+
 template <int SF>
 __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(const DemodArgs a)
 {
     using C = LeanCfg<SF>;
     using PR = fp::Prune<SF>;
-    constexpr int N = C::N, T = C::T, R = C::R, CP = C::CP, LV = C::LV, S = LEAN_STAGES;
+    using P = fx::Plan<SF>;
+    constexpr int N = C::N, T = C::T, R = C::R, LV = C::LV, S = LEAN_STAGES, TW = T / 32;
     static_assert(R >= 2 && R <= 8, "streaming variant: SF10..SF12");
+    static_assert(LEAN_CTA == CTA_THREADS, "the exact estimator's group helpers assume CTA_THREADS");
+    static_assert((size_t)TW * S * LEAN_CHUNK >= (size_t)N, "the team's ring doubles as the exact transform's exchange buffer");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, l = threadIdx.x & 31;
+    const int team = threadIdx.x / T, tid = threadIdx.x % T, wt = warp % TW;       // team, thread in team, warp in team
     cf* ring = reinterpret_cast<cf*>(smem_raw) + (size_t)warp * S * LEAN_CHUNK;
+    cf* ex = reinterpret_cast<cf*>(smem_raw) + (size_t)(team * TW) * S * LEAN_CHUNK;   // N entries: exchange, then spectrum
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::bar_off) + warp * S;
     cf* tws = reinterpret_cast<cf*>(smem_raw + C::tws_off);
     cf* twl = reinterpret_cast<cf*>(smem_raw + C::twl_off);
@@ -88,6 +104,9 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
     cf* w16 = reinterpret_cast<cf*>(smem_raw + C::w16_off);
     cf* hp = reinterpret_cast<cf*>(smem_raw + C::hp_off) + warp * 64;
     cf* g32 = reinterpret_cast<cf*>(smem_raw + C::g32_off) + warp * 8;
+    LeanTeamCell* cells = reinterpret_cast<LeanTeamCell*>(smem_raw + C::cell_off) + team * TW;
+    LeanEst* est = reinterpret_cast<LeanEst*>(smem_raw + C::est_off) + team * 2;
+    Peak* red = reinterpret_cast<Peak*>(smem_raw + C::red_off);
 
     if (l == 0) {
 #pragma unroll
@@ -124,214 +143,341 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
     const uint32_t ring0 = ptx::smem_u32(ring), bar0 = ptx::smem_u32(full);
     int stage = 0;
     unsigned phase_bits = 0;
-    unsigned st_pruned = 0, st_flagged = 0;
+    unsigned st_pruned = 0, st_flagged = 0, st_est2 = 0;
     const uint32_t n_warps = gridDim.x * C::WARPS;
+    const uint32_t gw0 = blockIdx.x * C::WARPS + (uint32_t)(team * TW);            // the team's first warp, grid-wide
+    float pred_max = 0.0f;                                     // max-abs of this warp's previous packet
+    int vpid = -1; float vmax = 0.0f, vrate = 0.0f; int vtoff = 0;                 // this warp's pending re-estimate
 
-    for (uint32_t pid = blockIdx.x * C::WARPS + warp; pid < a.n_packets; pid += n_warps) {
+    // The exact two-symbol estimator of packet `pid` with the samples scaled by 1/use_max when use_max > 1
+    // (LoRaDemod.cpp:61-139), by the whole team; thread 0 of the team gets cfo / time_offset / rate / t_off.
+    auto estimate = [&](uint32_t pid, float use_max, float& cfo, float& toff, float& rate, int& t_off) {
         const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
-        const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
-        const uint32_t total = count / (uint32_t)N;
-        const PacketState st = a.state[pid];
-        // regular packets only; everything else is the third pass's (it repeats the estimator with the right scale)
-        bool ok = st.flags == 0 && st.t_off == 0 && total >= 2 && count == total * (uint32_t)N &&
-                  (reinterpret_cast<uintptr_t>(pkt) & 15) == 0;
-        const float rate = st.rate;
-        const float start_max = fabsf(rate) * ((float)total * (float)N) * 1.01f;
-        const float Kc = LEAN_U * (LEAN_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
-        ok = ok && Kc < 0.0078125f;                            // tier 1 available (demod_cert.cu)
-        if (!ok) {
-            if (l == 0) { a.flagged[pid] = 1; ++st_flagged; }
-            continue;
-        }
-        const float tier1 = 0.75f * (float)N;
-
-        // ---- per packet: F_l = exp(j rate l); G^(1,2,4,8) (G = exp(j rate T)) and G32^j (exp(j rate 32 j)) in double;
-        //      hp[k0][m] = G^(2^m) W16^(k0 2^m) ------------------------------------------------------------------------
-        cf geo_f;
-        {
-            float sn, cs;
-            __sincosf(fx::fmul(rate, (float)l), &sn, &cs);     // |rate l| < 2 pi / 128
-            geo_f = fx::mk(cs, sn);
-            double ds = 0.0, dc = 1.0;
-            if (l < 4) sincos((double)rate * (double)(T << l), &ds, &dc);
-            else if (l < 12) sincos((double)rate * (double)(32 * (l - 4)), &ds, &dc);
-            const float gx = (float)dc, gy = (float)ds;
-            if (l >= 4 && l < 12) g32[l - 4] = fx::mk(gx, gy);
-#pragma unroll
-            for (int h2 = 0; h2 < 2; ++h2) {
-                const int e = l + 32 * h2, k = e >> 2, mi = e & 3;
-                const cf g = fx::mk(__shfl_sync(0xffffffffu, gx, mi), __shfl_sync(0xffffffffu, gy, mi));
-                hp[e] = ff::fcmul(g, w16[(k << mi) & 15]);
-            }
-            __syncwarp();
-        }
-        const cf geo_g1 = hp[0];
-
-        // ---- the stream: total * R chunks of 4 KB, contiguous ------------------------------------------------------------
-        const uint32_t n_chunks = total * (uint32_t)R;
-        auto issue = [&](uint32_t g, int stg) {                // lane 0
-            ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, LEAN_CHUNK * sizeof(cf));
-            ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_CHUNK * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK,
-                             LEAN_CHUNK * sizeof(cf), bar0 + 8u * (uint32_t)stg);
-        };
-        if (l == 0) {
-            int stg = stage;
-            for (uint32_t g = 0; g < (uint32_t)(S - 1) && g < n_chunks; ++g) { issue(g, stg); stg = stg + 1 == S ? 0 : stg + 1; }
-        }
-        float mmax = 0.0f;
-        int sw0 = 0, sw1 = 0;
-        bool bad = false;
-        uint32_t g = 0;
+        const bool norm = use_max > 1.0f;
+        const float scale = norm ? __fdiv_rn(1.0f, use_max) : 1.0f;
 #pragma unroll 1
-        for (uint32_t s = 0; s < total && !bad; ++s) {
-            cf acc[R];
-            cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
-            cf hq = fx::mk(1.0f, 0.0f);
-            cf h1 = hq, h2 = hq, h4 = hq, hs = hq;
-            int k0 = 0;
+        for (int s = 0; s < 2; ++s) {
+            cf v[P::R];
 #pragma unroll
-            for (int q = 0; q < R; ++q, ++g) {
-                __syncwarp();                                  // every lane has finished the slot that is refilled now
-                if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
-                    int stg = stage + (S - 1);
-                    if (stg >= S) stg -= S;
-                    issue(g + (uint32_t)(S - 1), stg);
+            for (int c = 0; c < P::R; ++c) {
+                cf x = ldg_cf(pkt + (size_t)s * N + tid + T * c);
+                if (norm) x = fx::cscale(x, scale);                                    // LoRaDemod.cpp:75-77
+                v[c] = x;
+            }
+            fft_inplace<SF, true>(v, tid, a.tw, a.ct, ex);
+            const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+            group_sync<T>();                                   // last exchange fully read: the buffer becomes the spectrum
+#pragma unroll
+            for (int r = 0; r < P::R; ++r) ex[P::bin_of_reg(tid, r)] = v[r];
+            group_sync<T>();
+            if (tid == 0) {
+                LeanEst e; e.idx = 0; e.fi = 0.0f; e.phase = 0.0f;
+                cf best_bin = fx::mk(0.0f, 0.0f);
+                if (pk.val > 0.0f) {                           // candidate kept iff its power beats -1e30 dB: max > 0
+                    const float fundamental = __fsqrt_rn(pk.val);
+                    const cf lft = ex[pk.idx > 0 ? pk.idx - 1 : N - 1];
+                    const cf rgt = ex[pk.idx < N - 1 ? pk.idx + 1 : 0];
+                    const float left = gm::hypotf_g(lft.x, lft.y), right = gm::hypotf_g(rgt.x, rgt.y);
+                    const double demon = (2.0 * (double)fundamental) - (double)right - (double)left;
+                    e.fi = (demon == 0.0) ? 0.0f : (float)(0.5 * (double)fx::fsub(right, left) / demon);
+                    e.idx = pk.idx;
+                    best_bin = ex[pk.idx];
                 }
-                ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
-                phase_bits ^= 1u << stage;
-                const cf* raw = ring + (size_t)stage * LEAN_CHUNK + l;
-                cf v[16];
-                float mw = 0.0f;
-#pragma unroll
-                for (int m = 0; m < 16; ++m) {
-                    const cf r = raw[32 * m];
-                    mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                     // LoRaDemod.cpp:61-68
-                    if (m & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
-                    v[m] = r;
-                }
-                mmax = fmaxf(mmax, mw);
-                if (q == 0) {
-                    // bin class from the phase step between samples T apart (m and m + R), four pairs per lane
-                    cf z = fx::mk(0.0f, 0.0f);
-#pragma unroll
-                    for (int m = 0; m < 4; ++m) {
-                        const cf p1 = v[m + R], p0 = v[m];
-                        z.x = ff::fma_(p1.x, p0.x, z.x); z.x = ff::fma_(p1.y, p0.y, z.x);
-                        z.y = ff::fma_(p1.y, p0.x, z.y); z.y = ff::fma_(-p1.x, p0.y, z.y);
+                e.phase = gm::atan2f_g(best_bin.y, best_bin.x);
+                est[s] = e;
+            }
+            group_sync<T>();
+        }
+        if (tid == 0) {                                        // LoRaDemod.cpp:126-139
+            const float PI_F = 3.14159265358979323846f;
+            const LeanEst e0 = est[0], e1 = est[1];
+            float sum_index = fx::fadd(0.0f, fx::fadd((float)e0.idx, e0.fi));
+            sum_index = fx::fadd(sum_index, fx::fadd((float)e1.idx, e1.fi));
+            float dd = fx::fsub(e1.phase, e0.phase);
+            while (dd > PI_F) dd = fx::fsub(dd, 2.0f * PI_F);
+            while (dd < -PI_F) dd = fx::fadd(dd, 2.0f * PI_F);
+            const float phase_diff = fx::fadd(0.0f, dd);
+            const float avg_index = __fdiv_rn(sum_index, 2.0f);
+            const float cfo_coarse = __fdiv_rn(avg_index, (float)N);
+            const float cfo_fine = __fdiv_rn(__fdiv_rn(phase_diff, 1.0f), fx::fmul(2.0f * PI_F, (float)N));
+            cfo = fx::fadd(cfo_coarse, cfo_fine);
+            const float frac = fx::fsub(avg_index, floorf(fx::fadd(avg_index, 0.5f)));
+            const float avg_t = __fdiv_rn(0.0f, 2.0f);
+            toff = fx::fsub(avg_t, fx::fmul(frac, (float)N));
+            t_off = (int)roundf(toff);
+            rate = __fdiv_rn(fx::fmul(-2.0f * PI_F, cfo), (float)N);
+        }
+    };
+
+#pragma unroll 1
+    for (uint32_t round = 0;; ++round) {
+        // ---- estimator phase (the team's ring is idle): pending re-estimates, then the packets about to be streamed ------
+        if (l == 0) {
+            LeanTeamCell& c = cells[wt];
+            c.vpid = vpid; c.vmax = vmax; c.vrate = vrate; c.vtoff = vtoff; c.pred = pred_max;
+        }
+        group_sync<T>();
+        bool any = false;
+#pragma unroll 1
+        for (int m = 0; m < TW; ++m) {
+            const int vp = cells[m].vpid;
+            if (vp >= 0) {
+                any = true;
+                float cfo = 0.0f, toff = 0.0f, rate = 0.0f; int t_off = 0;
+                estimate((uint32_t)vp, cells[m].vmax, cfo, toff, rate, t_off);
+                if (tid == 0) {
+                    // the streamed symbols stand iff the window bases and (within the certified tolerance) the rate do
+                    const bool same = t_off == cells[m].vtoff && fabsf(fx::fsub(rate, cells[m].vrate)) * (float)N <= 64.0f * LEAN_U;
+                    if (same) {
+                        if (a.cfo) a.cfo[vp] = cfo;
+                        if (a.time_offset) a.time_offset[vp] = toff;
+                    } else {
+                        a.flagged[vp] = 1; ++st_flagged;
                     }
+                    ++st_est2;
+                }
+            }
+            const unsigned long long pm = (unsigned long long)gw0 + (unsigned)m + (unsigned long long)round * n_warps;
+            int ok = 0;
+            if (pm < a.n_packets) {
+                any = true;
+                const uint32_t pid = (uint32_t)pm;
+                const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
+                const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
+                const uint32_t total = count / (uint32_t)N;
+                // regular packets only; everything else is the certified kernel's
+                const bool shape = total >= 2 && count == total * (uint32_t)N && (reinterpret_cast<uintptr_t>(pkt) & 15) == 0 &&
+                                   cells[m].pred < 3.0e38f;
+                if (shape) {
+                    float cfo = 0.0f, toff = 0.0f, rate = 0.0f; int t_off = 0;
+                    estimate(pid, cells[m].pred, cfo, toff, rate, t_off);
+                    if (tid == 0) {
+                        if (a.cfo) a.cfo[pid] = cfo;
+                        if (a.time_offset) a.time_offset[pid] = toff;
+                        cells[m].rate = rate; cells[m].t_off = t_off; cells[m].used_max = cells[m].pred;
+                    }
+                    ok = 1;
+                }
+                if (tid == 0) cells[m].ok = ok;
+            } else if (tid == 0) {
+                cells[m].ok = -1;                              // no packet this round
+            }
+        }
+        ptx::fence_proxy_async();                              // exchange-buffer stores precede the bulk copies into the ring
+        group_sync<T>();
+        if (!any) break;
+        vpid = -1;
+
+        // ---- stream phase: every warp its own packet -----------------------------------------------------------------------
+        const unsigned long long pme = (unsigned long long)blockIdx.x * C::WARPS + (unsigned)warp + (unsigned long long)round * n_warps;
+        const LeanTeamCell mine = cells[wt];
+        if (mine.ok >= 0 && pme < a.n_packets) {
+            const uint32_t pid = (uint32_t)pme;
+            const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
+            const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
+            const uint32_t total = count / (uint32_t)N;
+            const float rate = mine.rate;
+            const float start_max = fabsf(rate) * ((float)total * (float)N) * 1.01f;
+            const float Kc = LEAN_U * (LEAN_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
+            bool bad = !(mine.ok == 1 && mine.t_off == 0 && Kc < 0.0078125f);         // tier 1 available (demod_cert.cu)
+            const float tier1 = 0.75f * (float)N;
+            float mmax = 0.0f;
+            int sw0 = 0, sw1 = 0;
+            if (!bad) {
+                // per packet: F_l = exp(j rate l); G^(1,2,4,8) (G = exp(j rate T)) and G32^j (exp(j rate 32 j)) in double;
+                // hp[k0][m] = G^(2^m) W16^(k0 2^m)
+                cf geo_f;
+                {
+                    float sn, cs;
+                    __sincosf(fx::fmul(rate, (float)l), &sn, &cs);     // |rate l| < 2 pi / 128
+                    geo_f = fx::mk(cs, sn);
+                    double ds = 0.0, dc = 1.0;
+                    if (l < 4) sincos((double)rate * (double)(T << l), &ds, &dc);
+                    else if (l < 12) sincos((double)rate * (double)(32 * (l - 4)), &ds, &dc);
+                    const float gx = (float)dc, gy = (float)ds;
+                    if (l >= 4 && l < 12) g32[l - 4] = fx::mk(gx, gy);
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const int e = l + 32 * h2, k = e >> 2, mi = e & 3;
+                        const cf g = fx::mk(__shfl_sync(0xffffffffu, gx, mi), __shfl_sync(0xffffffffu, gy, mi));
+                        hp[e] = ff::fcmul(g, w16[(k << mi) & 15]);
+                    }
+                    __syncwarp();
+                }
+                const cf geo_g1 = hp[0];
+
+                // the stream: total * R chunks of 4 KB, contiguous
+                const uint32_t n_chunks = total * (uint32_t)R;
+                auto issue = [&](uint32_t g, int stg) {                // lane 0
+                    ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, LEAN_CHUNK * sizeof(cf));
+                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_CHUNK * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK,
+                                     LEAN_CHUNK * sizeof(cf), bar0 + 8u * (uint32_t)stg);
+                };
+                if (l == 0) {
+                    int stg = stage;
+                    for (uint32_t g = 0; g < (uint32_t)(S - 1) && g < n_chunks; ++g) { issue(g, stg); stg = stg + 1 == S ? 0 : stg + 1; }
+                }
+                uint32_t g = 0;
+#pragma unroll 1
+                for (uint32_t s = 0; s < total; ++s) {
+                    cf acc[R];
+                    cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
+                    cf hq = fx::mk(1.0f, 0.0f);
+                    cf h1 = hq, h2 = hq, h4 = hq, hs = hq;
+                    int k0 = 0;
+#pragma unroll
+                    for (int q = 0; q < R; ++q, ++g) {
+                        __syncwarp();                                  // every lane has finished the slot that is refilled now
+                        if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
+                            int stg = stage + (S - 1);
+                            if (stg >= S) stg -= S;
+                            issue(g + (uint32_t)(S - 1), stg);
+                        }
+                        ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                        phase_bits ^= 1u << stage;
+                        const cf* raw = ring + (size_t)stage * LEAN_CHUNK + l;
+                        cf v[16];
+                        float mw = 0.0f;
+#pragma unroll
+                        for (int m = 0; m < 16; ++m) {
+                            const cf r = raw[32 * m];
+                            mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                     // LoRaDemod.cpp:61-68
+                            if (m & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
+                            v[m] = r;
+                        }
+                        mmax = fmaxf(mmax, mw);
+                        if (q == 0) {
+                            // bin class from the phase step between samples T apart (m and m + R), four pairs per lane
+                            cf z = fx::mk(0.0f, 0.0f);
+#pragma unroll
+                            for (int m = 0; m < 4; ++m) {
+                                const cf p1 = v[m + R], p0 = v[m];
+                                z.x = ff::fma_(p1.x, p0.x, z.x); z.x = ff::fma_(p1.y, p0.y, z.x);
+                                z.y = ff::fma_(p1.y, p0.x, z.y); z.y = ff::fma_(-p1.x, p0.y, z.y);
+                            }
+#pragma unroll
+                            for (int off = 16; off > 0; off >>= 1) {
+                                z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
+                                z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
+                            }
+                            z = ff::fcmul(z, geo_g1);
+                            const float ax = fabsf(z.x), ay = fabsf(z.y);
+                            const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
+                            int qq = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
+                            if (ay > ax) qq = 4 - qq;
+                            if (z.x < 0.0f) qq = 8 - qq;
+                            if (z.y < 0.0f) qq = 16 - qq;
+                            k0 = qq & 15;
+                            const float4 hA = *reinterpret_cast<const float4*>(&hp[4 * k0]);
+                            const float4 hB = *reinterpret_cast<const float4*>(&hp[4 * k0 + 2]);
+                            h1 = fx::mk(hA.x, hA.y); h2 = fx::mk(hA.z, hA.w); h4 = fx::mk(hB.x, hB.y);
+                            hs = LV == 3 ? fx::mk(hB.z, hB.w) : (LV == 2 ? h4 : h2);           // h^(16 / R): the chunk's step
+                        }
+                        // inside the chunk: accumulator j gets sum_{c' < CP} v[j + R c'] h^c' by halving
+                        if (LV >= 3) {
+#pragma unroll
+                            for (int i = 0; i < 4 * R; ++i) v[i] = lean_cma(v[i], v[i + 4 * R], h4);
+                        }
+                        if (LV >= 2) {
+#pragma unroll
+                            for (int i = 0; i < 2 * R; ++i) v[i] = lean_cma(v[i], v[i + 2 * R], h2);
+                        }
+#pragma unroll
+                        for (int i = 0; i < R; ++i) v[i] = lean_cma(v[i], v[i + R], h1);
+                        if (q == 0) {
+#pragma unroll
+                            for (int j = 0; j < R; ++j) acc[j] = v[j];
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < R; ++j) acc[j] = lean_cma(acc[j], v[j], hq);
+                        }
+                        hq = q == 0 ? hs : ff::fcmul(hq, hs);
+                        stage = stage + 1 == S ? 0 : stage + 1;
+                    }
+                    // end of the window: thread t = l + 32 j holds acc[j]; twiddle exp(j t theta), theta = rate - 2 pi k0 / N
+                    const cf el = ff::fcmul(geo_f, twl[l * k0]);                               // F_l W_N^(l k0)
+#pragma unroll
+                    for (int j = 0; j < R; ++j) {
+                        cf u = ff::fcmul(acc[j], el);
+                        if (j > 0) u = ff::fcmul(u, ff::fcmul(g32[j], tw32[j * k0]));          // G32^j W_N^(32 j k0)
+                        acc[j] = u;
+                    }
+                    // R-point DFT across the window's warps-that-were (natural order), cross twiddle, R lane transforms
+                    if (R == 2) ff::dft2(acc[0], acc[1]);
+                    if (R == 4) ff::dft4(acc[0], acc[1], acc[2], acc[3]);
+                    if (R == 8) ff::dft8(acc[0], acc[1], acc[2], acc[3], acc[4], acc[5], acc[6], acc[7]);
+#pragma unroll
+                    for (int ka = 1; ka < R; ++ka) acc[ka] = ff::fcmul(acc[ka], twx[ka * 32 + l]);
+#pragma unroll
+                    for (int sgi = 0; sgi < 5; ++sgi) {
+                        const int h = 16 >> sgi;
+                        const bool last = sgi == 4;
+                        const cf tw = last ? fx::mk(1.0f, 0.0f) : tws[sgi * 32 + l];
+#pragma unroll
+                        for (int ka = 0; ka < R; ++ka) acc[ka] = fp::lane_stage(acc[ka], h, (l & h) != 0, tw, last);
+                    }
+                    unsigned qb = 0u;
+                    int kab = 0;
+#pragma unroll
+                    for (int ka = 0; ka < R; ++ka) {
+                        const unsigned qv = __float_as_uint(ff::fnorm(acc[ka]));              // >= +0, or NaN (sorts above everything)
+                        if (qv > qb) { qb = qv; kab = ka; }
+                    }
+                    unsigned qmax = qb;
+                    float en = ((e0.x + e0.y) + (e1.x + e1.y)) * 1.000002f;
 #pragma unroll
                     for (int off = 16; off > 0; off >>= 1) {
-                        z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
-                        z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
+                        qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
+                        en += __shfl_xor_sync(0xffffffffu, en, off);
                     }
-                    z = ff::fcmul(z, geo_g1);
-                    const float ax = fabsf(z.x), ay = fabsf(z.y);
-                    const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
-                    int qq = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
-                    if (ay > ax) qq = 4 - qq;
-                    if (z.x < 0.0f) qq = 8 - qq;
-                    if (z.y < 0.0f) qq = 16 - qq;
-                    k0 = qq & 15;
-                    const float4 hA = *reinterpret_cast<const float4*>(&hp[4 * k0]);
-                    const float4 hB = *reinterpret_cast<const float4*>(&hp[4 * k0 + 2]);
-                    h1 = fx::mk(hA.x, hA.y); h2 = fx::mk(hA.z, hA.w); h4 = fx::mk(hB.x, hB.y);
-                    hs = LV == 3 ? fx::mk(hB.z, hB.w) : (LV == 2 ? h4 : h2);           // h^(16 / R): the chunk's step
+                    const float q1 = __uint_as_float(qmax);
+                    const unsigned ball = __ballot_sync(0xffffffffu, qb == qmax);
+                    const int src = __ffs((int)ball) - 1;
+                    const int idx = __shfl_sync(0xffffffffu, k0 + 16 * (kab + R * (int)(__brev((unsigned)l) >> 27)), src);
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, off));
+                    // accepted iff the top bin holds 3/4 of N E (tier 1 of demod_cert.cu).  The decision does not depend on
+                    // the scale the estimate assumed (positive, finite; the rate it changes is re-checked); NaN samples are
+                    // invisible to fmaxf but poison E, an infinite max wipes the packet in the reference.  E is taken on the
+                    // raw samples: an upper bound of the scaled energy (scale <= 1) is all the test needs... but q1 is raw
+                    // too, so both sides carry the same factor.
+                    const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f) && (mmax < 3.0e38f);
+                    if (!cert) { bad = true; break; }
+                    if (s == 0) sw0 = idx;
+                    else if (s == 1) sw1 = idx;
+                    else if (l == 0) a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
                 }
-                // inside the chunk: accumulator j gets sum_{c' < CP} v[j + R c'] h^c' by halving
-                if (LV >= 3) {
-#pragma unroll
-                    for (int i = 0; i < 4 * R; ++i) v[i] = lean_cma(v[i], v[i + 4 * R], h4);
+                if (bad) {
+                    // abandon the packet: consume the copies still in flight so that the ring's phases stay consistent
+                    const uint32_t end = min(n_chunks, g + (uint32_t)(S - 1));
+                    for (; g < end; ++g) {
+                        ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                        phase_bits ^= 1u << stage;
+                        stage = stage + 1 == S ? 0 : stage + 1;
+                    }
+                    __syncwarp();
                 }
-                if (LV >= 2) {
-#pragma unroll
-                    for (int i = 0; i < 2 * R; ++i) v[i] = lean_cma(v[i], v[i + 2 * R], h2);
+            }
+            if (bad) {
+                if (l == 0) { a.flagged[pid] = 1; ++st_flagged; }
+            } else {
+                if (l == 0) {
+                    st_pruned += total;
+                    if (a.sync) a.sync[pid] = (uint8_t)((((sw0 >> (SF - 4)) & 0xf) << 4) | ((sw1 >> (SF - 4)) & 0xf));
+                    if (a.status) a.status[pid] = (int)(total - 2);
                 }
-#pragma unroll
-                for (int i = 0; i < R; ++i) v[i] = lean_cma(v[i], v[i + R], h1);
-                if (q == 0) {
-#pragma unroll
-                    for (int j = 0; j < R; ++j) acc[j] = v[j];
-                } else {
-#pragma unroll
-                    for (int j = 0; j < R; ++j) acc[j] = lean_cma(acc[j], v[j], hq);
-                }
-                hq = q == 0 ? hs : ff::fcmul(hq, hs);
-                stage = stage + 1 == S ? 0 : stage + 1;
+                // the estimate assumed max-abs used_max (LoRaDemod.cpp:61-78): right iff the packet's own max says the same
+                const bool hit = (mmax > 1.0f) ? (mmax == mine.used_max) : !(mine.used_max > 1.0f);
+                if (!hit) { vpid = (int)pid; vmax = mmax; vrate = rate; vtoff = mine.t_off; }
+                pred_max = mmax;
             }
-            // ---- end of the window: thread t = l + 32 j holds acc[j]; twiddle exp(j t theta), theta = rate - 2 pi k0 / N ----
-            const cf el = ff::fcmul(geo_f, twl[l * k0]);                               // F_l W_N^(l k0)
-#pragma unroll
-            for (int j = 0; j < R; ++j) {
-                cf u = ff::fcmul(acc[j], el);
-                if (j > 0) u = ff::fcmul(u, ff::fcmul(g32[j], tw32[j * k0]));          // G32^j W_N^(32 j k0)
-                acc[j] = u;
-            }
-            // R-point DFT across the window's warps-that-were (natural order), cross twiddle, R lane transforms
-            if (R == 2) ff::dft2(acc[0], acc[1]);
-            if (R == 4) ff::dft4(acc[0], acc[1], acc[2], acc[3]);
-            if (R == 8) ff::dft8(acc[0], acc[1], acc[2], acc[3], acc[4], acc[5], acc[6], acc[7]);
-#pragma unroll
-            for (int ka = 1; ka < R; ++ka) acc[ka] = ff::fcmul(acc[ka], twx[ka * 32 + l]);
-#pragma unroll
-            for (int sgi = 0; sgi < 5; ++sgi) {
-                const int h = 16 >> sgi;
-                const bool last = sgi == 4;
-                const cf tw = last ? fx::mk(1.0f, 0.0f) : tws[sgi * 32 + l];
-#pragma unroll
-                for (int ka = 0; ka < R; ++ka) acc[ka] = fp::lane_stage(acc[ka], h, (l & h) != 0, tw, last);
-            }
-            unsigned qb = 0u;
-            int kab = 0;
-#pragma unroll
-            for (int ka = 0; ka < R; ++ka) {
-                const unsigned qv = __float_as_uint(ff::fnorm(acc[ka]));              // >= +0, or NaN (sorts above everything)
-                if (qv > qb) { qb = qv; kab = ka; }
-            }
-            unsigned qmax = qb;
-            float en = ((e0.x + e0.y) + (e1.x + e1.y)) * 1.000002f;
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
-                en += __shfl_xor_sync(0xffffffffu, en, off);
-            }
-            const float q1 = __uint_as_float(qmax);
-            const unsigned ball = __ballot_sync(0xffffffffu, qb == qmax);
-            const int src = __ffs((int)ball) - 1;
-            const int idx = __shfl_sync(0xffffffffu, k0 + 16 * (kab + R * (int)(__brev((unsigned)l) >> 27)), src);
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, off));
-            // accepted iff the top bin holds 3/4 of N E (tier 1 of demod_cert.cu).  The decision does not depend on the 1/max
-            // normalisation the estimator pass assumed away (positive scale; the rate it changes is checked by the third
-            // pass); NaN samples are invisible to fmaxf but poison E, an infinite max wipes the packet in the reference
-            const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f) && (mmax < 3.0e38f);
-            if (!cert) { bad = true; break; }
-            if (s == 0) sw0 = idx;
-            else if (s == 1) sw1 = idx;
-            else if (l == 0) a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
-        }
-        if (bad) {
-            // abandon the packet: consume the copies still in flight so that the ring's phases stay consistent
-            const uint32_t end = min(n_chunks, g + (uint32_t)(S - 1));
-            for (; g < end; ++g) {
-                ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
-                phase_bits ^= 1u << stage;
-                stage = stage + 1 == S ? 0 : stage + 1;
-            }
-            __syncwarp();
-        }
-        if (bad) {
-            if (l == 0) { a.flagged[pid] = 1; ++st_flagged; }
-        } else if (l == 0) {
-            st_pruned += total;
-            if (mmax > 1.0f) { a.pmax[pid] = mmax; a.flagged[pid] = 2; }       // LoRaDemod.cpp:69-78: the estimator needs the scale
-            if (a.sync) a.sync[pid] = (uint8_t)((((sw0 >> (SF - 4)) & 0xf) << 4) | ((sw1 >> (SF - 4)) & 0xf));
-            if (a.status) a.status[pid] = (int)(total - 2);
         }
     }
     if (a.cert_stats && l == 0) {
         if (st_pruned) { atomicAdd(a.cert_stats + 0, (unsigned long long)st_pruned); atomicAdd(a.cert_stats + 4, (unsigned long long)st_pruned); }
         if (st_flagged) atomicAdd(a.cert_stats + 5, (unsigned long long)st_flagged);
     }
+    if (a.cert_stats && tid == 0 && st_est2) atomicAdd(a.cert_stats + 2, (unsigned long long)st_est2);
 }
 
 template <int SF>
