@@ -49,7 +49,9 @@ constexpr int LEAN_CHUNK = 512;                   // samples per step: 4 KB
 
 template <int SF>
 struct LeanCfg {
-    static constexpr int N = 1 << SF, T = N / 16, R = N / LEAN_CHUNK;      // R = T / 32 accumulators per lane
+    static constexpr bool WIDE = SF >= 10;                                // a window spans R > 1 chunks (else GD windows per chunk)
+    static constexpr int N = 1 << SF, T = N / 16, R = WIDE ? N / LEAN_CHUNK : 1;   // R = T / 32 accumulators per lane
+    static constexpr int GD = WIDE ? 1 : LEAN_CHUNK / N;                  // windows per chunk (SF7: 4, SF8: 2, SF9: 1)
     static constexpr int CP = 16 / R;                                     // terms per accumulator and chunk
     static constexpr int LV = CP == 8 ? 3 : CP == 4 ? 2 : 1;              // halving levels inside a chunk
     static constexpr int WARPS = LEAN_CTA / 32;
@@ -87,15 +89,19 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
     using C = LeanCfg<SF>;
     using PR = fp::Prune<SF>;
     using P = fx::Plan<SF>;
-    constexpr int N = C::N, T = C::T, R = C::R, LV = C::LV, S = LEAN_STAGES, TW = T / 32;
-    static_assert(R >= 2 && R <= 8, "streaming variant: SF10..SF12");
+    constexpr int N = C::N, T = C::T, R = C::R, LV = C::LV, S = LEAN_STAGES, TW = T > 32 ? T / 32 : 1;
+    constexpr bool WIDE = C::WIDE;
+    constexpr int GD = C::GD, GDE = T < 32 ? 32 / T : 1;       // windows per chunk; windows the estimator runs side by side
     static_assert(LEAN_CTA == CTA_THREADS, "the exact estimator's group helpers assume CTA_THREADS");
-    static_assert((size_t)TW * S * LEAN_CHUNK >= (size_t)N, "the team's ring doubles as the exact transform's exchange buffer");
+    static_assert((size_t)TW * S * LEAN_CHUNK >= (size_t)N * (GDE < 2 ? 1 : 2), "the team's ring doubles as the exact transform's exchange buffer");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, l = threadIdx.x & 31;
-    const int team = threadIdx.x / T, tid = threadIdx.x % T, wt = warp % TW;       // team, thread in team, warp in team
+    // team = the threads of one estimator transform's owner set: T / 32 warps (SF10-12) or one warp (SF7-9, where a warp
+    // holds 32 / T windows side by side); tid = thread inside a window, grp = window group inside the warp
+    const int team = WIDE ? threadIdx.x / T : warp, tid = threadIdx.x % T, wt = warp % TW, grp = WIDE ? 0 : l / T;
+    const bool lead = WIDE ? tid == 0 : l == 0;                // the team's first thread
     cf* ring = reinterpret_cast<cf*>(smem_raw) + (size_t)warp * S * LEAN_CHUNK;
-    cf* ex = reinterpret_cast<cf*>(smem_raw) + (size_t)(team * TW) * S * LEAN_CHUNK;   // N entries: exchange, then spectrum
+    cf* ex = reinterpret_cast<cf*>(smem_raw) + (size_t)(team * TW) * S * LEAN_CHUNK + (size_t)grp * N;   // N entries: exchange, then spectrum
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::bar_off) + warp * S;
     cf* tws = reinterpret_cast<cf*>(smem_raw + C::tws_off);
     cf* twl = reinterpret_cast<cf*>(smem_raw + C::twl_off);
@@ -113,14 +119,14 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
         for (int s = 0; s < S; ++s) ptx::mbar_init(&full[s], 1);
         ptx::fence_mbar_init();
     }
-    for (int j = threadIdx.x; j < PR::STAGES_TW * 32; j += LEAN_CTA) {
+    for (int j = threadIdx.x; j < PR::STAGES_TW * PR::W; j += LEAN_CTA) {
         double sn, cs;
-        sincospi(-2.0 * (double)PR::stage_exp(j / 32, j % 32) / 32.0, &sn, &cs);
+        sincospi(-2.0 * (double)PR::stage_exp(j / PR::W, j % PR::W) / (double)PR::W, &sn, &cs);
         tws[j] = fx::mk((float)cs, (float)sn);
     }
     for (int j = threadIdx.x; j < 512; j += LEAN_CTA) {
         double sn, cs;
-        sincospi(-2.0 * (double)j / (double)N, &sn, &cs);
+        sincospi(-2.0 * (double)(j & (N - 1)) / (double)N, &sn, &cs);
         twl[j] = fx::mk((float)cs, (float)sn);
     }
     for (int j = threadIdx.x; j < 128; j += LEAN_CTA) {
@@ -146,6 +152,7 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
     unsigned st_pruned = 0, st_flagged = 0, st_est2 = 0;
     const uint32_t n_warps = gridDim.x * C::WARPS;
     const uint32_t gw0 = blockIdx.x * C::WARPS + (uint32_t)(team * TW);            // the team's first warp, grid-wide
+    LeanTeamCell* mycell = &cells[wt];
     float pred_max = 0.0f;                                     // max-abs of this warp's previous packet
     int vpid = -1; float vmax = 0.0f, vrate = 0.0f; int vtoff = 0;                 // this warp's pending re-estimate
 
@@ -156,12 +163,17 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
         const bool norm = use_max > 1.0f;
         const float scale = norm ? __fdiv_rn(1.0f, use_max) : 1.0f;
 #pragma unroll 1
-        for (int s = 0; s < 2; ++s) {
+        for (int s0 = 0; s0 < 2; s0 += GDE) {
+            const int s = s0 + grp;
+            const bool live = s < 2;
             cf v[P::R];
 #pragma unroll
             for (int c = 0; c < P::R; ++c) {
-                cf x = ldg_cf(pkt + (size_t)s * N + tid + T * c);
-                if (norm) x = fx::cscale(x, scale);                                    // LoRaDemod.cpp:75-77
+                cf x = fx::mk(0.0f, 0.0f);
+                if (live) {
+                    x = ldg_cf(pkt + (size_t)s * N + tid + T * c);
+                    if (norm) x = fx::cscale(x, scale);                                // LoRaDemod.cpp:75-77
+                }
                 v[c] = x;
             }
             fft_inplace<SF, true>(v, tid, a.tw, a.ct, ex);
@@ -170,7 +182,7 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
 #pragma unroll
             for (int r = 0; r < P::R; ++r) ex[P::bin_of_reg(tid, r)] = v[r];
             group_sync<T>();
-            if (tid == 0) {
+            if (tid == 0 && live) {
                 LeanEst e; e.idx = 0; e.fi = 0.0f; e.phase = 0.0f;
                 cf best_bin = fx::mk(0.0f, 0.0f);
                 if (pk.val > 0.0f) {                           // candidate kept iff its power beats -1e30 dB: max > 0
@@ -188,7 +200,7 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
             }
             group_sync<T>();
         }
-        if (tid == 0) {                                        // LoRaDemod.cpp:126-139
+        if (lead) {                                            // LoRaDemod.cpp:126-139
             const float PI_F = 3.14159265358979323846f;
             const LeanEst e0 = est[0], e1 = est[1];
             float sum_index = fx::fadd(0.0f, fx::fadd((float)e0.idx, e0.fi));
@@ -225,7 +237,7 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
                 any = true;
                 float cfo = 0.0f, toff = 0.0f, rate = 0.0f; int t_off = 0;
                 estimate((uint32_t)vp, cells[m].vmax, cfo, toff, rate, t_off);
-                if (tid == 0) {
+                if (lead) {
                     // the streamed symbols stand iff the window bases and (within the certified tolerance) the rate do
                     const bool same = t_off == cells[m].vtoff && fabsf(fx::fsub(rate, cells[m].vrate)) * (float)N <= 64.0f * LEAN_U;
                     if (same) {
@@ -251,15 +263,15 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
                 if (shape) {
                     float cfo = 0.0f, toff = 0.0f, rate = 0.0f; int t_off = 0;
                     estimate(pid, cells[m].pred, cfo, toff, rate, t_off);
-                    if (tid == 0) {
+                    if (lead) {
                         if (a.cfo) a.cfo[pid] = cfo;
                         if (a.time_offset) a.time_offset[pid] = toff;
                         cells[m].rate = rate; cells[m].t_off = t_off; cells[m].used_max = cells[m].pred;
                     }
                     ok = 1;
                 }
-                if (tid == 0) cells[m].ok = ok;
-            } else if (tid == 0) {
+                if (lead) cells[m].ok = ok;
+            } else if (lead) {
                 cells[m].ok = -1;                              // no packet this round
             }
         }
@@ -283,6 +295,7 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
             const float tier1 = 0.75f * (float)N;
             float mmax = 0.0f;
             int sw0 = 0, sw1 = 0;
+            if constexpr (WIDE) {
             if (!bad) {
                 // per packet: F_l = exp(j rate l); G^(1,2,4,8) (G = exp(j rate T)) and G32^j (exp(j rate 32 j)) in double;
                 // hp[k0][m] = G^(2^m) W16^(k0 2^m)
@@ -458,6 +471,135 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
                     __syncwarp();
                 }
             }
+            } else {
+            if (!bad) {
+                // SF7-9: GD = 512 / N whole windows per 4 KB step, T = N / 16 <= 32 lanes per window (demod_cert.cu's
+                // geometric pruned step, with one bulk copy per step and nothing else in the kernel)
+                const int gq = l / T;
+                cf geo_f;
+                {
+                    float sn, cs;
+                    __sincosf(fx::fmul(rate, (float)tid), &sn, &cs);   // |rate tid| < 2 pi / 16
+                    geo_f = fx::mk(cs, sn);
+                    double ds = 0.0, dc = 1.0;
+                    if (l < 4) sincos((double)rate * (double)(T << l), &ds, &dc);
+                    const float gx = (float)dc, gy = (float)ds;
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const int e = l + 32 * h2, k = e >> 2, mi = e & 3;
+                        const cf g = fx::mk(__shfl_sync(0xffffffffu, gx, mi), __shfl_sync(0xffffffffu, gy, mi));
+                        hp[e] = ff::fcmul(g, w16[(k << mi) & 15]);
+                    }
+                    __syncwarp();
+                }
+                const cf geo_g1 = hp[0];
+                const uint32_t n_chunks = (total + (uint32_t)GD - 1) / (uint32_t)GD;
+                auto issue = [&](uint32_t g, int stg) {                // lane 0: the step's windows are contiguous
+                    const uint32_t left = total - g * (uint32_t)GD;
+                    const uint32_t bytes = (left < (uint32_t)GD ? left : (uint32_t)GD) * (uint32_t)(N * sizeof(cf));
+                    ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, bytes);
+                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_CHUNK * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK, bytes,
+                                     bar0 + 8u * (uint32_t)stg);
+                };
+                if (l == 0) {
+                    int stg = stage;
+                    for (uint32_t g = 0; g < (uint32_t)(S - 1) && g < n_chunks; ++g) { issue(g, stg); stg = stg + 1 == S ? 0 : stg + 1; }
+                }
+                uint32_t g = 0;
+#pragma unroll 1
+                for (; g < n_chunks && !bad; ++g) {
+                    __syncwarp();                                      // every lane has finished the slot that is refilled now
+                    if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
+                        int stg = stage + (S - 1);
+                        if (stg >= S) stg -= S;
+                        issue(g + (uint32_t)(S - 1), stg);
+                    }
+                    ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                    phase_bits ^= 1u << stage;
+                    const uint32_t s = g * (uint32_t)GD + (uint32_t)gq;
+                    const bool active = s < total;
+                    const cf* raw = ring + (size_t)stage * LEAN_CHUNK + gq * N + tid;
+                    cf v[16];
+                    float mw = 0.0f;
+                    cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) {
+                        const cf r = raw[T * c];
+                        mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                         // LoRaDemod.cpp:61-68
+                        if (c & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
+                        v[c] = r;
+                    }
+                    if (active) mmax = fmaxf(mmax, mw);
+                    float en = ((e0.x + e0.y) + (e1.x + e1.y)) * 1.000002f;
+                    // bin class from the phase step between neighbouring samples of a thread (T apart), four pairs per thread
+                    cf z = fx::mk(0.0f, 0.0f);
+#pragma unroll
+                    for (int c = 0; c < 16; c += 4) {
+                        z.x = ff::fma_(v[c + 1].x, v[c].x, z.x); z.x = ff::fma_(v[c + 1].y, v[c].y, z.x);
+                        z.y = ff::fma_(v[c + 1].y, v[c].x, z.y); z.y = ff::fma_(-v[c + 1].x, v[c].y, z.y);
+                    }
+#pragma unroll
+                    for (int off = T / 2; off > 0; off >>= 1) {
+                        z.x += __shfl_xor_sync(0xffffffffu, z.x, off);
+                        z.y += __shfl_xor_sync(0xffffffffu, z.y, off);
+                    }
+                    z = ff::fcmul(z, geo_g1);
+                    int k0;
+                    {
+                        const float ax = fabsf(z.x), ay = fabsf(z.y);
+                        const float mn = fminf(ax, ay), mx = fmaxf(ax, ay);
+                        int qq = (mn > 0.19891237f * mx ? 1 : 0) + (mn > 0.66817864f * mx ? 1 : 0);
+                        if (ay > ax) qq = 4 - qq;
+                        if (z.x < 0.0f) qq = 8 - qq;
+                        if (z.y < 0.0f) qq = 16 - qq;
+                        k0 = qq & 15;
+                    }
+                    const float4 hA = *reinterpret_cast<const float4*>(&hp[4 * k0]);
+                    const float4 hB = *reinterpret_cast<const float4*>(&hp[4 * k0 + 2]);
+                    const cf h1 = fx::mk(hA.x, hA.y), h2 = fx::mk(hA.z, hA.w), h4 = fx::mk(hB.x, hB.y), h8 = fx::mk(hB.z, hB.w);
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) v[c] = lean_cma(v[c], v[c + 8], h8);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) v[c] = lean_cma(v[c], v[c + 4], h4);
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) v[c] = lean_cma(v[c], v[c + 2], h2);
+                    const cf pv = lean_cma(v[0], v[1], h1);
+                    const cf cval = ff::fcmul(ff::fcmul(pv, twl[(tid * k0) & (N - 1)]), geo_f);
+                    const cf yv = fp::lane_dft<SF>(cval, tid, tws);
+                    const unsigned qb = __float_as_uint(ff::fnorm(yv));               // >= +0, or NaN (sorts above everything)
+                    unsigned qmax = qb;
+#pragma unroll
+                    for (int off = T / 2; off > 0; off >>= 1) {
+                        qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
+                        en += __shfl_xor_sync(0xffffffffu, en, off);
+                    }
+                    const float q1 = __uint_as_float(qmax);
+                    const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
+                    if (active && cert && qb == qmax) {                    // the lane that holds the top bin (unique when certified)
+                        const int idx = k0 + 16 * (int)(__brev((unsigned)tid) >> (32 - PR::LW));
+                        if (s < 2) mycell->pad[s] = idx;
+                        else a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
+                    }
+                    if (__any_sync(0xffffffffu, active && !cert)) bad = true;
+                    stage = stage + 1 == S ? 0 : stage + 1;
+                }
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, off));
+                if (!(mmax < 3.0e38f)) bad = true;                         // an infinite max wipes the packet in the reference
+                __syncwarp();
+                sw0 = mycell->pad[0]; sw1 = mycell->pad[1];
+                if (bad) {
+                    // abandon the packet: consume the copies still in flight so that the ring's phases stay consistent
+                    const uint32_t end = min(n_chunks, g + (uint32_t)(S - 1));
+                    for (; g < end; ++g) {
+                        ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                        phase_bits ^= 1u << stage;
+                        stage = stage + 1 == S ? 0 : stage + 1;
+                    }
+                    __syncwarp();
+                }
+            }
+            }
             if (bad) {
                 if (l == 0) { a.flagged[pid] = 1; ++st_flagged; }
             } else {
@@ -477,7 +619,7 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
         if (st_pruned) { atomicAdd(a.cert_stats + 0, (unsigned long long)st_pruned); atomicAdd(a.cert_stats + 4, (unsigned long long)st_pruned); }
         if (st_flagged) atomicAdd(a.cert_stats + 5, (unsigned long long)st_flagged);
     }
-    if (a.cert_stats && tid == 0 && st_est2) atomicAdd(a.cert_stats + 2, (unsigned long long)st_est2);
+    if (a.cert_stats && lead && st_est2) atomicAdd(a.cert_stats + 2, (unsigned long long)st_est2);
 }
 
 template <int SF>
@@ -499,13 +641,16 @@ static cudaError_t launch_lean_sf(const DemodArgs& a, int sm_count, cudaStream_t
 
 bool lean_supported(int sf, const DemodArgs& a)
 {
-    return sf >= 10 && sf <= 12 && a.osr == 1 && a.mode == MODE_LEGACY && !a.window && !a.down && !a.no_scratch &&
+    return sf >= 7 && sf <= 12 && a.osr == 1 && a.mode == MODE_LEGACY && !a.window && !a.down && !a.no_scratch &&
            !a.force_exact && (unsigned long long)a.samples_per_packet < 0xf0000000ull;
 }
 
 cudaError_t launch_demod_lean(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream)
 {
     switch (sf) {
+    case 7: return launch_lean_sf<7>(a, sm_count, stream);
+    case 8: return launch_lean_sf<8>(a, sm_count, stream);
+    case 9: return launch_lean_sf<9>(a, sm_count, stream);
     case 10: return launch_lean_sf<10>(a, sm_count, stream);
     case 11: return launch_lean_sf<11>(a, sm_count, stream);
     case 12: return launch_lean_sf<12>(a, sm_count, stream);
