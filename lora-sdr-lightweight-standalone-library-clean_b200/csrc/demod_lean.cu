@@ -33,6 +33,16 @@
 
 namespace lk {
 
+#ifndef LEAN_CTA_NARROW
+#define LEAN_CTA_NARROW 256                   // SF7-9 (a window is at most one warp): threads per CTA, any multiple of 32
+#endif
+#ifndef LEAN_CTAS_NARROW
+#define LEAN_CTAS_NARROW 2                    // ... and resident CTAs per SM for SF8 / SF9 (occupancy A/B knobs; measured on B200:
+                                              // SF7 5729 -> 6146 GB/s with 3 x 256 threads (80 registers), SF8 6886 -> 6124)
+#endif
+#ifndef LEAN_CTAS_SF7
+#define LEAN_CTAS_SF7 3
+#endif
 #ifndef LEAN_CTA
 #define LEAN_CTA 256
 #endif
@@ -54,13 +64,15 @@ struct LeanCfg {
     static constexpr int GD = WIDE ? 1 : LEAN_CHUNK / N;                  // windows per chunk (SF7: 4, SF8: 2, SF9: 1)
     static constexpr int CP = 16 / R;                                     // terms per accumulator and chunk
     static constexpr int LV = CP == 8 ? 3 : CP == 4 ? 2 : 1;              // halving levels inside a chunk
-    static constexpr int WARPS = LEAN_CTA / 32;
+    static constexpr int CTA = WIDE ? LEAN_CTA : LEAN_CTA_NARROW, CTAS = WIDE ? LEAN_CTAS_PER_SM : (SF == 7 ? LEAN_CTAS_SF7 : LEAN_CTAS_NARROW);
+    static constexpr int WARPS = CTA / 32;
     static constexpr size_t ring_bytes = (size_t)WARPS * LEAN_STAGES * LEAN_CHUNK * sizeof(cf);
     static constexpr size_t bar_off = ring_bytes;
     static constexpr size_t tws_off = (bar_off + (size_t)WARPS * LEAN_STAGES * 8 + 15) & ~(size_t)15;   // [4][32] lane-stage factors
     static constexpr size_t twl_off = tws_off + 4 * 32 * sizeof(cf);                                   // W_N^e, e < 512
-    static constexpr size_t tw32_off = twl_off + 512 * sizeof(cf);                                     // W_N^(32 e), e < 128
-    static constexpr size_t twx_off = tw32_off + 128 * sizeof(cf);                                     // W_T^(l ka), [ka][l]
+    static constexpr int TWL = WIDE ? 512 : N;                                                         // (narrow: the whole circle)
+    static constexpr size_t tw32_off = twl_off + (size_t)TWL * sizeof(cf);                             // W_N^(32 e), e < 128
+    static constexpr size_t twx_off = tw32_off + (WIDE ? 128 : 0) * sizeof(cf);                        // W_T^(l ka), [ka][l]
     static constexpr size_t w16_off = twx_off + (size_t)R * 32 * sizeof(cf);                           // W16^j
     static constexpr size_t hp_off = w16_off + 16 * sizeof(cf);                                        // per warp: [k0][4] powers of h
     static constexpr size_t g32_off = hp_off + (size_t)WARPS * 64 * sizeof(cf);                        // per warp: G32^j, j < 8
@@ -84,7 +96,7 @@ struct LeanTeamCell {       // one per warp: what the team's estimator phase han
 struct LeanEst { int idx; float fi; float phase; };
 
 template <int SF>
-__global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(const DemodArgs a)
+__global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lean_kernel(const DemodArgs a)
 {
     using C = LeanCfg<SF>;
     using PR = fp::Prune<SF>;
@@ -92,7 +104,7 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
     constexpr int N = C::N, T = C::T, R = C::R, LV = C::LV, S = LEAN_STAGES, TW = T > 32 ? T / 32 : 1;
     constexpr bool WIDE = C::WIDE;
     constexpr int GD = C::GD, GDE = T < 32 ? 32 / T : 1;       // windows per chunk; windows the estimator runs side by side
-    static_assert(LEAN_CTA == CTA_THREADS, "the exact estimator's group helpers assume CTA_THREADS");
+    static_assert(!WIDE || C::CTA == CTA_THREADS, "the exact estimator's group helpers assume CTA_THREADS for multi-warp windows");
     static_assert((size_t)TW * S * LEAN_CHUNK >= (size_t)N * (GDE < 2 ? 1 : 2), "the team's ring doubles as the exact transform's exchange buffer");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, l = threadIdx.x & 31;
@@ -119,27 +131,27 @@ __global__ void __launch_bounds__(LEAN_CTA, LEAN_CTAS_PER_SM) demod_lean_kernel(
         for (int s = 0; s < S; ++s) ptx::mbar_init(&full[s], 1);
         ptx::fence_mbar_init();
     }
-    for (int j = threadIdx.x; j < PR::STAGES_TW * PR::W; j += LEAN_CTA) {
+    for (int j = threadIdx.x; j < PR::STAGES_TW * PR::W; j += C::CTA) {
         double sn, cs;
         sincospi(-2.0 * (double)PR::stage_exp(j / PR::W, j % PR::W) / (double)PR::W, &sn, &cs);
         tws[j] = fx::mk((float)cs, (float)sn);
     }
-    for (int j = threadIdx.x; j < 512; j += LEAN_CTA) {
+    for (int j = threadIdx.x; j < C::TWL; j += C::CTA) {
         double sn, cs;
         sincospi(-2.0 * (double)(j & (N - 1)) / (double)N, &sn, &cs);
         twl[j] = fx::mk((float)cs, (float)sn);
     }
-    for (int j = threadIdx.x; j < 128; j += LEAN_CTA) {
+    for (int j = threadIdx.x; j < (WIDE ? 128 : 0); j += C::CTA) {
         double sn, cs;
         sincospi(-2.0 * (double)((32 * j) & (N - 1)) / (double)N, &sn, &cs);
         tw32[j] = fx::mk((float)cs, (float)sn);
     }
-    for (int j = threadIdx.x; j < R * 32; j += LEAN_CTA) {
+    for (int j = threadIdx.x; j < R * 32; j += C::CTA) {
         double sn, cs;
         sincospi(-2.0 * (double)PR::cross_exp(j / 32, j % 32) / (double)T, &sn, &cs);
         twx[j] = fx::mk((float)cs, (float)sn);
     }
-    for (int j = threadIdx.x; j < 16; j += LEAN_CTA) {
+    for (int j = threadIdx.x; j < 16; j += C::CTA) {
         double sn, cs;
         sincospi(-2.0 * (double)j / 16.0, &sn, &cs);
         w16[j] = fx::mk((float)cs, (float)sn);
@@ -633,9 +645,9 @@ static cudaError_t launch_lean_sf(const DemodArgs& a, int sm_count, cudaStream_t
         cudaFuncSetAttribute(demod_lean_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
         attr_done[dev & 63].store(true, std::memory_order_release);
     }
-    const unsigned max_ctas = (unsigned)sm_count * LEAN_CTAS_PER_SM;      // persistent grid
+    const unsigned max_ctas = (unsigned)sm_count * C::CTAS;               // persistent grid
     const unsigned need = (a.n_packets + C::WARPS - 1) / C::WARPS;
-    demod_lean_kernel<SF><<<need < max_ctas ? need : max_ctas, LEAN_CTA, C::bytes, stream>>>(a);
+    demod_lean_kernel<SF><<<need < max_ctas ? need : max_ctas, C::CTA, C::bytes, stream>>>(a);
     return cudaGetLastError();
 }
 
