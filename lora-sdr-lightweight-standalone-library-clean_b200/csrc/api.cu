@@ -327,7 +327,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.time_offset = d_to;
     a.status = d_status;
     a.force_exact = 0;
-    a.unit_scale = 0; a.skip_sync = 0; a.flagged = nullptr; a.only_flagged = nullptr; a.pmax = nullptr;
+    a.unit_scale = 0; a.skip_sync = 0; a.flagged = nullptr; a.only_flagged = nullptr; a.pmax = nullptr; a.n_flagged = nullptr;
     a.cert_stats = ctx->cert_stats;
     unsigned launches = 0;
     // SF10-12, pre-dechirped IQ (the cfg-3 shape): two launches.  (1) demod_lean.cu: the exact two-symbol estimator by
@@ -336,20 +336,22 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     static const bool lean_off = getenv("LORA_PHY_NO_LEAN") != nullptr;
     if (!lean_off && !(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&
         lk::lean_supported((int)cfg->sf, a) && lk::cert_supported((int)cfg->sf, a)) {
-        CK(ctx->flag.reserve(n_packets));
+        CK(ctx->flag.reserve(((n_packets + 15) & ~(size_t)15) + 16));
         CK(ctx->pmax.reserve(n_packets * sizeof(float)));
-        CK(cudaMemsetAsync(ctx->flag.p, 0, n_packets, ctx->stream));
+        CK(cudaMemsetAsync(ctx->flag.p, 0, ((n_packets + 15) & ~(size_t)15) + 16, ctx->stream));     // flags, then (16-byte aligned) the flagged-packet counter
         lk::DemodArgs p = a;
         cudaError_t e;
         p = a;
         p.flagged = static_cast<uint8_t*>(ctx->flag.p);
         p.pmax = static_cast<float*>(ctx->pmax.p);
+        p.n_flagged = reinterpret_cast<unsigned*>(static_cast<uint8_t*>(ctx->flag.p) + ((n_packets + 15) & ~(size_t)15));
         e = lk::launch_demod_lean((int)cfg->sf, p, ctx->sm_count, ctx->stream);
         ++launches;
         if (e != cudaSuccess) return fail(ctx, -EIO, "lean demodulator launch", e);
         p = a;
         p.only_flagged = static_cast<const uint8_t*>(ctx->flag.p);
         p.pmax = static_cast<float*>(ctx->pmax.p);
+        p.n_flagged = reinterpret_cast<unsigned*>(static_cast<uint8_t*>(ctx->flag.p) + ((n_packets + 15) & ~(size_t)15));
         e = lk::launch_demod_cert((int)cfg->sf, p, ctx->sm_count, ctx->stream);
         ++launches;
         ctx->launches += launches;

@@ -230,6 +230,7 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
     cf* tw1 = reinterpret_cast<cf*>(smem_raw + C::tw1_off);
     CertShared& ws = reinterpret_cast<CertShared*>(smem_raw + C::ws_off)[dom];
 
+    if (a.only_flagged && a.n_flagged && *a.n_flagged == 0u) return;     // lean route: nothing was handed over
     // ---- start-up: barriers, twiddles, address bases ------------------------------------------------------------
     if (lane == 0) {
 #pragma unroll

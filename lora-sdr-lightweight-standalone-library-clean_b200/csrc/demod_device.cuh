@@ -60,6 +60,7 @@ struct DemodArgs {
                                   // settled every symbol but the packet's max-abs (pmax) exceeds 1: redo the estimator with the
                                   // true scale, and keep the lean symbols if rate / t_off stay within the certified tolerance
     float* pmax;                  // lean pass: max-abs of the packets it marks 2
+    unsigned* n_flagged;          // lean pass: number of packets it flagged (the certified pass returns at once on 0)
     int force_exact;              // LORA_PHY_CUDA_F_EXACT: the certified kernel replays the exact chain for every window
     unsigned long long* cert_stats;   // [8] windows walked, windows replayed exactly, second estimates, re-walked packets, windows settled by the pruned transform
 };

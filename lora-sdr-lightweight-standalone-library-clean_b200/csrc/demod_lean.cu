@@ -631,6 +631,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
         if (st_pruned) { atomicAdd(a.cert_stats + 0, (unsigned long long)st_pruned); atomicAdd(a.cert_stats + 4, (unsigned long long)st_pruned); }
         if (st_flagged) atomicAdd(a.cert_stats + 5, (unsigned long long)st_flagged);
     }
+    if (a.n_flagged && st_flagged) atomicAdd(a.n_flagged, st_flagged);
     if (a.cert_stats && lead && st_est2) atomicAdd(a.cert_stats + 2, (unsigned long long)st_est2);
 }
 
