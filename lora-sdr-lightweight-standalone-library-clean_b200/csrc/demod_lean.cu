@@ -347,8 +347,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 for (uint32_t s = 0; s < total; ++s) {
                     cf acc[R];
                     cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
-                    cf hq = fx::mk(1.0f, 0.0f);
-                    cf h1 = hq, h2 = hq, h4 = hq, hs = hq;
+                    cf h1 = fx::mk(1.0f, 0.0f), h2 = h1, h4 = h1, h8 = h1;
                     int k0 = 0;
 #pragma unroll
                     for (int q = 0; q < R; ++q, ++g) {
@@ -395,8 +394,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                             k0 = qq & 15;
                             const float4 hA = *reinterpret_cast<const float4*>(&hp[4 * k0]);
                             const float4 hB = *reinterpret_cast<const float4*>(&hp[4 * k0 + 2]);
-                            h1 = fx::mk(hA.x, hA.y); h2 = fx::mk(hA.z, hA.w); h4 = fx::mk(hB.x, hB.y);
-                            hs = LV == 3 ? fx::mk(hB.z, hB.w) : (LV == 2 ? h4 : h2);           // h^(16 / R): the chunk's step
+                            h1 = fx::mk(hA.x, hA.y); h2 = fx::mk(hA.z, hA.w); h4 = fx::mk(hB.x, hB.y); h8 = fx::mk(hB.z, hB.w);
                         }
                         // inside the chunk: accumulator j gets sum_{c' < CP} v[j + R c'] h^c' by halving
                         if (LV >= 3) {
@@ -413,10 +411,17 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
 #pragma unroll
                             for (int j = 0; j < R; ++j) acc[j] = v[j];
                         } else {
+                            // h^(q 16 / R) from the table's powers of two (at most two products of accurate factors: a running
+                            // product would carry seven roundings into the window's last chunk)
+                            const int e = q * (16 / R);                    // 2 .. 14, compile-time
+                            cf hq = fx::mk(1.0f, 0.0f);
+                            bool first = true;
+                            if (e & 2) { hq = h2; first = false; }
+                            if (e & 4) { hq = first ? h4 : ff::fcmul(hq, h4); first = false; }
+                            if (e & 8) { hq = first ? h8 : ff::fcmul(hq, h8); first = false; }
 #pragma unroll
                             for (int j = 0; j < R; ++j) acc[j] = lean_cma(acc[j], v[j], hq);
                         }
-                        hq = q == 0 ? hs : ff::fcmul(hq, hs);
                         stage = stage + 1 == S ? 0 : stage + 1;
                     }
                     // end of the window: thread t = l + 32 j holds acc[j]; twiddle exp(j t theta), theta = rate - 2 pi k0 / N

@@ -44,10 +44,11 @@ def test_fft_fast_emulation():
     within 2e-6 of a double DFT, every exchange address written once and read once inside the window slot, every 64-bit
     access phase bank-conflict free, output bin map a permutation -- SF7 (both register layouts) to SF12; and the pruned
     transform of fft_prune.cuh (pass-0 and geometric variants, single- and multi-warp windows): every bin of every class
-    against the double DFT, bin map covering each class exactly once."""
+    against the double DFT, bin map covering each class exactly once; and its streaming form (demod_lean.cu: R accumulators
+    per lane, chunk joins from the table's powers of two, in-register cross stage) for SF10-12."""
     exe = compile_cpp("test_fft_fast_emulation", ["-lm"])
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
-    assert len(lines) == 15 and all(l["match"] and l["worst_bank_conflict"] == 1 for l in lines)
-    assert sum("pruned" in l.get("layout", "") for l in lines) == 8
+    assert len(lines) == 18 and all(l["match"] and l["worst_bank_conflict"] == 1 for l in lines)
+    assert sum("pruned" in l.get("layout", "") for l in lines) == 11
