@@ -431,10 +431,10 @@ def run_ours(args, wl):
     peak = float(peaks["hbm_gbs"])
     b_sym = 8 * N + 2                                   # algorithmic bytes per demodulated symbol
     if two:
-        kname = "symbols_stream_kernel<SF%d>" % sf
+        kname = "symbols_kernel<SF%d>" % sf
         sym_bytes = P * (nsym - 2) * b_sym              # symbols kernel: data symbols of every packet, once
     else:
-        kname = (("demod_warp_kernel<SF%d>" if sf <= 11 else "demod_packet_kernel<SF%d>") if args.exact else "demod_lean_kernel<SF%d> (+ demod_cert_kernel over the packets it flags)") % sf
+        kname = ("demod_cert_kernel<SF%d>, every window replayed exactly" if args.exact else "demod_lean_kernel<SF%d> (+ demod_cert_kernel over the packets it flags)") % sf
         sym_bytes = P * nsym * b_sym                    # single launch: every symbol of every packet, once
     traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "r02_traffic.json")

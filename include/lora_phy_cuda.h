@@ -68,8 +68,8 @@ typedef struct lora_phy_cuda_cfg {
                                                margin-certified fast path that falls back to that replay per window only
                                                when the argmax is not provably the reference's.
                                                Symbols, sync word, status, cfo and time_offset are identical either way. */
-#define LORA_PHY_CUDA_F_TWO_KERNEL   0x80u /* A/B: force the older prepass + symbols kernel pair instead of the default
-                                              single launch with one CTA per packet (demod_packet.cu) */
+#define LORA_PHY_CUDA_F_TWO_KERNEL   0x80u /* A/B: force the prepass + symbols kernel pair (demod.cu: the route of osr > 1,
+                                              SF2-6 and estimate-only calls) instead of the default */
 
 /* ---- context -------------------------------------------------------------------------- */
 /* replaces lora_demod_init / init (LoRaDemod.cpp:11-33, phy.cpp:27-52): builds, ON THE DEVICE,

@@ -367,12 +367,13 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
         if (e != cudaSuccess) return fail(ctx, -EIO, "certified demodulator launch", e);
         return 0;
     }
-    // F_EXACT (A/B): one launch, every window through the operation-for-operation replay (demod_packet.cu)
+    // F_EXACT (A/B): the certified kernel with every window sent through its operation-for-operation replay
     if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL)) &&
-        lk::packet_supported((int)cfg->sf, a)) {
-        cudaError_t e = lk::launch_demod_packet((int)cfg->sf, a, ctx->sm_count, ctx->stream);
+        lk::cert_supported((int)cfg->sf, a)) {
+        a.force_exact = 1;
+        cudaError_t e = lk::launch_demod_cert((int)cfg->sf, a, ctx->sm_count, ctx->stream);
         ++ctx->launches;
-        if (e != cudaSuccess) return fail(ctx, -EIO, "packet demodulator launch", e);
+        if (e != cudaSuccess) return fail(ctx, -EIO, "certified demodulator launch (exact replay)", e);
         return 0;
     }
     const bool do_pre = !(cfg->flags & LORA_PHY_CUDA_F_ONLY_SYMBOLS);

@@ -305,11 +305,7 @@ static cudaError_t launch_demod_sf(const DemodArgs& a, int sm_count, cudaStream_
         ++*launches;
     }
     const unsigned long long items = (unsigned long long)a.n_packets * a.data_symbols_max;
-    if (symbols && items && stream_supported(SF, a)) {
-        cudaError_t e = launch_symbols_stream(SF, a, sm_count, stream);
-        if (e != cudaSuccess) return e;
-        ++*launches;
-    } else if (symbols && items) {
+    if (symbols && items) {
         unsigned long long need = (items + S::G - 1) / S::G;
         unsigned grid = need < max_ctas ? (unsigned)need : max_ctas;
         symbols_kernel<SF><<<grid, CTA_THREADS, S::bytes, stream>>>(a);

@@ -3,11 +3,11 @@
 // per-window work done by a THROUGHPUT transform whose argmax is PROVEN to be the reference's, window by window.
 //
 // Why: replaying the reference's float operations (glibc-exact sincosf per sample in FP64, un-fused kissfft
-// butterflies; demod_packet.cu) costs 92 thread-instructions per sample and leaves the kernel issue-bound at a
+// butterflies; round 1's kernels) costs 92 thread-instructions per sample and leaves the kernel issue-bound at a
 // third of the HBM rate.  north_star asks for bit-exact SYMBOLS (and 1e-4 on |X|^2), not bit-exact spectra, so:
 //
 //   E units (exact)   symbols 0,1 raw through the exact-order FFT: cfo, time_offset, rate, t_off bit for bit
-//                     (LoRaDemod.cpp:80-139) -- unchanged from demod_packet.cu.
+//                     (LoRaDemod.cpp:80-139) -- round 1's code.
 //   C units (fast)    every symbol: samples * f_c, where f_c = scale * [down_i] * exp(j*rate*i) * [w_i] is computed ONCE
 //                     PER PACKET per thread (|X|^2 does not depend on the per-symbol start phase, LoRaDemod.cpp:152-159),
 //                     then ff::Plan (fft_fast.cuh: FMA radix-16/8/4, 1-2 exchanges), |Y|^2, and the top bin.
@@ -18,7 +18,7 @@
 //                     second by more than that margin (tier 1: the top bin holds > 3/4 of N*E, by Parseval nothing else
 //                     can come near; tier 2: the true second maximum).  Then X^ has the same strict, unique maximum.
 //   fallback          windows that fail -- ties, noise-only windows with close bins, NaN / Inf / denormal input -- are
-//                     replayed through the exact chain of demod_packet.cu at the end of the packet, same launch.
+//                     replayed through round 1's exact chain (stream_common.cuh) at the end of the packet, same launch.
 //                     Symbols, sync word, status, cfo and time_offset are therefore bit-exact BY CONSTRUCTION.
 //
 // The 1/max normalisation (LoRaDemod.cpp:61-78) no longer forces a second walk: the certified decision is invariant to

@@ -31,14 +31,8 @@ __host__ __device__ inline float power_scale_of(int sf)
 cudaError_t launch_demod(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream, bool prepass,
                          bool symbols, unsigned* launches);
 cudaError_t launch_detect(int sf, const DetectArgs& a, int sm_count, cudaStream_t stream);
-// demod_stream.cu: TMA-staged data-symbol kernel (SF 7..12, osr == 1)
-bool stream_supported(int sf, const DemodArgs& a);
-cudaError_t launch_symbols_stream(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
-// demod_packet.cu: one CTA per packet, scan -> estimator -> symbols in one launch (SF 7..12, osr == 1)
-bool packet_supported(int sf, const DemodArgs& a);
-cudaError_t launch_demod_packet(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
-// demod_cert.cu: the default -- pipeline per packet, throughput FFT with a per-window proof that its argmax is the
-// reference's, exact replay of the windows that cannot be proven (SF 7..12, osr == 1)
+// demod_cert.cu: pipeline per packet, throughput FFT with a per-window proof that its argmax is the reference's, exact
+// replay of the windows that cannot be proven (SF 7..12, osr == 1); F_EXACT = the same kernel, every window replayed
 bool cert_supported(int sf, const DemodArgs& a);
 cudaError_t launch_demod_cert(int sf, const DemodArgs& a, int sm_count, cudaStream_t stream);
 

@@ -1,5 +1,5 @@
-// stream_common.cuh -- pieces shared by the streaming kernels (demod_stream.cu: data symbols only;
-// demod_packet.cu / demod_cert.cu: max-abs + estimator + sync + data symbols in one launch).
+// stream_common.cuh -- pieces shared by the streaming kernels (demod_cert.cu, demod_lean.cu): the exact transform on a
+// shared-memory exchange buffer, the reference's per-sample chain, window fetches with cp.async.bulk.
 #pragma once
 #include "demod_device.cuh"
 #include "stream_ptx.cuh"
