@@ -459,6 +459,55 @@ def test_lean_route_hands_over_what_it_cannot_settle(phy, lp, oracle, sf):
             assert np.array_equal(out["symbols"][p, :n].cpu().numpy(), s_ref) and int(out["sync"][p]) == sync
 
 
+@pytest.mark.parametrize("sf", [7, 9, 10, 12])
+def test_lean_route_many_rounds_gain_changes_and_long_packets(phy, lp, oracle, sf):
+    """More packets than the streaming kernel has warps, so every warp goes through several rounds and its max-abs
+    prediction meets every transition (quiet -> loud -> louder -> quiet: re-estimates with the true scale); tiny batches
+    (fewer packets than warps of one CTA); and a packet of 600 symbols (no staging limit on that route).  The whole batch
+    equals the exact-replay arm on the GPU, a sample of it equals the oracle."""
+    import torch
+    rng = np.random.default_rng(3100 + sf)
+    N = 1 << sf
+    S = 4
+    down = oracle.gen_chirp(N, 1, N, 0.0, True, 1.0, 0.0, 1.0)[0]
+    props = torch.cuda.get_device_properties(0)
+    n_warps = props.multi_processor_count * 3 * 8
+    P = (2 * n_warps + 17) if sf <= 9 else 1200
+    base = []
+    for _ in range(8):
+        syms = rng.integers(0, N, S - 2).astype(np.uint16)
+        base.append((oracle.lora_modulate(syms, sf, 1, 125000, 1.0, 0x12).reshape(-1, N) * down[None, :]).astype(np.complex64).ravel())
+    base = np.stack(base)
+    gains = np.array([0.5, 3.0, 7.25, 0.9, 1.0, 2.0, 2.0, 0.25], np.float32)
+    # gain class changes from round to round for every warp: packet p of round r gets gains[(p + r) % 8]
+    pick = rng.integers(0, 8, P)
+    g = gains[(np.arange(P) + np.arange(P) // max(1, n_warps)) % 8]
+    iq = (base[pick] * g[:, None]).astype(np.complex64)
+    d = to_dev(phy, iq)
+    cfg, cfg_x = lp.make_cfg(sf), lp.make_cfg(sf, flags=lp.F_EXACT)
+    c0 = phy.cert_stats()
+    out = {k: v.clone() for k, v in phy.demodulate_batch(cfg, d).items()}
+    c1 = phy.cert_stats()
+    ref = phy.demodulate_batch(cfg_x, d)
+    phy.synchronize()
+    for k in ("symbols", "sync", "status"):
+        assert torch.equal(out[k], ref[k]), k
+    for k in ("cfo", "time_offset"):
+        assert torch.equal(out[k].view(torch.int32), ref[k].view(torch.int32)), k
+    assert c1[4] - c0[4] >= P * S * 9 // 10 and c1[2] - c0[2] > 0, (c0, c1)      # pruned windows; re-estimates happened
+    for p in list(range(0, P, max(1, P // 40)))[:40]:
+        n, s_ref, sync, cfo, to = oracle.lora_demodulate(iq[p], sf, 1, 0, 1)
+        assert int(out["status"][p]) == n and np.array_equal(out["symbols"][p, :n].cpu().numpy(), s_ref)
+        assert bits(out["cfo"][p:p + 1].cpu().numpy())[0] == bits(np.array([cfo], np.float32))[0]
+    for small in (1, 3, 7):
+        check_legacy(phy, lp, oracle, iq[:small].copy(), sf, 1, 0)
+    if sf in (7, 10):
+        L = 600
+        syms = rng.integers(0, N, L - 2).astype(np.uint16)
+        long_pkt = (oracle.lora_modulate(syms, sf, 1, 125000, 0.8, 0x12).reshape(-1, N) * down[None, :]).astype(np.complex64).ravel()
+        check_legacy(phy, lp, oracle, np.stack([long_pkt, long_pkt[::-1].copy() * np.complex64(0.5)]), sf, 1, 0)
+
+
 def test_every_kernel_family_small_cases():
     """tools/sanitize_driver.py (written for compute-sanitizer, which is closed on this pool) as a plain run: every kernel
     family on ragged / oversized / odd-aligned / loud / noise-only inputs must complete without a CUDA error."""
