@@ -43,6 +43,9 @@ namespace lk {
 #ifndef LEAN_CTAS_SF7
 #define LEAN_CTAS_SF7 3
 #endif
+#ifndef LEAN_PAIR_SF7
+#define LEAN_PAIR_SF7 1                       // SF7: one exact estimator pass serves two jobs (A/B knob)
+#endif
 #ifndef LEAN_CTA
 #define LEAN_CTA 256
 #endif
@@ -62,6 +65,8 @@ struct LeanCfg {
     static constexpr bool WIDE = SF >= 10;                                // a window spans R > 1 chunks (else GD windows per chunk)
     static constexpr int N = 1 << SF, T = N / 16, R = WIDE ? N / LEAN_CHUNK : 1;   // R = T / 32 accumulators per lane
     static constexpr int GD = WIDE ? 1 : LEAN_CHUNK / N;                  // windows per chunk (SF7: 4, SF8: 2, SF9: 1)
+    static constexpr int JOBS = (LEAN_PAIR_SF7 && SF == 7) ? 2 : 1;       // packets per warp and round: SF7's estimator holds four
+                                                                          // windows side by side = the two symbols of TWO packets
     static constexpr int CP = 16 / R;                                     // terms per accumulator and chunk
     static constexpr int LV = CP == 8 ? 3 : CP == 4 ? 2 : 1;              // halving levels inside a chunk
     static constexpr int CTA = WIDE ? LEAN_CTA : LEAN_CTA_NARROW, CTAS = WIDE ? LEAN_CTAS_PER_SM : (SF == 7 ? LEAN_CTAS_SF7 : LEAN_CTAS_NARROW);
@@ -77,8 +82,8 @@ struct LeanCfg {
     static constexpr size_t hp_off = w16_off + 16 * sizeof(cf);                                        // per warp: [k0][4] powers of h
     static constexpr size_t g32_off = hp_off + (size_t)WARPS * 64 * sizeof(cf);                        // per warp: G32^j, j < 8
     static constexpr size_t cell_off = g32_off + (size_t)WARPS * 8 * sizeof(cf);                       // per warp: LeanTeamCell (48 B)
-    static constexpr size_t est_off = cell_off + (size_t)WARPS * 48;                                   // per team: two LeanEst (16 B slots)
-    static constexpr size_t red_off = est_off + (size_t)WARPS * 2 * 16;                                // Peak[8] of the exact estimator
+    static constexpr size_t est_off = cell_off + (size_t)WARPS * JOBS * 48;                            // per team: LeanEst[4] + LeanRes[2]
+    static constexpr size_t red_off = est_off + (size_t)WARPS * 128;                                   // Peak[8] of the exact estimator
     static constexpr size_t bytes = red_off + 8 * 8;
 };
 
@@ -93,7 +98,8 @@ struct LeanTeamCell {       // one per warp: what the team's estimator phase han
     float pred;                                             // max-abs the next estimate should assume (the warp's last packet's)
     int pad[3];
 };
-struct LeanEst { int idx; float fi; float phase; };
+struct LeanEst { int idx; float fi; float phase; int pad; };
+struct LeanRes { float cfo, toff, rate; int t_off; };       // a paired pass leaves each job's result here
 
 template <int SF>
 __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lean_kernel(const DemodArgs a)
@@ -122,8 +128,10 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
     cf* w16 = reinterpret_cast<cf*>(smem_raw + C::w16_off);
     cf* hp = reinterpret_cast<cf*>(smem_raw + C::hp_off) + warp * 64;
     cf* g32 = reinterpret_cast<cf*>(smem_raw + C::g32_off) + warp * 8;
-    LeanTeamCell* cells = reinterpret_cast<LeanTeamCell*>(smem_raw + C::cell_off) + team * TW;
-    LeanEst* est = reinterpret_cast<LeanEst*>(smem_raw + C::est_off) + team * 2;
+    constexpr int JOBS = C::JOBS;
+    LeanTeamCell* cells = reinterpret_cast<LeanTeamCell*>(smem_raw + C::cell_off) + team * TW * JOBS;
+    LeanEst* est = reinterpret_cast<LeanEst*>(smem_raw + C::est_off + (size_t)(WIDE ? team * TW : warp) * 128);
+    LeanRes* res = reinterpret_cast<LeanRes*>(est + 4);
     Peak* red = reinterpret_cast<Peak*>(smem_raw + C::red_off);
 
     if (l == 0) {
@@ -164,9 +172,10 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
     unsigned st_pruned = 0, st_flagged = 0, st_est2 = 0;
     const uint32_t n_warps = gridDim.x * C::WARPS;
     const uint32_t gw0 = blockIdx.x * C::WARPS + (uint32_t)(team * TW);            // the team's first warp, grid-wide
-    LeanTeamCell* mycell = &cells[wt];
     float pred_max = 0.0f;                                     // max-abs of this warp's previous packet
-    int vpid = -1; float vmax = 0.0f, vrate = 0.0f; int vtoff = 0;                 // this warp's pending re-estimate
+    int vpid[JOBS]; float vmax[JOBS], vrate[JOBS]; int vtoff[JOBS];                // this warp's pending re-estimates
+#pragma unroll
+    for (int j = 0; j < JOBS; ++j) { vpid[j] = -1; vmax[j] = 0.0f; vrate[j] = 0.0f; vtoff[j] = 0; }
 
     // The exact two-symbol estimator of packet `pid` with the samples scaled by 1/use_max when use_max > 1
     // (LoRaDemod.cpp:61-139), by the whole team; thread 0 of the team gets cfo / time_offset / rate / t_off.
@@ -233,15 +242,139 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
         }
     };
 
+    // SF7 (T = 8: four windows side by side): ONE exact pass for two jobs -- groups 0, 1 hold the two symbols of job 0,
+    // groups 2, 3 those of job 1; each job's first thread leaves cfo / time_offset / rate / t_off in res[job].
+    auto estimate_pair = [&](uint32_t pid0, float max0, bool on0, uint32_t pid1, float max1, bool on1) {
+        const int job = grp >> 1, s = grp & 1;
+        const bool live = job ? on1 : on0;
+        const cf* pkt = a.iq + (size_t)(job ? pid1 : pid0) * a.packet_stride;
+        const float use_max = job ? max1 : max0;
+        const bool norm = use_max > 1.0f;
+        const float scale = norm ? __fdiv_rn(1.0f, use_max) : 1.0f;
+        cf v[P::R];
+#pragma unroll
+        for (int c = 0; c < P::R; ++c) {
+            cf x = fx::mk(0.0f, 0.0f);
+            if (live) {
+                x = ldg_cf(pkt + (size_t)s * N + tid + T * c);
+                if (norm) x = fx::cscale(x, scale);                                    // LoRaDemod.cpp:75-77
+            }
+            v[c] = x;
+        }
+        fft_inplace<SF, true>(v, tid, a.tw, a.ct, ex);
+        const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
+        group_sync<T>();
+#pragma unroll
+        for (int r = 0; r < P::R; ++r) ex[P::bin_of_reg(tid, r)] = v[r];
+        group_sync<T>();
+        if (tid == 0 && live) {
+            LeanEst e; e.idx = 0; e.fi = 0.0f; e.phase = 0.0f; e.pad = 0;
+            cf best_bin = fx::mk(0.0f, 0.0f);
+            if (pk.val > 0.0f) {
+                const float fundamental = __fsqrt_rn(pk.val);
+                const cf lft = ex[pk.idx > 0 ? pk.idx - 1 : N - 1];
+                const cf rgt = ex[pk.idx < N - 1 ? pk.idx + 1 : 0];
+                const float left = gm::hypotf_g(lft.x, lft.y), right = gm::hypotf_g(rgt.x, rgt.y);
+                const double demon = (2.0 * (double)fundamental) - (double)right - (double)left;
+                e.fi = (demon == 0.0) ? 0.0f : (float)(0.5 * (double)fx::fsub(right, left) / demon);
+                e.idx = pk.idx;
+                best_bin = ex[pk.idx];
+            }
+            e.phase = gm::atan2f_g(best_bin.y, best_bin.x);
+            est[grp] = e;
+        }
+        group_sync<T>();
+        if (tid == 0 && s == 0 && live) {                      // LoRaDemod.cpp:126-139, one thread per job
+            const float PI_F = 3.14159265358979323846f;
+            const LeanEst e0 = est[2 * job], e1 = est[2 * job + 1];
+            float sum_index = fx::fadd(0.0f, fx::fadd((float)e0.idx, e0.fi));
+            sum_index = fx::fadd(sum_index, fx::fadd((float)e1.idx, e1.fi));
+            float dd = fx::fsub(e1.phase, e0.phase);
+            while (dd > PI_F) dd = fx::fsub(dd, 2.0f * PI_F);
+            while (dd < -PI_F) dd = fx::fadd(dd, 2.0f * PI_F);
+            const float phase_diff = fx::fadd(0.0f, dd);
+            const float avg_index = __fdiv_rn(sum_index, 2.0f);
+            const float cfo_coarse = __fdiv_rn(avg_index, (float)N);
+            const float cfo_fine = __fdiv_rn(__fdiv_rn(phase_diff, 1.0f), fx::fmul(2.0f * PI_F, (float)N));
+            LeanRes r;
+            r.cfo = fx::fadd(cfo_coarse, cfo_fine);
+            const float frac = fx::fsub(avg_index, floorf(fx::fadd(avg_index, 0.5f)));
+            const float avg_t = __fdiv_rn(0.0f, 2.0f);
+            r.toff = fx::fsub(avg_t, fx::fmul(frac, (float)N));
+            r.t_off = (int)roundf(r.toff);
+            r.rate = __fdiv_rn(fx::fmul(-2.0f * PI_F, r.cfo), (float)N);
+            res[job] = r;
+        }
+        group_sync<T>();
+    };
+
 #pragma unroll 1
     for (uint32_t round = 0;; ++round) {
         // ---- estimator phase (the team's ring is idle): pending re-estimates, then the packets about to be streamed ------
         if (l == 0) {
-            LeanTeamCell& c = cells[wt];
-            c.vpid = vpid; c.vmax = vmax; c.vrate = vrate; c.vtoff = vtoff; c.pred = pred_max;
+#pragma unroll
+            for (int j = 0; j < JOBS; ++j) {
+                LeanTeamCell& c = cells[wt * JOBS + j];
+                c.vpid = vpid[j]; c.vmax = vmax[j]; c.vrate = vrate[j]; c.vtoff = vtoff[j]; c.pred = pred_max;
+            }
         }
         group_sync<T>();
         bool any = false;
+        if constexpr (JOBS == 2) {
+            // SF7: up to four jobs (two re-estimates, two new packets), two per exact pass
+            uint32_t jp[4]; float jm[4]; int jk[4];            // packet, max-abs to assume, kind: 0/1 = re-estimate of cell, 2/3 = new packet of cell
+            int nj = 0;
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                if (cells[j].vpid >= 0) { jp[nj] = (uint32_t)cells[j].vpid; jm[nj] = cells[j].vmax; jk[nj] = j; ++nj; }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const unsigned long long pm = (unsigned long long)gw0 + ((unsigned long long)round * 2 + (unsigned)j) * n_warps;
+                int ok = -1;
+                if (pm < a.n_packets) {
+                    const uint32_t pid = (uint32_t)pm;
+                    const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
+                    const uint32_t count = a.sample_counts ? min(a.sample_counts[pid], a.samples_per_packet) : a.samples_per_packet;
+                    const uint32_t total = count / (uint32_t)N;
+                    const bool shape = total >= 2 && count == total * (uint32_t)N && (reinterpret_cast<uintptr_t>(pkt) & 15) == 0 &&
+                                       cells[j].pred < 3.0e38f;
+                    ok = shape ? 1 : 0;
+                    if (shape) { jp[nj] = pid; jm[nj] = cells[j].pred; jk[nj] = 2 + j; ++nj; }
+                    any = true;
+                }
+                if (lead) cells[j].ok = ok;
+            }
+            if (nj) any = true;
+#pragma unroll 1
+            for (int b = 0; b < nj; b += 2) {
+                const bool two = b + 1 < nj;
+                estimate_pair(jp[b], jm[b], true, two ? jp[b + 1] : 0u, two ? jm[b + 1] : 0.0f, two);
+                if (lead) {
+                    for (int q = 0; q < (two ? 2 : 1); ++q) {
+                        const LeanRes r = res[q];
+                        const int kind = jk[b + q];
+                        const uint32_t pid = jp[b + q];
+                        LeanTeamCell& c = cells[kind & 1];
+                        if (kind < 2) {
+                            // the streamed symbols stand iff the window bases and (within the certified tolerance) the rate do
+                            const bool same = r.t_off == c.vtoff && fabsf(fx::fsub(r.rate, c.vrate)) * (float)N <= 64.0f * LEAN_U;
+                            if (same) {
+                                if (a.cfo) a.cfo[pid] = r.cfo;
+                                if (a.time_offset) a.time_offset[pid] = r.toff;
+                            } else {
+                                a.flagged[pid] = 1; ++st_flagged;
+                            }
+                            ++st_est2;
+                        } else {
+                            if (a.cfo) a.cfo[pid] = r.cfo;
+                            if (a.time_offset) a.time_offset[pid] = r.toff;
+                            c.rate = r.rate; c.t_off = r.t_off; c.used_max = c.pred;
+                        }
+                    }
+                }
+                group_sync<T>();
+            }
+        } else
 #pragma unroll 1
         for (int m = 0; m < TW; ++m) {
             const int vp = cells[m].vpid;
@@ -290,11 +423,16 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
         ptx::fence_proxy_async();                              // exchange-buffer stores precede the bulk copies into the ring
         group_sync<T>();
         if (!any) break;
-        vpid = -1;
+#pragma unroll
+        for (int j = 0; j < JOBS; ++j) vpid[j] = -1;
 
-        // ---- stream phase: every warp its own packet -----------------------------------------------------------------------
-        const unsigned long long pme = (unsigned long long)blockIdx.x * C::WARPS + (unsigned)warp + (unsigned long long)round * n_warps;
-        const LeanTeamCell mine = cells[wt];
+        // ---- stream phase: every warp its own packet(s) --------------------------------------------------------------------
+#pragma unroll 1
+        for (int job = 0; job < JOBS; ++job) {
+        const unsigned long long pme = (unsigned long long)blockIdx.x * C::WARPS + (unsigned)warp +
+                                       ((unsigned long long)round * JOBS + (unsigned)job) * n_warps;
+        LeanTeamCell* mycell = &cells[wt * JOBS + job];
+        const LeanTeamCell mine = *mycell;
         if (mine.ok >= 0 && pme < a.n_packets) {
             const uint32_t pid = (uint32_t)pme;
             const cf* pkt = a.iq + (size_t)pid * a.packet_stride;
@@ -627,10 +765,11 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 }
                 // the estimate assumed max-abs used_max (LoRaDemod.cpp:61-78): right iff the packet's own max says the same
                 const bool hit = (mmax > 1.0f) ? (mmax == mine.used_max) : !(mine.used_max > 1.0f);
-                if (!hit) { vpid = (int)pid; vmax = mmax; vrate = rate; vtoff = mine.t_off; }
+                if (!hit) { vpid[job] = (int)pid; vmax[job] = mmax; vrate[job] = rate; vtoff[job] = mine.t_off; }
                 pred_max = mmax;
             }
         }
+        }                                                      // jobs of the round
     }
     if (a.cert_stats && l == 0) {
         if (st_pruned) { atomicAdd(a.cert_stats + 0, (unsigned long long)st_pruned); atomicAdd(a.cert_stats + 4, (unsigned long long)st_pruned); }
