@@ -321,12 +321,32 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
         group_sync<T>();
         bool any = false;
         if constexpr (JOBS == 2) {
-            // SF7: up to four jobs (two re-estimates, two new packets), two per exact pass
-            uint32_t jp[4]; float jm[4]; int jk[4];            // packet, max-abs to assume, kind: 0/1 = re-estimate of cell, 2/3 = new packet of cell
-            int nj = 0;
+            // SF7: two re-estimates in one exact pass (when any is pending), the two new packets in another
+            const int v0 = cells[0].vpid, v1 = cells[1].vpid;
+            if (v0 >= 0 || v1 >= 0) {
+                any = true;
+                estimate_pair((uint32_t)max(v0, 0), cells[0].vmax, v0 >= 0, (uint32_t)max(v1, 0), cells[1].vmax, v1 >= 0);
+                if (lead) {
 #pragma unroll
-            for (int j = 0; j < 2; ++j)
-                if (cells[j].vpid >= 0) { jp[nj] = (uint32_t)cells[j].vpid; jm[nj] = cells[j].vmax; jk[nj] = j; ++nj; }
+                    for (int q = 0; q < 2; ++q) {
+                        const LeanTeamCell& c = cells[q];
+                        if (c.vpid < 0) continue;
+                        const LeanRes r = res[q];
+                        // the streamed symbols stand iff the window bases and (within the certified tolerance) the rate do
+                        const bool same = r.t_off == c.vtoff && fabsf(fx::fsub(r.rate, c.vrate)) * (float)N <= 64.0f * LEAN_U;
+                        if (same) {
+                            if (a.cfo) a.cfo[c.vpid] = r.cfo;
+                            if (a.time_offset) a.time_offset[c.vpid] = r.toff;
+                        } else {
+                            a.flagged[c.vpid] = 1; ++st_flagged;
+                        }
+                        ++st_est2;
+                    }
+                }
+                group_sync<T>();
+            }
+            uint32_t np[2] = { 0u, 0u };
+            bool non[2] = { false, false };
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 const unsigned long long pm = (unsigned long long)gw0 + ((unsigned long long)round * 2 + (unsigned)j) * n_warps;
@@ -339,37 +359,22 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     const bool shape = total >= 2 && count == total * (uint32_t)N && (reinterpret_cast<uintptr_t>(pkt) & 15) == 0 &&
                                        cells[j].pred < 3.0e38f;
                     ok = shape ? 1 : 0;
-                    if (shape) { jp[nj] = pid; jm[nj] = cells[j].pred; jk[nj] = 2 + j; ++nj; }
+                    np[j] = pid; non[j] = shape;
                     any = true;
                 }
                 if (lead) cells[j].ok = ok;
             }
-            if (nj) any = true;
-#pragma unroll 1
-            for (int b = 0; b < nj; b += 2) {
-                const bool two = b + 1 < nj;
-                estimate_pair(jp[b], jm[b], true, two ? jp[b + 1] : 0u, two ? jm[b + 1] : 0.0f, two);
+            if (non[0] || non[1]) {
+                estimate_pair(np[0], cells[0].pred, non[0], np[1], cells[1].pred, non[1]);
                 if (lead) {
-                    for (int q = 0; q < (two ? 2 : 1); ++q) {
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        if (!non[q]) continue;
                         const LeanRes r = res[q];
-                        const int kind = jk[b + q];
-                        const uint32_t pid = jp[b + q];
-                        LeanTeamCell& c = cells[kind & 1];
-                        if (kind < 2) {
-                            // the streamed symbols stand iff the window bases and (within the certified tolerance) the rate do
-                            const bool same = r.t_off == c.vtoff && fabsf(fx::fsub(r.rate, c.vrate)) * (float)N <= 64.0f * LEAN_U;
-                            if (same) {
-                                if (a.cfo) a.cfo[pid] = r.cfo;
-                                if (a.time_offset) a.time_offset[pid] = r.toff;
-                            } else {
-                                a.flagged[pid] = 1; ++st_flagged;
-                            }
-                            ++st_est2;
-                        } else {
-                            if (a.cfo) a.cfo[pid] = r.cfo;
-                            if (a.time_offset) a.time_offset[pid] = r.toff;
-                            c.rate = r.rate; c.t_off = r.t_off; c.used_max = c.pred;
-                        }
+                        LeanTeamCell& c = cells[q];
+                        if (a.cfo) a.cfo[np[q]] = r.cfo;
+                        if (a.time_offset) a.time_offset[np[q]] = r.toff;
+                        c.rate = r.rate; c.t_off = r.t_off; c.used_max = c.pred;
                     }
                 }
                 group_sync<T>();
