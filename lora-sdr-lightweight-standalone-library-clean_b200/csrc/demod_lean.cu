@@ -1,30 +1,34 @@
-// demod_lean.cu -- first pass of the three-launch demodulator for SF10-12 (lora_demodulate, LoRaDemod.cpp:50-197):
-// the pruned transform of fft_prune.cuh as a STREAMING kernel, one warp per packet, 4 KB of IQ per step.
+// demod_lean.cu -- the default demodulator for pre-dechirped IQ (lora_demodulate, LoRaDemod.cpp:50-197; SF7-12, osr 1,
+// no downchirp / window tables): ONE WARP PER PACKET, the packet streamed once in 4 KB steps, every window settled by the
+// pruned transform of fft_prune.cuh and the tier-1 Parseval test of demod_cert.cu.  What it cannot settle it FLAGS for
+// demod_cert_kernel, which api.cu launches right after over the flagged packets only.
 //
-// Why a kernel of its own: in demod_cert.cu a 1024..4096-point window is held by 2..8 warps (16 samples per thread, the
-// layout its full transform needs), so every window costs barriers and only 2-8 windows are in flight per SM; that kernel
-// is latency-bound at ~0.7 of the HBM rate for SF11 / SF12.  The pruned transform does not need the window in registers:
-// with f_c = F_tid G^c ("geometric variant") the class-k0 output of pass 0 is a POLYNOMIAL in the raw samples,
-//     V_t[k0] = F_t * sum_c r_{t + T c} h^c,   h = G W16^k0,  T = N / 16 = 32 R,
-// which a warp can accumulate while the window streams past in R = N / 512 chunks of 512 samples: lane l keeps R complex
-// accumulators (t = l + 32 j), each chunk adds 16 / R terms to each of them (halving levels inside the chunk, one
-// multiply-add with the running power h^(c0) to join).  At the end of the window the lane holds the R inputs of the
-// cross-warp stage of fft_prune.cuh itself: an R-point DFT in registers, the W_T twiddles, R lane transforms, top bin.
-// No shared-memory exchange, no barrier, 2-3 x 4 KB of ring per warp.
+// Why a kernel of its own: in demod_cert.cu a window is held in registers (16 samples per thread: the layout its full
+// transform needs) -- 2..8 warps, four to six barriers and a 9-35 KB slot per window at SF10-12, 128 registers and a
+// slow path the hot loop pays for at every SF.  The pruned transform needs none of that.  With f_c = F_t G^c (DESIGN.md,
+// "geometric variant") the class-k0 output of pass 0 is a POLYNOMIAL in the raw samples,
+//     V_t[k0] = F_t * sum_c r_{t + T c} h^c,   h = G W16^k0,  T = N / 16,
+//   SF7-9   T <= 32: a 4 KB step is GD = 512 / N whole windows side by side (4 / 2 / 1), 16 samples per thread, four
+//           halving levels, then the T-point transform across the lanes by shfl.xor;
+//   SF10-12 T = 32 R: a window is R = N / 512 steps; lane l keeps R complex accumulators (t = l + 32 j), each step adds
+//           16 / R terms to each (halving levels inside the step, one multiply-add with h^(c0) from the table's powers of
+//           two to join).  At the end of the window the lane holds the R inputs of fft_prune.cuh's cross-warp stage: an
+//           R-point DFT in registers, the W_T twiddles, R lane transforms, top bin.
+// No shared-memory exchange, no barrier, no window ever resident; 2 x 4 KB of ring per warp, one cp.async.bulk per step.
 //
-// Division of labour (api.cu):
-//   1. prepass_kernel (demod.cu, unit_scale): the exact two-symbol estimator -> cfo, time_offset, rate, t_off per packet.
-//      It assumes the packet needs no 1/max normalisation (LoRaDemod.cpp:61-78), which only this pass can check.
-//   2. THIS kernel: every window of every "regular" packet (t_off == 0, whole symbols, 16-byte aligned, finite) through
-//      the pruned transform and the tier-1 Parseval test of demod_cert.cu, tracking the max-abs.  The first window that
-//      is refused -- or any irregularity -- FLAGS the packet (1) and abandons it.  A packet settled completely whose
-//      max-abs exceeds 1 is flagged 2: its symbols stand (the decisions are scale-invariant) if the estimator, redone
-//      with the true scale, keeps t_off and moves the rate by no more than the tolerance the proof budgets.
-//   3. demod_cert_kernel over the flagged packets only: flag 1 = the whole packet again (full transform, tier 2, exact
-//      replay, normalisation), every output rewritten; flag 2 = the two exact estimator symbols with the true scale ->
-//      cfo / time_offset, and the rate check (a failed check turns it into flag 1).
+// Per round of packets:
+//   estimator phase (the ring is idle and doubles as the exact transform's exchange buffer): the exact two-symbol
+//     estimator (LoRaDemod.cpp:80-139: exact-order FFT of fft_exact.cuh, first-max, fIndex, atan2f) -> cfo, time_offset,
+//     rate, t_off bit for bit.  A 2^SF-point exact transform needs T threads: teams of T / 32 warps at SF10-12 (packet
+//     after packet of the team's members), the warp itself at SF7-9 (SF7: four windows side by side = two jobs per
+//     pass, so a round is two packets per warp).  The 1/max normalisation (LoRaDemod.cpp:61-78) is PREDICTED from the
+//     warp's previous packet; the stream tracks the true max-abs, and a miss is re-estimated with the true scale in the
+//     next estimator phase: the symbols (scale-invariant decisions) stand iff t_off is unchanged and the rate moved by
+//     no more than the tolerance the certificate budgets, else the packet is flagged.
+//   stream phase: every window as above; the first refused window (noise, weak signal, NaN / Inf), an irregular packet
+//     (t_off != 0, partial symbol, 8-byte alignment, non-finite max) flags the packet and abandons it.
 // Symbols, sync word, status, cfo, time_offset are bit-exact either way: accepted windows carry demod_cert.cu's proof
-// (same constants, same budget: DESIGN.md section 5), everything else is the old path.
+// (same constants, same budget: DESIGN.md section 5), everything else is that kernel.
 #include <atomic>
 #include "stream_common.cuh"
 #include "fft_fast.cuh"
