@@ -15,7 +15,7 @@
 //                     S = sqrt(N * sum|u_i|^2) >= sum|u_i| every bin obeys | |X^_k| - |Y_k| | <= K*S, K = u*(C0 +
 //                     |start| + 2|rate|N), u = 2^-24 (DESIGN.md derives C0 from kissfft's stage count, its float twiddle
 //                     table, the libm bounds and our own rounding).  The window is accepted iff the top |Y|^2 beats the
-//                     second by more than that margin (tier 1: the top bin holds > 3/4 of N*E, by Parseval nothing else
+//                     second by more than that margin (tier 1: the top bin holds > 9/16 of N*E, by Parseval nothing else
 //                     can come near; tier 2: the true second maximum).  Then X^ has the same strict, unique maximum.
 //   fallback          windows that fail -- ties, noise-only windows with close bins, NaN / Inf / denormal input -- are
 //                     replayed through round 1's exact chain (stream_common.cuh) at the end of the packet, same launch.
@@ -560,7 +560,7 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
             const float start_max = fabsf(rate) * ((float)total * (float)N + fabsf((float)t_off)) * 1.01f;
             const float Kc = CERT_U * (CERT_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
             const float c2 = 16.32f * Kc * Kc * (float)N;
-            const float tier1 = (Kc < 0.0078125f) ? 0.75f * (float)N : __int_as_float(0x7f800000);
+            const float tier1 = (Kc < 0.0078125f) ? fp::TIER1 * (float)N : __int_as_float(0x7f800000);
 
             // ---- C units: the walk ------------------------------------------------------------------------------
             // Loop bookkeeping is kept out of the issue slots: the window slot, its mbarrier and the prefetch target are
@@ -980,7 +980,7 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
                     for (int k = 1; k < T / 32; ++k) { kmax = max(kmax, redc[w0 + k].key); en += redc[w0 + k].e; }
                 }
                 const float q1 = __uint_as_float(kmax & ~15u);
-                // tier 1: the top bin holds more than 3/4 of N*E (Parseval: every other bin is below half its modulus)
+                // tier 1: the top bin holds more than 9/16 of N*E (Parseval: every other bin is below half its modulus)
                 bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
 #if defined(CERT_ABLATE)
                 cert = true;

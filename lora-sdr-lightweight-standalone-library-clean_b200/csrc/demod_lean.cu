@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
             const float start_max = fabsf(rate) * ((float)total * (float)N) * 1.01f;
             const float Kc = LEAN_U * (LEAN_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
             bool bad = !(mine.ok == 1 && mine.t_off == 0 && Kc < 0.0078125f);         // tier 1 available (demod_cert.cu)
-            const float tier1 = 0.75f * (float)N;
+            const float tier1 = fp::TIER1 * (float)N;
             float mmax = 0.0f;
             int sw0 = 0, sw1 = 0;
             if constexpr (WIDE) {
@@ -613,7 +613,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     const int idx = __shfl_sync(0xffffffffu, k0 + 16 * (kab + R * (int)(__brev((unsigned)l) >> 27)), src);
 #pragma unroll
                     for (int off = 16; off > 0; off >>= 1) mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, off));
-                    // accepted iff the top bin holds 3/4 of N E (tier 1 of demod_cert.cu).  The decision does not depend on
+                    // accepted iff the top bin holds 9/16 of N E (tier 1 of demod_cert.cu).  The decision does not depend on
                     // the scale the estimate assumed (positive, finite; the rate it changes is re-checked); NaN samples are
                     // invisible to fmaxf but poison E, an infinite max wipes the packet in the reference.  E is taken on the
                     // raw samples: an upper bound of the scaled energy (scale <= 1) is all the test needs... but q1 is raw

@@ -10,7 +10,7 @@
 //               R-point DFT across warps, c_l = W_T^{l ka} sum_w u_{l+32w} W_R^{w ka}, then the 32-lane transform:
 //               lane l of warp ka ends with bin k' = ka + R * bitrev5(l).
 // That is N/16 bins for 1/16 of the work of passes 1..  The certificate does not need the other bins: tier 1 accepts
-// a window iff the top bin found holds more than 3/4 of N*E, and by Parseval no bin of the exact transform -- computed
+// a window iff the top bin found holds more than 9/16 of N*E, and by Parseval no bin of the exact transform -- computed
 // here or not -- can then come near it.  It also makes ANY choice of k0 safe: a wrong class
 // cannot pass the test.  Windows that fail (noise, weak signal) take the full transform of fft_fast.cuh.
 //
@@ -21,6 +21,15 @@
 namespace fp {
 
 using ff::cf;
+
+// Tier 1 of the certificate (demod_cert.cu, demod_lean.cu): the top bin found is accepted iff q1 > TIER1 * N * E.
+// Parseval on the exact transform Z of the true inputs: every other bin has |Z_k|^2 <= S^2 - |Z_top|^2, S^2 = N E.
+// With y = sqrt(q1) / S >= 0.75, our error K_o S and the reference's K_r S (K_o + K_r = K < 2^-7, the kernels check it):
+// z = |Z_top| / S >= 0.742, the reference computes |X^_top| >= (z - K_r) S >= 0.734 S and every other
+// |X^_k| <= (sqrt(1 - z^2) + K_r) S <= 0.679 S: a strict, unique maximum with a margin of 0.05 S.  (The first version
+// of the test asked for 3/4 of the energy; 9/16 keeps windows down to ~1 dB per-sample SNR and carrier corrections
+// up to 0.4 bin on the cheap path.)
+constexpr float TIER1 = 0.5625f;
 
 template <int SF>
 struct Prune {

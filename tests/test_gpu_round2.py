@@ -367,7 +367,7 @@ def test_certified_fallbacks_fire(phy, lp, oracle):
 def test_pruned_transform_policy_over_snr_and_sync_words(phy, lp, oracle, sf):
     """The pruned transform (one bin class, accepted by the Parseval test) and its hand-over to the full transform:
     packets whose per-sample SNR steps from clean to -6 dB and back, sync words that put the reference's carrier
-    correction anywhere between 0 and 1 bin (0x88: half a bin, where the top bin holds less than 3/4 of the energy and
+    correction anywhere between 0 and 1 bin (0x88: half a bin, where the top bin holds less than 9/16 of the energy and
     the pruned test must refuse), two tones in different bin classes.  Every packet equals the oracle; the counters
     show both outcomes."""
     rng = np.random.default_rng(900 + sf)
