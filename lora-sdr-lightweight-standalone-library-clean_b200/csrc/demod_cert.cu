@@ -1049,13 +1049,30 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
 
             // ---- verify the trusted max against the samples actually walked -----------------------------------------
             if (known) break;
-            if (t_off != 0 || count != total * (uint32_t)N || cany<DT>(suspicious)) {
-                m = cert_scan_max<DT>(pkt, count, lane, redf);       // shifted windows / partial tail / NaN: the reference's own scan
-            } else if (DT <= 32) {
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+            if (cany<DT>(suspicious)) {
+                m = cert_scan_max<DT>(pkt, count, lane, redf);       // NaN somewhere: the reference's own comparison chain
             } else {
-                m = group_max<DT>(m, redf);
+                if (DT <= 32) {
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+                } else {
+                    m = group_max<DT>(m, redf);
+                }
+                // Shifted windows (LoRaDemod.cpp:143-150) and a partial last symbol leave a few samples the walk never
+                // read: with t_off > 0 the windows cover [t_off, total N) (the last ones stay unshifted), with t_off < 0
+                // [0, total N - |t_off|).  Only those ends are scanned (a superset is harmless for a maximum) -- a full
+                // second pass over the packet doubled the HBM traffic of every noisy packet.
+                const uint32_t whole = total * (uint32_t)N;
+                if (t_off > 0) {
+                    const uint32_t n0 = min((uint32_t)t_off, count);
+                    m = fmaxf(m, cert_scan_max<DT>(pkt, n0, lane, redf));
+                    if (count > whole) m = fmaxf(m, cert_scan_max<DT>(pkt + whole, count - whole, lane, redf));
+                } else if (t_off < 0) {
+                    const uint32_t a0 = (uint32_t)(-t_off), lo = whole > a0 ? whole - a0 : 0u;
+                    m = fmaxf(m, cert_scan_max<DT>(pkt + lo, count - lo, lane, redf));
+                } else if (count != whole) {
+                    m = fmaxf(m, cert_scan_max<DT>(pkt + whole, count - whole, lane, redf));
+                }
             }
             const bool ok = (m > 1.0f) ? (m == use_max) : !(use_max > 1.0f);
             pred_max = m;
