@@ -67,6 +67,14 @@ struct lora_phy_cuda_ctx {
     std::map<std::tuple<int, int, int>, cf*> chirps;   // (sf, bw_hz, osr) -> conjugate downchirp, N*osr entries
     DevBuf state, phases, tmp;                          // PacketState[], modulator phases, compensate scratch
     DevBuf flag, pmax;                                  // lean route: one byte / one max-abs per packet (handed to the certified kernel)
+    // lean route, adaptive: the share of packets the streaming pass handed over in the previous call comes back through a
+    // pinned word (asynchronously); when most were handed over (noisy traffic) the next calls skip that pass and retry it
+    // every 8th call
+    unsigned* h_flagged = nullptr;
+    cudaEvent_t ev_flagged = nullptr;
+    size_t flagged_of = 0;                              // packets of the call the pending word belongs to
+    bool flagged_pending = false;
+    int lean_skip = 0;
     cf* sync_tab[3][13] = {};                            // stream detector tables per (bandwidth scale, sf): up | down | fine
     DevBuf txrx[3];                                      // tx/rx pipelines: symbols, status, host-variant results
     DevBuf mc[8];                                        // Monte-Carlo driver: payload, tx symbols, IQ, rx symbols, status+sync, decoded, len, flags
@@ -186,6 +194,12 @@ int lora_phy_cuda_create(lora_phy_cuda_ctx** out, int device)
         return -EIO;
     }
     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { lora_phy_cuda_destroy(ctx); return -EIO; }
+    if (cudaMallocHost(reinterpret_cast<void**>(&ctx->h_flagged), sizeof(unsigned)) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_flagged, cudaEventDisableTiming) != cudaSuccess) {
+        lora_phy_cuda_destroy(ctx);
+        return -ENOMEM;
+    }
+    *ctx->h_flagged = 0;
     *out = ctx;
     return 0;
 }
@@ -214,6 +228,8 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
         if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
     }
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    if (ctx->ev_flagged) cudaEventDestroy(ctx->ev_flagged);
+    if (ctx->h_flagged) cudaFreeHost(ctx->h_flagged);
     for (int i = 0; i < 8; ++i) {
         if (ctx->side_done[i]) cudaEventDestroy(ctx->side_done[i]);
         if (ctx->side[i]) cudaStreamDestroy(ctx->side[i]);
@@ -335,7 +351,15 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     // settle; (2) the certified kernel over the flagged packets.
     static const bool lean_off = getenv("LORA_PHY_NO_LEAN") != nullptr;
     if (!lean_off && !(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&
-        lk::lean_supported((int)cfg->sf, a) && lk::cert_supported((int)cfg->sf, a)) {
+        lk::lean_supported((int)cfg->sf, a) && lk::cert_supported((int)cfg->sf, a) && [&]() {
+            // verdict of the previous call, if it has arrived: mostly handed over -> the certified kernel alone for a while
+            if (ctx->flagged_pending && cudaEventQuery(ctx->ev_flagged) == cudaSuccess) {
+                ctx->flagged_pending = false;
+                if (ctx->flagged_of >= 64 && (size_t)*ctx->h_flagged * 2 > ctx->flagged_of) ctx->lean_skip = 7;
+            }
+            if (ctx->lean_skip > 0) { --ctx->lean_skip; return false; }
+            return true;
+        }()) {
         CK(ctx->flag.reserve(((n_packets + 15) & ~(size_t)15) + 16));
         CK(ctx->pmax.reserve(n_packets * sizeof(float)));
         CK(cudaMemsetAsync(ctx->flag.p, 0, ((n_packets + 15) & ~(size_t)15) + 16, ctx->stream));     // flags, then (16-byte aligned) the flagged-packet counter
@@ -356,6 +380,12 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
         ++launches;
         ctx->launches += launches;
         if (e != cudaSuccess) return fail(ctx, -EIO, "certified demodulator launch", e);
+        if (!ctx->flagged_pending) {                       // (a still-pending word keeps its own call's count)
+            CK(cudaMemcpyAsync(ctx->h_flagged, p.n_flagged, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaEventRecord(ctx->ev_flagged, ctx->stream));
+            ctx->flagged_of = n_packets;
+            ctx->flagged_pending = true;
+        }
         return 0;
     }
     // default: one launch, one pipeline per packet, margin-certified throughput transform with exact replay of the
