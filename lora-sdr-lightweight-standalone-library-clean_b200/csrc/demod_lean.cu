@@ -63,6 +63,8 @@ namespace lk {
 constexpr float LEAN_U = 5.9604644775390625e-08f;
 constexpr float LEAN_C0 = 384.0f;                 // CERT_C0 of demod_cert.cu (same budget)
 constexpr int LEAN_CHUNK = 512;                   // samples per step: 4 KB
+constexpr int LEAN_SLOT = LEAN_CHUNK + 2;         // entries per ring stage: a stream that starts 8 bytes into a 16-byte unit is
+                                                  // copied from the boundary below it (one extra sample at either end)
 
 template <int SF>
 struct LeanCfg {
@@ -75,7 +77,7 @@ struct LeanCfg {
     static constexpr int LV = CP == 8 ? 3 : CP == 4 ? 2 : 1;              // halving levels inside a chunk
     static constexpr int CTA = WIDE ? LEAN_CTA : LEAN_CTA_NARROW, CTAS = WIDE ? LEAN_CTAS_PER_SM : (SF == 7 ? LEAN_CTAS_SF7 : LEAN_CTAS_NARROW);
     static constexpr int WARPS = CTA / 32;
-    static constexpr size_t ring_bytes = (size_t)WARPS * LEAN_STAGES * LEAN_CHUNK * sizeof(cf);
+    static constexpr size_t ring_bytes = (size_t)WARPS * LEAN_STAGES * LEAN_SLOT * sizeof(cf);
     static constexpr size_t bar_off = ring_bytes;
     static constexpr size_t tws_off = (bar_off + (size_t)WARPS * LEAN_STAGES * 8 + 15) & ~(size_t)15;   // [4][32] lane-stage factors
     static constexpr size_t twl_off = tws_off + 4 * 32 * sizeof(cf);                                   // W_N^e, e < 512
@@ -115,15 +117,15 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
     constexpr bool WIDE = C::WIDE;
     constexpr int GD = C::GD, GDE = T < 32 ? 32 / T : 1;       // windows per chunk; windows the estimator runs side by side
     static_assert(!WIDE || C::CTA == CTA_THREADS, "the exact estimator's group helpers assume CTA_THREADS for multi-warp windows");
-    static_assert((size_t)TW * S * LEAN_CHUNK >= (size_t)N * (GDE < 2 ? 1 : 2), "the team's ring doubles as the exact transform's exchange buffer");
+    static_assert((size_t)TW * S * LEAN_SLOT >= (size_t)N * (GDE < 2 ? 1 : 2), "the team's ring doubles as the exact transform's exchange buffer");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, l = threadIdx.x & 31;
     // team = the threads of one estimator transform's owner set: T / 32 warps (SF10-12) or one warp (SF7-9, where a warp
     // holds 32 / T windows side by side); tid = thread inside a window, grp = window group inside the warp
     const int team = WIDE ? threadIdx.x / T : warp, tid = threadIdx.x % T, wt = warp % TW, grp = WIDE ? 0 : l / T;
     const bool lead = WIDE ? tid == 0 : l == 0;                // the team's first thread
-    cf* ring = reinterpret_cast<cf*>(smem_raw) + (size_t)warp * S * LEAN_CHUNK;
-    cf* ex = reinterpret_cast<cf*>(smem_raw) + (size_t)(team * TW) * S * LEAN_CHUNK + (size_t)grp * N;   // N entries: exchange, then spectrum
+    cf* ring = reinterpret_cast<cf*>(smem_raw) + (size_t)warp * S * LEAN_SLOT;
+    cf* ex = reinterpret_cast<cf*>(smem_raw) + (size_t)(team * TW) * S * LEAN_SLOT + (size_t)grp * N;   // N entries: exchange, then spectrum
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::bar_off) + warp * S;
     cf* tws = reinterpret_cast<cf*>(smem_raw + C::tws_off);
     cf* twl = reinterpret_cast<cf*>(smem_raw + C::twl_off);
@@ -450,7 +452,9 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
             const float rate = mine.rate;
             const float start_max = fabsf(rate) * ((float)total * (float)N) * 1.01f;
             const float Kc = LEAN_U * (LEAN_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
-            bool bad = !(mine.ok == 1 && mine.t_off == 0 && Kc < 0.0078125f);         // tier 1 available (demod_cert.cu)
+            // tier 1 available (demod_cert.cu); shifted windows (t_off != 0, LoRaDemod.cpp:143-150) only where a step is whole
+            // windows (SF7-9)
+            bool bad = !(mine.ok == 1 && (mine.t_off == 0 || (!WIDE && mine.t_off > -N && mine.t_off < N)) && Kc < 0.0078125f);
             const float tier1 = fp::TIER1 * (float)N;
             float mmax = 0.0f;
             int sw0 = 0, sw1 = 0;
@@ -482,7 +486,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 const uint32_t n_chunks = total * (uint32_t)R;
                 auto issue = [&](uint32_t g, int stg) {                // lane 0
                     ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, LEAN_CHUNK * sizeof(cf));
-                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_CHUNK * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK,
+                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_SLOT * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK,
                                      LEAN_CHUNK * sizeof(cf), bar0 + 8u * (uint32_t)stg);
                 };
                 if (l == 0) {
@@ -506,7 +510,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                         }
                         ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
                         phase_bits ^= 1u << stage;
-                        const cf* raw = ring + (size_t)stage * LEAN_CHUNK + l;
+                        const cf* raw = ring + (size_t)stage * LEAN_SLOT + l;
                         cf v[16];
                         float mw = 0.0f;
 #pragma unroll
@@ -657,12 +661,22 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     __syncwarp();
                 }
                 const cf geo_g1 = hp[0];
-                const uint32_t n_chunks = (total + (uint32_t)GD - 1) / (uint32_t)GD;
+                // Window bases (LoRaDemod.cpp:143-150, count == total N here): with t_off > 0 every window but the last
+                // starts t_off later; with t_off < 0 every window but the first starts |t_off| earlier.  The shifted windows
+                // are one contiguous run and go through the ring (from the 16-byte boundary below its first sample when
+                // that one is odd); the one unshifted window comes straight from global memory afterwards.
+                const int toff = mine.t_off;
+                const uint32_t run0 = toff > 0 ? (uint32_t)toff : (toff < 0 ? (uint32_t)(N + toff) : 0u);    // first sample of the run
+                const uint32_t n_run = toff ? total - 1 : total;                                          // windows in it
+                const uint32_t sym0 = toff < 0 ? 1u : 0u;                                                  // symbol of its first window
+                const uint32_t odd = run0 & 1u;
+                const cf* src0 = pkt + (run0 - odd);
+                const uint32_t n_chunks = (n_run + (uint32_t)GD - 1) / (uint32_t)GD;
                 auto issue = [&](uint32_t g, int stg) {                // lane 0: the step's windows are contiguous
-                    const uint32_t left = total - g * (uint32_t)GD;
-                    const uint32_t bytes = (left < (uint32_t)GD ? left : (uint32_t)GD) * (uint32_t)(N * sizeof(cf));
+                    const uint32_t left = n_run - g * (uint32_t)GD;
+                    const uint32_t bytes = (left < (uint32_t)GD ? left : (uint32_t)GD) * (uint32_t)(N * sizeof(cf)) + odd * 16u;
                     ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, bytes);
-                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_CHUNK * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK, bytes,
+                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_SLOT * sizeof(cf)), src0 + (size_t)g * LEAN_CHUNK, bytes,
                                      bar0 + 8u * (uint32_t)stg);
                 };
                 if (l == 0) {
@@ -670,28 +684,45 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     for (uint32_t g = 0; g < (uint32_t)(S - 1) && g < n_chunks; ++g) { issue(g, stg); stg = stg + 1 == S ? 0 : stg + 1; }
                 }
                 uint32_t g = 0;
+                // one more step after the run when t_off != 0: the unshifted window (group 0 of the warp), from global memory
+                const uint32_t n_steps = n_chunks + (toff ? 1u : 0u);
 #pragma unroll 1
-                for (; g < n_chunks && !bad; ++g) {
-                    __syncwarp();                                      // every lane has finished the slot that is refilled now
-                    if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
-                        int stg = stage + (S - 1);
-                        if (stg >= S) stg -= S;
-                        issue(g + (uint32_t)(S - 1), stg);
-                    }
-                    ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
-                    phase_bits ^= 1u << stage;
-                    const uint32_t s = g * (uint32_t)GD + (uint32_t)gq;
-                    const bool active = s < total;
-                    const cf* raw = ring + (size_t)stage * LEAN_CHUNK + gq * N + tid;
+                for (uint32_t step = 0; step < n_steps && !bad; ++step) {
+                    const bool direct = step >= n_chunks;
                     cf v[16];
+                    uint32_t s;
+                    bool active;
+                    if (!direct) {
+                        __syncwarp();                                  // every lane has finished the slot that is refilled now
+                        if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
+                            int stg = stage + (S - 1);
+                            if (stg >= S) stg -= S;
+                            issue(g + (uint32_t)(S - 1), stg);
+                        }
+                        ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                        phase_bits ^= 1u << stage;
+                        const uint32_t w = g * (uint32_t)GD + (uint32_t)gq;
+                        s = sym0 + w;
+                        active = w < n_run;
+                        const cf* raw = ring + (size_t)stage * LEAN_SLOT + odd + gq * N + tid;
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) v[c] = raw[T * c];
+                        stage = stage + 1 == S ? 0 : stage + 1;
+                        ++g;
+                    } else {
+                        s = toff > 0 ? total - 1 : 0u;
+                        active = gq == 0;
+                        const cf* gsrc = pkt + (size_t)s * N + tid;
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) v[c] = active ? ldg_cf(gsrc + T * c) : fx::mk(0.0f, 0.0f);
+                    }
                     float mw = 0.0f;
                     cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
 #pragma unroll
                     for (int c = 0; c < 16; ++c) {
-                        const cf r = raw[T * c];
+                        const cf r = v[c];
                         mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                         // LoRaDemod.cpp:61-68
                         if (c & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
-                        v[c] = r;
                     }
                     if (active) mmax = fmaxf(mmax, mw);
                     float en = ((e0.x + e0.y) + (e1.x + e1.y)) * 1.000002f;
@@ -745,7 +776,16 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                         else a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
                     }
                     if (__any_sync(0xffffffffu, active && !cert)) bad = true;
-                    stage = stage + 1 == S ? 0 : stage + 1;
+                }
+                // samples no window covered (the max-abs is over the whole packet, LoRaDemod.cpp:61-68): the first t_off of
+                // the packet, or its last |t_off|
+                if (toff != 0 && !bad) {
+                    const uint32_t a0 = (uint32_t)(toff > 0 ? toff : -toff);
+                    const cf* e = pkt + (toff > 0 ? 0u : count - a0);
+                    for (uint32_t i = (uint32_t)l; i < a0; i += 32u) {
+                        const cf r = ldg_cf(e + i);
+                        mmax = fmaxf(fmaxf(mmax, fabsf(r.x)), fabsf(r.y));
+                    }
                 }
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, off));

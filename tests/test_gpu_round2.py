@@ -508,6 +508,40 @@ def test_lean_route_many_rounds_gain_changes_and_long_packets(phy, lp, oracle, s
         check_legacy(phy, lp, oracle, np.stack([long_pkt, long_pkt[::-1].copy() * np.complex64(0.5)]), sf, 1, 0)
 
 
+@pytest.mark.parametrize("sf", [7, 8, 9, 10])
+def test_lean_route_shifted_windows(phy, lp, oracle, sf):
+    """The reference's estimator turns a fractional peak position of the two sync symbols into an integer time offset and
+    every window but one then starts t_off samples later (or earlier), LoRaDemod.cpp:138-150.  Packets whose sync tones
+    sit a few N-ths of a bin off the grid, both signs, odd and even offsets, with and without noise: every output equals
+    the oracle; at SF7-9 the streaming pass keeps them (shifted run through the ring, the unshifted window from global
+    memory), at SF10 it hands them over."""
+    rng = np.random.default_rng(4100 + sf)
+    N = 1 << sf
+    S = 9
+    i = np.arange(N)
+    rows, want_toff = [], []
+    # the estimator's fIndex grows with the square of a small offset: 0.1 .. 0.3 bin give |t_off| = 1 .. 9 at SF7, 6 .. 76 at SF10
+    for k, delta in enumerate([0.1, -0.1, 0.15, -0.15, 0.2, -0.2, 0.25, -0.25, 0.0, 0.3, -0.3, 0.12]):
+        syms = rng.integers(0, N, S - 2)
+        b0, b1 = 8 * (N // 128) + 3, 16 * (N // 128) + 3
+        wins = [np.exp(2j * np.pi * (b0 + delta) * i / N), np.exp(2j * np.pi * (b1 + delta) * i / N)]
+        wins += [np.exp(2j * np.pi * int(b) * i / N) for b in syms]
+        d = np.concatenate(wins).astype(np.complex64) * np.float32(0.9 if k % 3 else 1.6)
+        if k % 2:
+            d = (d + np.float32(0.03) * (rng.standard_normal(d.size) + 1j * rng.standard_normal(d.size))).astype(np.complex64)
+        rows.append(d)
+    iq = np.stack(rows)
+    got_toff = [int(round(oracle.lora_demodulate(r, sf, 1, 0, 1)[4])) for r in rows]
+    assert sum(1 for t in got_toff if t != 0) >= 8, got_toff         # the construction really shifts the windows
+    c0 = phy.cert_stats()
+    check_legacy(phy, lp, oracle, iq, sf, 1, 0)
+    c1 = phy.cert_stats()
+    if sf <= 9:
+        assert c1[5] - c0[5] <= 3, (got_toff, c0, c1)               # kept by the streaming pass
+    else:
+        assert c1[5] - c0[5] >= 8
+
+
 def test_every_kernel_family_small_cases():
     """tools/sanitize_driver.py (written for compute-sanitizer, which is closed on this pool) as a plain run: every kernel
     family on ragged / oversized / odd-aligned / loud / noise-only inputs must complete without a CUDA error."""
