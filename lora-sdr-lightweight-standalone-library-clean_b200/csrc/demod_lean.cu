@@ -452,9 +452,8 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
             const float rate = mine.rate;
             const float start_max = fabsf(rate) * ((float)total * (float)N) * 1.01f;
             const float Kc = LEAN_U * (LEAN_C0 + start_max + 2.0f * fabsf(rate) * (float)N);
-            // tier 1 available (demod_cert.cu); shifted windows (t_off != 0, LoRaDemod.cpp:143-150) only where a step is whole
-            // windows (SF7-9)
-            bool bad = !(mine.ok == 1 && (mine.t_off == 0 || (!WIDE && mine.t_off > -N && mine.t_off < N)) && Kc < 0.0078125f);
+            // tier 1 available (demod_cert.cu)
+            bool bad = !(mine.ok == 1 && mine.t_off > -N && mine.t_off < N && Kc < 0.0078125f);
             const float tier1 = fp::TIER1 * (float)N;
             float mmax = 0.0f;
             int sw0 = 0, sw1 = 0;
@@ -482,43 +481,65 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 }
                 const cf geo_g1 = hp[0];
 
-                // the stream: total * R chunks of 4 KB, contiguous
-                const uint32_t n_chunks = total * (uint32_t)R;
+                // the stream: 4 KB chunks, contiguous.  With a time offset (LoRaDemod.cpp:143-150, count == total N here) every
+                // window but the last (t_off > 0) or the first (t_off < 0) is shifted: those are one contiguous run through
+                // the ring (copied from the 16-byte boundary below an odd first sample), the unshifted window is read from
+                // global memory by the same code afterwards.
+                const int toff = mine.t_off;
+                const uint32_t run0 = toff > 0 ? (uint32_t)toff : (toff < 0 ? (uint32_t)(N + toff) : 0u);
+                const uint32_t n_run = toff ? total - 1 : total;
+                const uint32_t sym0 = toff < 0 ? 1u : 0u;
+                const uint32_t odd = run0 & 1u;
+                const cf* src0 = pkt + (run0 - odd);
+                const uint32_t n_chunks = n_run * (uint32_t)R;
                 auto issue = [&](uint32_t g, int stg) {                // lane 0
-                    ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, LEAN_CHUNK * sizeof(cf));
-                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_SLOT * sizeof(cf)), pkt + (size_t)g * LEAN_CHUNK,
-                                     LEAN_CHUNK * sizeof(cf), bar0 + 8u * (uint32_t)stg);
+                    const uint32_t bytes = LEAN_CHUNK * sizeof(cf) + odd * 16u;
+                    ptx::mbar_arrive_expect_tx_sa(bar0 + 8u * (uint32_t)stg, bytes);
+                    ptx::bulk_g2s_sa(ring0 + (uint32_t)stg * (LEAN_SLOT * sizeof(cf)), src0 + (size_t)g * LEAN_CHUNK, bytes,
+                                     bar0 + 8u * (uint32_t)stg);
                 };
                 if (l == 0) {
                     int stg = stage;
                     for (uint32_t g = 0; g < (uint32_t)(S - 1) && g < n_chunks; ++g) { issue(g, stg); stg = stg + 1 == S ? 0 : stg + 1; }
                 }
                 uint32_t g = 0;
+                const uint32_t n_win = n_run + (toff ? 1u : 0u);
 #pragma unroll 1
-                for (uint32_t s = 0; s < total; ++s) {
+                for (uint32_t w = 0; w < n_win; ++w) {
+                    const bool direct = w >= n_run;                    // the unshifted window, from global memory
+                    const uint32_t s = direct ? (toff > 0 ? total - 1 : 0u) : sym0 + w;
                     cf acc[R];
                     cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
                     cf h1 = fx::mk(1.0f, 0.0f), h2 = h1, h4 = h1, h8 = h1;
                     int k0 = 0;
 #pragma unroll
-                    for (int q = 0; q < R; ++q, ++g) {
-                        __syncwarp();                                  // every lane has finished the slot that is refilled now
-                        if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
-                            int stg = stage + (S - 1);
-                            if (stg >= S) stg -= S;
-                            issue(g + (uint32_t)(S - 1), stg);
-                        }
-                        ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
-                        phase_bits ^= 1u << stage;
-                        const cf* raw = ring + (size_t)stage * LEAN_SLOT + l;
+                    for (int q = 0; q < R; ++q) {
                         cf v[16];
+                        if (!direct) {
+                            __syncwarp();                              // every lane has finished the slot that is refilled now
+                            if (l == 0 && g + (uint32_t)(S - 1) < n_chunks) {
+                                int stg = stage + (S - 1);
+                                if (stg >= S) stg -= S;
+                                issue(g + (uint32_t)(S - 1), stg);
+                            }
+                            ptx::mbar_wait_sa(bar0 + 8u * (uint32_t)stage, (phase_bits >> stage) & 1u);
+                            phase_bits ^= 1u << stage;
+                            const cf* raw = ring + (size_t)stage * LEAN_SLOT + odd + l;
+#pragma unroll
+                            for (int m = 0; m < 16; ++m) v[m] = raw[32 * m];
+                            stage = stage + 1 == S ? 0 : stage + 1;
+                            ++g;
+                        } else {
+                            const cf* gsrc = pkt + (size_t)s * N + (size_t)q * LEAN_CHUNK + l;
+#pragma unroll
+                            for (int m = 0; m < 16; ++m) v[m] = ldg_cf(gsrc + 32 * m);
+                        }
                         float mw = 0.0f;
 #pragma unroll
                         for (int m = 0; m < 16; ++m) {
-                            const cf r = raw[32 * m];
+                            const cf r = v[m];
                             mw = fmaxf(fmaxf(mw, fabsf(r.x)), fabsf(r.y));                     // LoRaDemod.cpp:61-68
                             if (m & 1) e1 = ff::sqacc(e1, r); else e0 = ff::sqacc(e0, r);
-                            v[m] = r;
                         }
                         mmax = fmaxf(mmax, mw);
                         if (q == 0) {
@@ -573,7 +594,6 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
 #pragma unroll
                             for (int j = 0; j < R; ++j) acc[j] = lean_cma(acc[j], v[j], hq);
                         }
-                        stage = stage + 1 == S ? 0 : stage + 1;
                     }
                     // end of the window: thread t = l + 32 j holds acc[j]; twiddle exp(j t theta), theta = rate - 2 pi k0 / N
                     const cf el = ff::fcmul(geo_f, twl[l * k0]);                               // F_l W_N^(l k0)
@@ -627,6 +647,19 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     if (s == 0) sw0 = idx;
                     else if (s == 1) sw1 = idx;
                     else if (l == 0) a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
+                }
+                // samples no window covered (the max-abs is over the whole packet, LoRaDemod.cpp:61-68): the first t_off of
+                // the packet, or its last |t_off|
+                if (toff != 0 && !bad) {
+                    const uint32_t a0 = (uint32_t)(toff > 0 ? toff : -toff);
+                    const cf* e = pkt + (toff > 0 ? 0u : count - a0);
+                    for (uint32_t i = (uint32_t)l; i < a0; i += 32u) {
+                        const cf r = ldg_cf(e + i);
+                        mmax = fmaxf(fmaxf(mmax, fabsf(r.x)), fabsf(r.y));
+                    }
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) mmax = fmaxf(mmax, __shfl_xor_sync(0xffffffffu, mmax, off));
+                    if (!(mmax < 3.0e38f)) bad = true;
                 }
                 if (bad) {
                     // abandon the packet: consume the copies still in flight so that the ring's phases stay consistent

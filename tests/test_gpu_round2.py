@@ -508,13 +508,13 @@ def test_lean_route_many_rounds_gain_changes_and_long_packets(phy, lp, oracle, s
         check_legacy(phy, lp, oracle, np.stack([long_pkt, long_pkt[::-1].copy() * np.complex64(0.5)]), sf, 1, 0)
 
 
-@pytest.mark.parametrize("sf", [7, 8, 9, 10])
+@pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
 def test_lean_route_shifted_windows(phy, lp, oracle, sf):
     """The reference's estimator turns a fractional peak position of the two sync symbols into an integer time offset and
     every window but one then starts t_off samples later (or earlier), LoRaDemod.cpp:138-150.  Packets whose sync tones
     sit a few N-ths of a bin off the grid, both signs, odd and even offsets, with and without noise: every output equals
-    the oracle; at SF7-9 the streaming pass keeps them (shifted run through the ring, the unshifted window from global
-    memory), at SF10 it hands them over."""
+    the oracle, and the streaming pass keeps them (shifted run through the ring, the unshifted window from global
+    memory)."""
     rng = np.random.default_rng(4100 + sf)
     N = 1 << sf
     S = 9
@@ -536,10 +536,7 @@ def test_lean_route_shifted_windows(phy, lp, oracle, sf):
     c0 = phy.cert_stats()
     check_legacy(phy, lp, oracle, iq, sf, 1, 0)
     c1 = phy.cert_stats()
-    if sf <= 9:
-        assert c1[5] - c0[5] <= 3, (got_toff, c0, c1)               # kept by the streaming pass
-    else:
-        assert c1[5] - c0[5] >= 8
+    assert c1[5] - c0[5] <= 6, (got_toff, c0, c1)                   # (most of them) kept by the streaming pass
 
 
 def test_every_kernel_family_small_cases():
