@@ -295,7 +295,7 @@ def also_stream_mixed(phy, lp, torch, peak, gbytes=6.0, symbols=24, steps=3):
 def also_awgn(phy, lp, torch, sf=7, snr_db=-6.0, packets=200000, payload=16):
     """AWGN Monte-Carlo driver (cfg 5 shape, one cell): modulate + noise + demodulate + decode + score on the device."""
     cc = lp.make_chain_cfg(sf, cr=4)
-    phy.awgn_roundtrip(cc, snr_db, 2048, payload, cell_id=1)
+    phy.awgn_roundtrip(cc, snr_db, packets, payload, cell_id=1)      # untimed: the context's scratch grows to the cell's size here
     torch.cuda.synchronize()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
