@@ -25,8 +25,10 @@
 //     warp's previous packet; the stream tracks the true max-abs, and a miss is re-estimated with the true scale in the
 //     next estimator phase: the symbols (scale-invariant decisions) stand iff t_off is unchanged and the rate moved by
 //     no more than the tolerance the certificate budgets, else the packet is flagged.
-//   stream phase: every window as above; the first refused window (noise, weak signal, NaN / Inf), an irregular packet
-//     (t_off != 0, partial symbol, 8-byte alignment, non-finite max) flags the packet and abandons it.
+//   stream phase: every window as above.  A time offset (t_off != 0: every window but one shifted, LoRaDemod.cpp:143-150)
+//     is streamed as one contiguous run from the 16-byte boundary below its first sample, the unshifted window comes
+//     from global memory.  The first refused window (noise, weak signal, NaN / Inf), an irregular packet (partial
+//     symbol, 8-byte alignment, non-finite max) flags the packet and abandons it.
 // Symbols, sync word, status, cfo, time_offset are bit-exact either way: accepted windows carry demod_cert.cu's proof
 // (same constants, same budget: DESIGN.md section 5), everything else is that kernel.
 #include <atomic>
