@@ -49,6 +49,9 @@ namespace lk {
 #ifndef LEAN_CTAS_SF7
 #define LEAN_CTAS_SF7 3
 #endif
+#ifndef LEAN_RETRY
+#define LEAN_RETRY 1                          // SF7-9: a refused window is tried again with the two neighbouring bin classes (A/B knob)
+#endif
 #ifndef LEAN_PAIR_SF7
 #define LEAN_PAIR_SF7 1                       // SF7: one exact estimator pass serves two jobs (A/B knob)
 #endif
@@ -784,33 +787,58 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                         if (z.y < 0.0f) qq = 16 - qq;
                         k0 = qq & 15;
                     }
-                    const float4 hA = *reinterpret_cast<const float4*>(&hp[4 * k0]);
-                    const float4 hB = *reinterpret_cast<const float4*>(&hp[4 * k0 + 2]);
-                    const cf h1 = fx::mk(hA.x, hA.y), h2 = fx::mk(hA.z, hA.w), h4 = fx::mk(hB.x, hB.y), h8 = fx::mk(hB.z, hB.w);
+                    // The class is judged from 4 x T sample pairs; in noise it can land one sector off.  Any class that passes
+                    // the test is right (a wrong one cannot hold 9/16 of the energy), so a refused window is tried again with
+                    // the two neighbouring classes before the packet is given up -- from the samples still in the slot.
+                    float en_w = en;
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) v[c] = lean_cma(v[c], v[c + 8], h8);
+                    for (int off = T / 2; off > 0; off >>= 1) en_w += __shfl_xor_sync(0xffffffffu, en_w, off);
+                    bool settled = !active;
+                    auto settle = [&](int kk) {                        // the pruned transform of class kk on v (consumed)
+                        const float4 hA = *reinterpret_cast<const float4*>(&hp[4 * kk]);
+                        const float4 hB = *reinterpret_cast<const float4*>(&hp[4 * kk + 2]);
+                        const cf h1 = fx::mk(hA.x, hA.y), h2 = fx::mk(hA.z, hA.w), h4 = fx::mk(hB.x, hB.y), h8 = fx::mk(hB.z, hB.w);
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) v[c] = lean_cma(v[c], v[c + 4], h4);
+                        for (int c = 0; c < 8; ++c) v[c] = lean_cma(v[c], v[c + 8], h8);
 #pragma unroll
-                    for (int c = 0; c < 2; ++c) v[c] = lean_cma(v[c], v[c + 2], h2);
-                    const cf pv = lean_cma(v[0], v[1], h1);
-                    const cf cval = ff::fcmul(ff::fcmul(pv, twl[(tid * k0) & (N - 1)]), geo_f);
-                    const cf yv = fp::lane_dft<SF>(cval, tid, tws);
-                    const unsigned qb = __float_as_uint(ff::fnorm(yv));               // >= +0, or NaN (sorts above everything)
-                    unsigned qmax = qb;
+                        for (int c = 0; c < 4; ++c) v[c] = lean_cma(v[c], v[c + 4], h4);
 #pragma unroll
-                    for (int off = T / 2; off > 0; off >>= 1) {
-                        qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
-                        en += __shfl_xor_sync(0xffffffffu, en, off);
+                        for (int c = 0; c < 2; ++c) v[c] = lean_cma(v[c], v[c + 2], h2);
+                        const cf pv = lean_cma(v[0], v[1], h1);
+                        const cf cval = ff::fcmul(ff::fcmul(pv, twl[(tid * kk) & (N - 1)]), geo_f);
+                        const cf yv = fp::lane_dft<SF>(cval, tid, tws);
+                        const unsigned qb = __float_as_uint(ff::fnorm(yv));           // >= +0, or NaN (sorts above everything)
+                        unsigned qmax = qb;
+#pragma unroll
+                        for (int off = T / 2; off > 0; off >>= 1) qmax = max(qmax, __shfl_xor_sync(0xffffffffu, qmax, off));
+                        const float q1 = __uint_as_float(qmax);
+                        const bool cert = (q1 > tier1 * en_w) && (en_w < 1.0e30f) && (q1 >= 8.3e-25f);
+                        if (!settled && cert) {
+                            if (qb == qmax) {                              // the lane that holds the top bin (unique when certified)
+                                const int idx = kk + 16 * (int)(__brev((unsigned)tid) >> (32 - PR::LW));
+                                if (s < 2) mycell->pad[s] = idx;
+                                else a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
+                            }
+                            settled = true;
+                        }
+                    };
+                    settle(k0);
+                    // The class is judged from 4 x T sample pairs; in noise it can land one sector off.  Any class that passes
+                    // the test is right (a wrong one cannot hold 9/16 of the energy), so a refused window is tried again with
+                    // the two neighbouring classes before the packet is given up -- from the samples still in the slot.
+                    if (LEAN_RETRY && __builtin_expect(__any_sync(0xffffffffu, !settled) != 0, 0)) {
+                        const int prev = stage == 0 ? S - 1 : stage - 1;   // the slot this step consumed (not refilled before the next step)
+                        const cf* vsrc = direct ? pkt + (size_t)s * N + tid : ring + (size_t)prev * LEAN_SLOT + odd + gq * N + tid;
+#pragma unroll 1
+                        for (int att = 1; att < 3; ++att) {
+#pragma unroll
+                            for (int c = 0; c < 16; ++c)
+                                v[c] = (direct && !active) ? fx::mk(0.0f, 0.0f) : (direct ? ldg_cf(vsrc + T * c) : vsrc[T * c]);
+                            settle((k0 + (att == 1 ? 1 : 15)) & 15);
+                            if (!__any_sync(0xffffffffu, !settled)) break;
+                        }
                     }
-                    const float q1 = __uint_as_float(qmax);
-                    const bool cert = (q1 > tier1 * en) && (en < 1.0e30f) && (q1 >= 8.3e-25f);
-                    if (active && cert && qb == qmax) {                    // the lane that holds the top bin (unique when certified)
-                        const int idx = k0 + 16 * (int)(__brev((unsigned)tid) >> (32 - PR::LW));
-                        if (s < 2) mycell->pad[s] = idx;
-                        else a.symbols[(size_t)pid * a.symbol_stride + (s - 2)] = (uint16_t)idx;
-                    }
-                    if (__any_sync(0xffffffffu, active && !cert)) bad = true;
+                    if (__any_sync(0xffffffffu, !settled)) bad = true;
                 }
                 // samples no window covered (the max-abs is over the whole packet, LoRaDemod.cpp:61-68): the first t_off of
                 // the packet, or its last |t_off|
