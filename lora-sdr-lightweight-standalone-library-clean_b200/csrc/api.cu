@@ -68,8 +68,8 @@ struct lora_phy_cuda_ctx {
     DevBuf state, phases, tmp;                          // PacketState[], modulator phases, compensate scratch
     DevBuf flag, pmax;                                  // lean route: one byte / one max-abs per packet (handed to the certified kernel)
     // lean route, adaptive: the share of packets the streaming pass handed over in the previous call comes back through a
-    // pinned word (asynchronously); when most were handed over (noisy traffic) the next calls skip that pass and retry it
-    // every 8th call
+    // pinned word (asynchronously); when more than a third were handed over (noisy traffic: measured break-even) the next
+    // calls skip that pass and retry it every 8th call
     unsigned* h_flagged = nullptr;
     cudaEvent_t ev_flagged = nullptr;
     size_t flagged_of = 0;                              // packets of the call the pending word belongs to
@@ -355,7 +355,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
             // verdict of the previous call, if it has arrived: mostly handed over -> the certified kernel alone for a while
             if (ctx->flagged_pending && cudaEventQuery(ctx->ev_flagged) == cudaSuccess) {
                 ctx->flagged_pending = false;
-                if (ctx->flagged_of >= 64 && (size_t)*ctx->h_flagged * 2 > ctx->flagged_of) ctx->lean_skip = 7;
+                if (ctx->flagged_of >= 64 && (size_t)*ctx->h_flagged * 3 > ctx->flagged_of) ctx->lean_skip = 7;
             }
             if (ctx->lean_skip > 0) { --ctx->lean_skip; return false; }
             return true;
