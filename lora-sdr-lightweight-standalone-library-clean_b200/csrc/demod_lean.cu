@@ -32,6 +32,7 @@
 // Symbols, sync word, status, cfo, time_offset are bit-exact either way: accepted windows carry demod_cert.cu's proof
 // (same constants, same budget: DESIGN.md section 5), everything else is that kernel.
 #include <atomic>
+#include <type_traits>
 #include "stream_common.cuh"
 #include "fft_fast.cuh"
 #include "fft_prune.cuh"
@@ -386,6 +387,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                         if (a.cfo) a.cfo[np[q]] = r.cfo;
                         if (a.time_offset) a.time_offset[np[q]] = r.toff;
                         c.rate = r.rate; c.t_off = r.t_off; c.used_max = c.pred;
+                        c.pad[2] = fabsf(r.toff) > 0.02f ? 1 : 0;
                     }
                 }
                 group_sync<T>();
@@ -428,6 +430,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                         if (a.cfo) a.cfo[pid] = cfo;
                         if (a.time_offset) a.time_offset[pid] = toff;
                         cells[m].rate = rate; cells[m].t_off = t_off; cells[m].used_max = cells[m].pred;
+                        cells[m].pad[2] = fabsf(toff) > 0.02f ? 1 : 0;         // sync peaks off the grid: not a clean packet
                     }
                     ok = 1;
                 }
@@ -490,7 +493,12 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 // window but the last (t_off > 0) or the first (t_off < 0) is shifted: those are one contiguous run through
                 // the ring (copied from the 16-byte boundary below an odd first sample), the unshifted window is read from
                 // global memory by the same code afterwards.
-                const int toff = mine.t_off;
+                // Two copies of the stream: clean packets (no time offset, sync peaks on the grid) run code in which the offset,
+                // the odd-alignment entry, the extra unshifted window and the retry are compile-time absent; the others the
+                // general one.
+                auto run = [&](auto shifted_tag) {
+                constexpr bool SH = decltype(shifted_tag)::value;
+                const int toff = SH ? mine.t_off : 0;
                 const uint32_t run0 = toff > 0 ? (uint32_t)toff : (toff < 0 ? (uint32_t)(N + toff) : 0u);
                 const uint32_t n_run = toff ? total - 1 : total;
                 const uint32_t sym0 = toff < 0 ? 1u : 0u;
@@ -511,7 +519,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 const uint32_t n_win = n_run + (toff ? 1u : 0u);
 #pragma unroll 1
                 for (uint32_t w = 0; w < n_win; ++w) {
-                    const bool direct = w >= n_run;                    // the unshifted window, from global memory
+                    const bool direct = SH && w >= n_run;              // the unshifted window, from global memory
                     const uint32_t s = direct ? (toff > 0 ? total - 1 : 0u) : sym0 + w;
                     cf acc[R];
                     cf e0 = fx::mk(0.0f, 0.0f), e1 = fx::mk(0.0f, 0.0f);
@@ -655,7 +663,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 }
                 // samples no window covered (the max-abs is over the whole packet, LoRaDemod.cpp:61-68): the first t_off of
                 // the packet, or its last |t_off|
-                if (toff != 0 && !bad) {
+                if constexpr (SH) if (toff != 0 && !bad) {
                     const uint32_t a0 = (uint32_t)(toff > 0 ? toff : -toff);
                     const cf* e = pkt + (toff > 0 ? 0u : count - a0);
                     for (uint32_t i = (uint32_t)l; i < a0; i += 32u) {
@@ -676,6 +684,8 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     }
                     __syncwarp();
                 }
+                };
+                if (mine.t_off != 0 || mine.pad[2] != 0) run(std::true_type{}); else run(std::false_type{});
             }
             } else {
             if (!bad) {
@@ -703,7 +713,12 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 // starts t_off later; with t_off < 0 every window but the first starts |t_off| earlier.  The shifted windows
                 // are one contiguous run and go through the ring (from the 16-byte boundary below its first sample when
                 // that one is odd); the one unshifted window comes straight from global memory afterwards.
-                const int toff = mine.t_off;
+                // Two copies of the stream: clean packets (no time offset, sync peaks on the grid) run code in which the offset,
+                // the odd-alignment entry, the extra unshifted window and the retry are compile-time absent; the others the
+                // general one.
+                auto run = [&](auto shifted_tag) {
+                constexpr bool SH = decltype(shifted_tag)::value;
+                const int toff = SH ? mine.t_off : 0;
                 const uint32_t run0 = toff > 0 ? (uint32_t)toff : (toff < 0 ? (uint32_t)(N + toff) : 0u);    // first sample of the run
                 const uint32_t n_run = toff ? total - 1 : total;                                          // windows in it
                 const uint32_t sym0 = toff < 0 ? 1u : 0u;                                                  // symbol of its first window
@@ -726,7 +741,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 const uint32_t n_steps = n_chunks + (toff ? 1u : 0u);
 #pragma unroll 1
                 for (uint32_t step = 0; step < n_steps && !bad; ++step) {
-                    const bool direct = step >= n_chunks;
+                    const bool direct = SH && step >= n_chunks;
                     cf v[16];
                     uint32_t s;
                     bool active;
@@ -826,7 +841,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     // The class is judged from 4 x T sample pairs; in noise it can land one sector off.  Any class that passes
                     // the test is right (a wrong one cannot hold 9/16 of the energy), so a refused window is tried again with
                     // the two neighbouring classes before the packet is given up -- from the samples still in the slot.
-                    if (LEAN_RETRY && __builtin_expect(__any_sync(0xffffffffu, !settled) != 0, 0)) {
+                    if (SH && LEAN_RETRY && __builtin_expect(__any_sync(0xffffffffu, !settled) != 0, 0)) {
                         const int prev = stage == 0 ? S - 1 : stage - 1;   // the slot this step consumed (not refilled before the next step)
                         const cf* vsrc = direct ? pkt + (size_t)s * N + tid : ring + (size_t)prev * LEAN_SLOT + odd + gq * N + tid;
 #pragma unroll 1
@@ -842,7 +857,7 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                 }
                 // samples no window covered (the max-abs is over the whole packet, LoRaDemod.cpp:61-68): the first t_off of
                 // the packet, or its last |t_off|
-                if (toff != 0 && !bad) {
+                if constexpr (SH) if (toff != 0 && !bad) {
                     const uint32_t a0 = (uint32_t)(toff > 0 ? toff : -toff);
                     const cf* e = pkt + (toff > 0 ? 0u : count - a0);
                     for (uint32_t i = (uint32_t)l; i < a0; i += 32u) {
@@ -865,6 +880,8 @@ __global__ void __launch_bounds__(LeanCfg<SF>::CTA, LeanCfg<SF>::CTAS) demod_lea
                     }
                     __syncwarp();
                 }
+                };
+                if (mine.t_off != 0 || mine.pad[2] != 0) run(std::true_type{}); else run(std::false_type{});
             }
             }
             if (bad) {
