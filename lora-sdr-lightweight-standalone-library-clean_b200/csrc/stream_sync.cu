@@ -15,6 +15,13 @@
 // Two pieces are serial on thread 0 because their order is observable in the results: the fine-tune index
 // recurrence (an int decremented by a float and truncated, per sample, :160-163) and the detector's
 // double-precision running total (LoRaDetector.hpp:45-52).
+//
+// Streams do not wait for each other: every barrier and vote of the walk spans one DOMAIN only -- the warp for
+// windows of up to 32 threads (SF7-9; the 4 / 2 / 1 streams of a warp step together), the stream's own thread
+// group (named barrier) above.  A stream that looks ahead for sync word1, or falls back to a serial loop, delays the
+// streams of its warp, not the 32 streams of its CTA.  The next window always starts inside the 3N chips after the
+// current window's start, so each step asks L2 for the lines up to 4N chips ahead (prefetch.global.L2): the window
+// load that follows a slide decision finds its samples on chip.
 #include "demod_device.cuh"
 #include "internal.h"
 
@@ -32,10 +39,16 @@ struct GroupCtl {            // written by the group's thread 0, read by the who
     int ok, ft2;
 };
 
+// CTA size: multi-warp windows use the CTA_THREADS-wide group helpers; sub-warp windows need no CTA-wide anything,
+// so they run in 128-thread CTAs (twice the CTAs for the same streams: a few thousand SF7 streams reach every SM)
+template <int SF>
+constexpr int sync_cta() { return fx::Plan<SF>::T <= 32 ? 128 : CTA_THREADS; }
+
 template <int SF>
 struct SyncSmem {
     using P = fx::Plan<SF>;
-    static constexpr int G = CTA_THREADS / P::T;
+    static constexpr int CTA = sync_cta<SF>();
+    static constexpr int G = CTA / P::T;
     static constexpr size_t buf_bytes = 2 * (size_t)G * P::N * sizeof(cf);
     static constexpr size_t ft_bytes = (size_t)G * P::N * sizeof(int);
     static constexpr size_t red_off = buf_bytes + ft_bytes;                       // 8 Peaks, then 8 doubles
@@ -52,6 +65,17 @@ __device__ __forceinline__ int ft_step(int idx, float d, int wrap)
     if (r < 0) r += wrap;
     else if (r >= wrap) r -= wrap;
     return r;
+}
+
+// barrier / vote over one domain: the warp (T <= 32) or the stream's own thread group.  For T > 32 the predicate must
+// already be uniform over the group (it is read from the group's control block after a barrier); the barrier keeps the
+// control block from being rewritten before every thread has read it.
+template <int T>
+__device__ __forceinline__ bool dom_any(bool p)
+{
+    if (T <= 32) return __any_sync(0xffffffffu, p) != 0;
+    group_sync<T>();
+    return p;
 }
 
 // sum of the group's doubles (any order: the caller proves the order does not matter)
@@ -134,8 +158,8 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     group_sync<T>();
     const bool progression = *ok_flag != 0;
     int ft_end = constant ? idx0 : (int)(((unsigned)idx0 - (unsigned)N * (unsigned)k) & (unsigned)(wrap - 1));
-    // the barrier domain (warp or CTA) may hold several groups: enter the fallback together
-    const bool any_serial = T > 32 ? (__syncthreads_or(!progression) != 0) : (__any_sync(0xffffffffu, !progression) != 0);
+    // a warp may hold several groups: they enter the fallback together (a multi-warp group is alone in its domain)
+    const bool any_serial = T > 32 ? !progression : (__any_sync(0xffffffffu, !progression) != 0);
     if (any_serial) {                                        // literal recurrence on thread 0
         if (!progression && tid == 0) {
             int idx = idx0;
@@ -176,22 +200,36 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     for (int r = 0; r < P::R; ++r) spec[P::bin_of_reg(tid, r)] = v[r];
     group_sync<T>();
     DetectOut o; o.value = 0; o.snr = 0.0f; o.findex = 0.0f;
+    float rest = 0.0f;
     if (tid == 0 && live) {
         const double eps = tree * (4.0 * (double)N * 0x1p-53);
-        float rest = (float)((tree - eps) - (double)pk.val);
+        rest = (float)((tree - eps) - (double)pk.val);
         if (a.force_serial || !(rest == (float)((tree + eps) - (double)pk.val))) {
             double total = 0.0;                              // LoRaDetector.hpp:45-52, ascending
             for (int i = 0; i < N; ++i) total += (double)fx::cnorm(spec[i]);
             rest = (float)(total - (double)pk.val);
         }
-        const float noise = __fsqrt_rn(rest);
+    }
+    // The detector's two hypotf and two log10f (LoRaDetector.hpp:60-72) run on threads 0 and 1 side by side -- same code on
+    // two lanes, half the serial tail: thread 0 takes the left neighbour and the fundamental, thread 1 the right neighbour
+    // and the noise.  (T >= 8, so both sit in one warp; every thread of the warp executes the shuffles.)
+    const int lane = threadIdx.x & 31;
+    const float rest1 = __shfl_sync(0xffffffffu, rest, (lane - (tid & 31)) & 31);
+    float hyp = 0.0f, lg = 0.0f;
+    if (tid < 2 && live) {
+        const int nb = tid == 0 ? (pk.idx > 0 ? pk.idx - 1 : N - 1) : (pk.idx < N - 1 ? pk.idx + 1 : 0);
+        const cf c = spec[nb];
+        hyp = gm::hypotf_g(c.x, c.y);
+        lg = gm::log10f_g(__fsqrt_rn(tid == 0 ? pk.val : rest1));
+    }
+    const float right = __shfl_sync(0xffffffffu, hyp, (lane + 1) & 31);
+    const float lg_noise = __shfl_sync(0xffffffffu, lg, (lane + 1) & 31);
+    if (tid == 0 && live) {
         const float fundamental = __fsqrt_rn(pk.val);
-        const cf l = spec[pk.idx > 0 ? pk.idx - 1 : N - 1];
-        const cf r = spec[pk.idx < N - 1 ? pk.idx + 1 : 0];
-        const float left = gm::hypotf_g(l.x, l.y), right = gm::hypotf_g(r.x, r.y);
+        const float left = hyp;
         const double demon = (2.0 * (double)fundamental) - (double)right - (double)left;
-        const float power = fx::fsub(fx::fmul(20.0f, gm::log10f_g(fundamental)), a.power_scale);
-        const float power_avg = fx::fsub(fx::fmul(20.0f, gm::log10f_g(noise)), a.power_scale);
+        const float power = fx::fsub(fx::fmul(20.0f, lg), a.power_scale);
+        const float power_avg = fx::fsub(fx::fmul(20.0f, lg_noise), a.power_scale);
         o.value = pk.idx;
         o.snr = fx::fsub(power, power_avg);
         o.findex = (demon == 0.0) ? 0.0f : (float)(0.5 * (double)fx::fsub(right, left) / demon);
@@ -201,7 +239,7 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
 }
 
 template <int SF, bool EX>
-__global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const StreamSyncArgs a)
+__global__ void __launch_bounds__(sync_cta<SF>(), 512 / sync_cta<SF>()) stream_sync_kernel(const StreamSyncArgs a)
 {
     using P = fx::Plan<SF>;
     using S = SyncSmem<SF>;
@@ -235,6 +273,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
     int state = ST_FRAMESYNC, prev_value = 0, freq_error = 0, fine_idx = 0, down = 0;
     float fine_err = 0.0f;
     uint32_t pos = 0, sym_count = 0, frames = 0, cur_start = 0;
+    uint32_t pf_end = 0;                                                       // samples below this were asked for already
 
     for (;;) {
         if (tid == 0) {
@@ -245,11 +284,25 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
             ctl.fine_err = fine_err;
             ctl.need2 = 0;
         }
-        __syncthreads();
+        group_sync<T>();
         const bool live = ctl.live != 0;
-        if (!__syncthreads_or(live)) break;
+        if (!dom_any<T>(live)) break;
         const uint32_t wpos = ctl.pos;
         const float ferr = ctl.fine_err;
+        if (live) {                                                            // L2 prefetch of the samples the next windows can touch
+            const unsigned long long span = (unsigned long long)N * osr;
+            unsigned long long lo = wpos + span, hi = wpos + 4ull * span;
+            if (lo < pf_end) lo = pf_end;
+            if (hi > n) hi = n;
+            if (hi > lo) {
+                const long long shift = view.comp ? (long long)view.offset : 0ll;  // stream_sample reads m - offset
+                for (unsigned long long m = (lo & ~15ull) + 16ull * tid; m < hi; m += 16ull * T) {
+                    const long long idx = (long long)m - shift;
+                    if (idx >= 0 && idx < (long long)n) asm volatile("prefetch.global.L2 [%0];" ::"l"(iq + idx));
+                }
+                pf_end = (uint32_t)hi;
+            }
+        }
         const cf* chirp = ctl.down ? a.down : a.up;
         int ft = ctl.ft;
         DetectOut d = sync_window<SF, EX>(a, view, wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, ftidx, red, redd,
@@ -264,10 +317,10 @@ __global__ void __launch_bounds__(CTA_THREADS, 2) stream_sync_kernel(const Strea
                 if (syncd && match0) { ctl.need2 = 1; ctl.ft2 = ft; }
             }
         }
-        __syncthreads();
+        group_sync<T>();
         const bool need2 = ctl.need2 != 0;
         int value1 = 0;
-        if (__syncthreads_or(need2)) {                                         // look ahead one window for sync word1 (:188-205)
+        if (dom_any<T>(need2)) {                                         // look ahead one window for sync word1 (:188-205)
             int ft2 = 0;                                                       // (a copy: _fineTuneIndex itself is not advanced)
             DetectOut d1 = sync_window<SF, EX>(a, view, wpos + (uint32_t)N * osr, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
                                            ftidx, red, redd, &ctl.ok);
@@ -333,10 +386,10 @@ cudaError_t launch_sync_sf(const StreamSyncArgs& a, cudaStream_t stream)
     const unsigned grid = (a.n_streams + S::G - 1) / S::G;
     if (ex) {
         cudaFuncSetAttribute(stream_sync_kernel<SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
-        stream_sync_kernel<SF, true><<<grid, CTA_THREADS, S::bytes, stream>>>(a);
+        stream_sync_kernel<SF, true><<<grid, S::CTA, S::bytes, stream>>>(a);
     } else {
         cudaFuncSetAttribute(stream_sync_kernel<SF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes);
-        stream_sync_kernel<SF, false><<<grid, CTA_THREADS, S::bytes, stream>>>(a);
+        stream_sync_kernel<SF, false><<<grid, S::CTA, S::bytes, stream>>>(a);
     }
     return cudaGetLastError();
 }
