@@ -141,17 +141,20 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     const float d = fx::fmul(fine_err, (float)FINE_STEPS);
     // k: the integer step of the first sample, before wrapping
     const int k = idx0 - (int)fx::fsub((float)idx0, d);
-    bool mine_ok = !a.force_serial;
+    // With |d| <= wrap / 2 the one wrap of ft_step is a reduction mod wrap (a power of two), and the next term of the
+    // progression is c_i - k mod wrap: the check per sample is ((int)(float(c_i) - d) - c_i + k) mod wrap == 0.
+    // A larger |d| (never seen: it is 128 x a fraction of a bin plus at most N/4 bins) takes the literal loop.
+    bool mine_ok = !a.force_serial && fabsf(d) <= (float)(wrap / 2);
+    const bool check = !constant && live && !a.force_serial;
     int ci[P::R];
+    int bad = 0;
 #pragma unroll
     for (int c = 0; c < P::R; ++c) {
         const int i = tid + T * c;
         ci[c] = constant ? idx0 : (int)(((unsigned)idx0 - (unsigned)i * (unsigned)k) & (unsigned)(wrap - 1));
-        if (!constant && live && !a.force_serial) {
-            const int nxt = (int)(((unsigned)idx0 - (unsigned)(i + 1) * (unsigned)k) & (unsigned)(wrap - 1));
-            mine_ok = mine_ok && ft_step(ci[c], d, wrap) == nxt;
-        }
+        if (check) bad |= ((int)fx::fsub((float)ci[c], d) - ci[c] + k) & (wrap - 1);
     }
+    mine_ok = mine_ok && bad == 0;
     if (tid == 0) *ok_flag = 1;
     group_sync<T>();
     if (!mine_ok) *ok_flag = 0;
