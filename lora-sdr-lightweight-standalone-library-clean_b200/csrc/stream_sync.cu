@@ -22,6 +22,7 @@
 // streams of its warp, not the 32 streams of its CTA.  The next window always starts inside the 3N chips after the
 // current window's start, so each step asks L2 for the lines up to 4N chips ahead (prefetch.global.L2): the window
 // load that follows a slide decision finds its samples on chip.
+#include <type_traits>
 #include "demod_device.cuh"
 #include "internal.h"
 
@@ -30,6 +31,11 @@ namespace lk {
 namespace {
 
 constexpr int FINE_STEPS = 128;
+// Resident threads per SM the register budget is cut for.  Multi-warp windows (SF10-12) gain 3-6 % from 768 (80
+// registers, a few spilled words, 3 x 64 KB of exchange buffers); sub-warp windows are latency-bound walks of few warps,
+// where the tighter budget costs 25 % (same-box A/B, 4 GB batches) -- they keep 128 registers.
+template <int SF>
+constexpr int sync_threads_per_sm() { return fx::Plan<SF>::T <= 32 ? 512 : 768; }
 enum { ST_FRAMESYNC = 0, ST_DOWNCHIRP0, ST_DOWNCHIRP1, ST_QUARTERCHIRP, ST_DATASYMBOLS };
 
 struct GroupCtl {            // written by the group's thread 0, read by the whole group
@@ -50,8 +56,7 @@ struct SyncSmem {
     static constexpr int CTA = sync_cta<SF>();
     static constexpr int G = CTA / P::T;
     static constexpr size_t buf_bytes = 2 * (size_t)G * P::N * sizeof(cf);
-    static constexpr size_t ft_bytes = (size_t)G * P::N * sizeof(int);
-    static constexpr size_t red_off = buf_bytes + ft_bytes;                       // 8 Peaks, then 8 doubles
+    static constexpr size_t red_off = buf_bytes;                       // 8 Peaks, then 8 doubles
     static constexpr size_t ctl_off = red_off + 8 * sizeof(Peak) + 8 * sizeof(double);
     static constexpr size_t bytes = ctl_off + (size_t)G * sizeof(GroupCtl);
 };
@@ -131,7 +136,7 @@ __device__ __forceinline__ cf stream_sample(const StreamView& v, uint32_t m)
 template <int SF, bool EX>
 __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const StreamView& view, uint32_t wpos, bool live,
                                                  const cf* __restrict__ chirp, int idx0, int* ft_out, float fine_err,
-                                                 int tid, cf* buf0, cf* buf1, int& flip, int* ftidx, Peak* red,
+                                                 int tid, cf* buf0, cf* buf1, int& flip, Peak* red,
                                                  double* redd, volatile int* ok_flag)
 {
     using P = fx::Plan<SF>;
@@ -146,13 +151,14 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     // A larger |d| (never seen: it is 128 x a fraction of a bin plus at most N/4 bins) takes the literal loop.
     bool mine_ok = !a.force_serial && fabsf(d) <= (float)(wrap / 2);
     const bool check = !constant && live && !a.force_serial;
-    int ci[P::R];
+    const unsigned c0 = (unsigned)idx0 - (unsigned)tid * (unsigned)k, cstep = (unsigned)T * (unsigned)k;   // c_i, i = tid + T c
     int bad = 0;
+    if (check) {
 #pragma unroll
-    for (int c = 0; c < P::R; ++c) {
-        const int i = tid + T * c;
-        ci[c] = constant ? idx0 : (int)(((unsigned)idx0 - (unsigned)i * (unsigned)k) & (unsigned)(wrap - 1));
-        if (check) bad |= ((int)fx::fsub((float)ci[c], d) - ci[c] + k) & (wrap - 1);
+        for (int c = 0; c < P::R; ++c) {
+            const int ci = (int)((c0 - (unsigned)c * cstep) & (unsigned)(wrap - 1));
+            bad |= ((int)fx::fsub((float)ci, d) - ci + k) & (wrap - 1);
+        }
     }
     mine_ok = mine_ok && bad == 0;
     if (tid == 0) *ok_flag = 1;
@@ -160,9 +166,12 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     if (!mine_ok) *ok_flag = 0;
     group_sync<T>();
     const bool progression = *ok_flag != 0;
-    int ft_end = constant ? idx0 : (int)(((unsigned)idx0 - (unsigned)N * (unsigned)k) & (unsigned)(wrap - 1));
+    int ft_end = (int)(((unsigned)idx0 - (unsigned)N * (unsigned)k) & (unsigned)(wrap - 1));   // d == 0: k == 0
     // a warp may hold several groups: they enter the fallback together (a multi-warp group is alone in its domain)
     const bool any_serial = T > 32 ? !progression : (__any_sync(0xffffffffu, !progression) != 0);
+    // the literal indices live in the exchange buffer the transform writes SECOND (after its first barrier, which every
+    // thread reaches with its samples loaded), so they need no memory of their own
+    int* ftidx = reinterpret_cast<int*>(flip ? buf0 : buf1);
     if (any_serial) {                                        // literal recurrence on thread 0
         if (!progression && tid == 0) {
             int idx = idx0;
@@ -173,24 +182,26 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
             ft_end = idx;
         }
         group_sync<T>();
-        if (!progression) {
-#pragma unroll
-            for (int c = 0; c < P::R; ++c) ci[c] = ftidx[tid + T * c];
-        }
     }
     if (tid == 0 && live) *ft_out = ft_end;
     cf v[P::R];
+    // two copies of the load loop, so that the usual one has no shared-memory read between its global loads (a select on
+    // `progression` inside ONE loop keeps the compiler from batching the 3 x R loads: measured 2x slower at SF7-9)
+    auto load = [&](auto from_table) {
 #pragma unroll
-    for (int c = 0; c < P::R; ++c) {
-        const int i = tid + T * c;
-        cf x = fx::mk(0.0f, 0.0f);
-        if (live) {
-            // EX: oversampled and / or compensated stream (osr > 1: phase 0 of every chip); else the plain one-sample-per-chip load
-            x = fx::cmul(EX ? stream_sample(view, wpos + (uint32_t)i * a.osr) : ldg_cf(view.iq + wpos + i), ldg_cf(chirp + i));
-            x = fx::cmul(x, ldg_cf(a.fine + ci[c]));
+        for (int c = 0; c < P::R; ++c) {
+            const int i = tid + T * c;
+            cf x = fx::mk(0.0f, 0.0f);
+            if (live) {
+                // EX: oversampled and / or compensated stream (osr > 1: phase 0 of every chip); else the plain one-sample-per-chip load
+                x = fx::cmul(EX ? stream_sample(view, wpos + (uint32_t)i * a.osr) : ldg_cf(view.iq + wpos + i), ldg_cf(chirp + i));
+                const int ci = decltype(from_table)::value ? ftidx[i] : (int)((c0 - (unsigned)c * cstep) & (unsigned)(wrap - 1));
+                x = fx::cmul(x, ldg_cf(a.fine + ci));
+            }
+            v[c] = x;
         }
-        v[c] = x;
-    }
+    };
+    if (progression) load(std::false_type{}); else load(std::true_type{});
     fft_group<SF, true>(v, tid, a.tw, a.ct, buf0, buf1, flip);
     const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
     double part = 0.0;
@@ -242,7 +253,7 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
 }
 
 template <int SF, bool EX>
-__global__ void __launch_bounds__(sync_cta<SF>(), 512 / sync_cta<SF>()) stream_sync_kernel(const StreamSyncArgs a)
+__global__ void __launch_bounds__(sync_cta<SF>(), sync_threads_per_sm<SF>() / sync_cta<SF>()) stream_sync_kernel(const StreamSyncArgs a)
 {
     using P = fx::Plan<SF>;
     using S = SyncSmem<SF>;
@@ -252,7 +263,6 @@ __global__ void __launch_bounds__(sync_cta<SF>(), 512 / sync_cta<SF>()) stream_s
     cf* base = reinterpret_cast<cf*>(smem_raw);
     cf* buf0 = base + (size_t)g * N;
     cf* buf1 = base + (size_t)G * N + (size_t)g * N;
-    int* ftidx = reinterpret_cast<int*>(smem_raw + S::buf_bytes) + (size_t)g * N;
     Peak* red = reinterpret_cast<Peak*>(smem_raw + S::red_off);
     double* redd = reinterpret_cast<double*>(smem_raw + S::red_off + 8 * sizeof(Peak));
     GroupCtl& ctl = reinterpret_cast<GroupCtl*>(smem_raw + S::ctl_off)[g];
@@ -308,7 +318,7 @@ __global__ void __launch_bounds__(sync_cta<SF>(), 512 / sync_cta<SF>()) stream_s
         }
         const cf* chirp = ctl.down ? a.down : a.up;
         int ft = ctl.ft;
-        DetectOut d = sync_window<SF, EX>(a, view, wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, ftidx, red, redd,
+        DetectOut d = sync_window<SF, EX>(a, view, wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, red, redd,
                                       &ctl.ok);
         bool squelched = false, syncd = false, match0 = false;
         if (tid == 0 && live) {
@@ -326,7 +336,7 @@ __global__ void __launch_bounds__(sync_cta<SF>(), 512 / sync_cta<SF>()) stream_s
         if (dom_any<T>(need2)) {                                         // look ahead one window for sync word1 (:188-205)
             int ft2 = 0;                                                       // (a copy: _fineTuneIndex itself is not advanced)
             DetectOut d1 = sync_window<SF, EX>(a, view, wpos + (uint32_t)N * osr, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
-                                           ftidx, red, redd, &ctl.ok);
+                                           red, redd, &ctl.ok);
             if (tid == 0 && need2) { value1 = d1.value; d.findex = d1.findex; }
         }
         if (tid == 0 && live) {
