@@ -91,9 +91,11 @@ struct lora_phy_cuda_ctx {
     cudaEvent_t ev_h2d[2] = { nullptr, nullptr }, ev_done[2] = { nullptr, nullptr }, ev_start = nullptr;
     size_t host_chunk_bytes = (size_t)64 << 20;         // LORA_PHY_HOST_CHUNK_MB
     // mixed stream batches: one launch per (sf, bandwidth, osr) group, each a small grid of sequential walkers -- the groups
-    // run side by side on these streams and join the context's stream at the end
-    cudaStream_t side[8] = {};
-    cudaEvent_t side_done[8] = {}, side_start = nullptr;
+    // run side by side on these streams (one each up to N_SIDE groups, longest walks launched first) and join the
+    // context's stream at the end
+    static constexpr int N_SIDE = 32;
+    cudaStream_t side[N_SIDE] = {};
+    cudaEvent_t side_done[N_SIDE] = {}, side_start = nullptr;
     std::recursive_mutex mu;                            // held for a whole entry point (staging buffers, scratch, err)
 };
 
@@ -230,7 +232,7 @@ void lora_phy_cuda_destroy(lora_phy_cuda_ctx* ctx)
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
     if (ctx->ev_flagged) cudaEventDestroy(ctx->ev_flagged);
     if (ctx->h_flagged) cudaFreeHost(ctx->h_flagged);
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < lora_phy_cuda_ctx::N_SIDE; ++i) {
         if (ctx->side_done[i]) cudaEventDestroy(ctx->side_done[i]);
         if (ctx->side[i]) cudaStreamDestroy(ctx->side[i]);
     }
@@ -926,9 +928,12 @@ static int detect_streams_common(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, ui
         }
         CK(cudaStreamSynchronize(ctx->stream));                    // the host vectors go out of scope below
     }
-    if (!one_group && !ctx->side_start) {
-        CK(cudaEventCreateWithFlags(&ctx->side_start, cudaEventDisableTiming));
-        for (int i = 0; i < 8; ++i) {
+    constexpr int N_SIDE = lora_phy_cuda_ctx::N_SIDE;
+    const int n_side = one_group ? 0 : (int)std::min<size_t>(groups.size(), (size_t)N_SIDE);
+    if (!one_group) {
+        if (!ctx->side_start) CK(cudaEventCreateWithFlags(&ctx->side_start, cudaEventDisableTiming));
+        for (int i = 0; i < n_side; ++i) {
+            if (ctx->side[i]) continue;
             CK(cudaStreamCreateWithFlags(&ctx->side[i], cudaStreamNonBlocking));
             CK(cudaEventCreateWithFlags(&ctx->side_done[i], cudaEventDisableTiming));
         }
@@ -940,18 +945,31 @@ static int detect_streams_common(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, ui
     }
     if (!one_group) {
         CK(cudaEventRecord(ctx->side_start, ctx->stream));
-        for (int i = 0; i < 8; ++i) CK(cudaStreamWaitEvent(ctx->side[i], ctx->side_start, 0));
+        for (int i = 0; i < n_side; ++i) CK(cudaStreamWaitEvent(ctx->side[i], ctx->side_start, 0));
     }
-    size_t off = 0, gi = 0;
-    for (auto& kv : groups) {
-        const uint32_t sf = (uint32_t)std::get<0>(kv.first), k = (uint32_t)std::get<1>(kv.first), osr = (uint32_t)std::get<2>(kv.first);
+    // A group's time is the walk of its longest row -- windows = samples / (N * osr) -- not its size: launch the longest
+    // walks first, every group on a stream of its own while they last.
+    struct Launch { const std::tuple<int, int, int>* key; const std::vector<uint32_t>* rows; size_t off; };
+    std::vector<Launch> order;
+    {
+        size_t off = 0;
+        for (auto& kv : groups) { order.push_back({ &kv.first, &kv.second, off }); off += kv.second.size(); }
+        std::stable_sort(order.begin(), order.end(), [](const Launch& x, const Launch& y) {
+            return ((size_t)1 << std::get<0>(*x.key)) * (size_t)std::get<2>(*x.key) < ((size_t)1 << std::get<0>(*y.key)) * (size_t)std::get<2>(*y.key);
+        });
+    }
+    size_t gi = 0;
+    for (const Launch& L : order) {
+        const auto& key = *L.key;
+        const size_t off = L.off, rows = L.rows->size();
+        const uint32_t sf = (uint32_t)std::get<0>(key), k = (uint32_t)std::get<1>(key), osr = (uint32_t)std::get<2>(key);
         cf* tab = nullptr;
         int rc = sync_tables(ctx, sf, k, &tab);
         if (rc) return rc;
         const size_t N = (size_t)1 << sf;
         lk::StreamSyncArgs a;
         a.iq = static_cast<const cf*>(d_iq); a.stream_stride = stream_stride; a.counts = d_counts;
-        a.n_samples = (uint32_t)n_samples; a.n_streams = (uint32_t)kv.second.size();
+        a.n_samples = (uint32_t)n_samples; a.n_streams = (uint32_t)rows;
         a.up = tab; a.down = tab + N; a.fine = tab + 2 * N;
         a.tw = ctx->tab[sf].tw; a.ct = ctx->tab[sf].ct; a.power_scale = lk::power_scale_of((int)sf);
         a.sync = sync_word & 0xff; a.thresh = thresh_db; a.mtu = mtu; a.max_frames = (uint32_t)max_frames;
@@ -962,13 +980,12 @@ static int detect_streams_common(lora_phy_cuda_ctx* ctx, const uint8_t* h_sf, ui
         { const char* e = getenv("LORA_PHY_STREAM_SERIAL"); a.force_serial = e && *e == '1'; }
         a.frame_start = d_frame_start; a.frame_err = d_frame_err; a.frame_nsym = d_frame_nsym; a.symbols = d_symbols;
         a.n_frames = d_n_frames; a.end_pos = d_end_pos; a.ids = one_group ? nullptr : d_ids + off;
-        CK(lk::launch_stream_sync((int)sf, a, one_group ? ctx->stream : ctx->side[gi % 8]));
+        CK(lk::launch_stream_sync((int)sf, a, one_group ? ctx->stream : ctx->side[gi % (size_t)n_side]));
         ++ctx->launches;
-        off += kv.second.size();
         ++gi;
     }
     if (!one_group) {
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < n_side; ++i) {
             CK(cudaEventRecord(ctx->side_done[i], ctx->side[i]));
             CK(cudaStreamWaitEvent(ctx->stream, ctx->side_done[i], 0));
         }

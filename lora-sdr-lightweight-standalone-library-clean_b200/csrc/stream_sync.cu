@@ -120,19 +120,21 @@ __device__ __forceinline__ double group_dsum(double x, double* redd)
 struct StreamView {
     const cf* iq; uint32_t n; float rate; int offset; bool comp;
 };
-__device__ __forceinline__ cf stream_sample(const StreamView& v, uint32_t m)
+// The compensated sample is a call, not inline code: 64 inlined copies of the double-precision sincosf (16 samples x
+// two windows x two load loops) spread the walk's hot path over 150 KB of instructions, and a lone warp per scheduler
+// -- all a small group of streams gives the GPU -- then waits on instruction fetches (measured on the cfg-4 groups:
+// 3x per window against the plain kernel, without any compensation requested).
+__device__ __noinline__ cf stream_sample_comp(const cf* __restrict__ iq, uint32_t n, float rate, int offset, uint32_t m)
 {
-    if (!v.comp) return ldg_cf(v.iq + m);
-    const long long k = (long long)m - v.offset;
+    const long long k = (long long)m - offset;
     // |offset| >= n: the reference leaves the buffer unshifted (phy.cpp:166,171)
-    const long long idx = ((v.offset > 0 && (uint32_t)v.offset < v.n) || (v.offset < 0 && (uint32_t)(-v.offset) < v.n)) ? k : (long long)m;
-    if (idx < 0 || idx >= (long long)v.n) return fx::mk(0.0f, 0.0f);
-    const cf x = ldg_cf(v.iq + idx);
+    const long long idx = ((offset > 0 && (uint32_t)offset < n) || (offset < 0 && (uint32_t)(-offset) < n)) ? k : (long long)m;
+    if (idx < 0 || idx >= (long long)n) return fx::mk(0.0f, 0.0f);
+    const cf x = ldg_cf(iq + idx);
     float sn, cs;
-    gm::sincosf_g(fx::fmul(v.rate, (float)(uint32_t)idx), &sn, &cs);
+    gm::sincosf_g(fx::fmul(rate, (float)(uint32_t)idx), &sn, &cs);
     return fx::cmul(x, fx::mk(cs, sn));
 }
-
 template <int SF, bool EX>
 __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const StreamView& view, uint32_t wpos, bool live,
                                                  const cf* __restrict__ chirp, int idx0, int* ft_out, float fine_err,
@@ -149,31 +151,91 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
     // With |d| <= wrap / 2 the one wrap of ft_step is a reduction mod wrap (a power of two), and the next term of the
     // progression is c_i - k mod wrap: the check per sample is ((int)(float(c_i) - d) - c_i + k) mod wrap == 0.
     // A larger |d| (never seen: it is 128 x a fraction of a bin plus at most N/4 bins) takes the literal loop.
-    bool mine_ok = !a.force_serial && fabsf(d) <= (float)(wrap / 2);
-    const bool check = !constant && live && !a.force_serial;
+    //
+    // Where the check fails the recurrence has left the progression -- in practice once per wrap of the index (the
+    // truncation rounds the other way below zero) or at a change of float binade.  Everything up to the first failing
+    // sample i* is still the literal sequence, so the walk restarts there: c_{i*+1} = ft_step(c_{i*}) computed literally, a
+    // new step k from it, the remaining samples checked against the new progression -- up to SEGMENTS pieces, then
+    // the literal loop.  (A carrier offset of a quarter bin wraps the index every eighth window; at SF12 the serial
+    // loop costs ten windows' time.)
+    constexpr int SEGMENTS = 4;
+    constexpr unsigned MASK = (unsigned)(wrap - 1);
+    bool serial = a.force_serial || !(fabsf(d) <= (float)(wrap / 2));      // uniform over the group
+    const bool check = !constant && live && !serial;
     const unsigned c0 = (unsigned)idx0 - (unsigned)tid * (unsigned)k, cstep = (unsigned)T * (unsigned)k;   // c_i, i = tid + T c
     int bad = 0;
     if (check) {
 #pragma unroll
         for (int c = 0; c < P::R; ++c) {
-            const int ci = (int)((c0 - (unsigned)c * cstep) & (unsigned)(wrap - 1));
+            const int ci = (int)((c0 - (unsigned)c * cstep) & MASK);
             bad |= ((int)fx::fsub((float)ci, d) - ci + k) & (wrap - 1);
         }
     }
-    mine_ok = mine_ok && bad == 0;
-    if (tid == 0) *ok_flag = 1;
-    group_sync<T>();
-    if (!mine_ok) *ok_flag = 0;
-    group_sync<T>();
-    const bool progression = *ok_flag != 0;
-    int ft_end = (int)(((unsigned)idx0 - (unsigned)N * (unsigned)k) & (unsigned)(wrap - 1));   // d == 0: k == 0
-    // a warp may hold several groups: they enter the fallback together (a multi-warp group is alone in its domain)
-    const bool any_serial = T > 32 ? !progression : (__any_sync(0xffffffffu, !progression) != 0);
+    int* const flag = const_cast<int*>(ok_flag);            // the group's cell: first failing sample, N when none
+    // first failing sample among this thread's, at or after j0, against the progression (e0 at j0, step kk)
+    auto first_fail = [&](int j0, unsigned e0, int kk) {
+        int mb = N;
+#pragma unroll 1
+        for (int c = P::R - 1; c >= 0; --c) {
+            const int i = tid + T * c;
+            if (i < j0) break;
+            const int ci = (int)((e0 - (unsigned)(i - j0) * (unsigned)kk) & MASK);
+            if (((int)fx::fsub((float)ci, d) - ci + kk) & (wrap - 1)) mb = i;
+        }
+        return mb;
+    };
+    auto group_min = [&](int mine) {
+        if (tid == 0) *flag = N;
+        group_sync<T>();
+        if (mine < N) atomicMin(flag, mine);
+        group_sync<T>();
+        return *ok_flag;
+    };
+    auto vote = [&](bool p) { return T > 32 ? p : (__any_sync(0xffffffffu, p) != 0); };   // T > 32: p is uniform over the group
+    int first_bad = group_min(bad ? first_fail(0, (unsigned)idx0, k) : N);
     // the literal indices live in the exchange buffer the transform writes SECOND (after its first barrier, which every
     // thread reaches with its samples loaded), so they need no memory of their own
     int* ftidx = reinterpret_cast<int*>(flip ? buf0 : buf1);
-    if (any_serial) {                                        // literal recurrence on thread 0
-        if (!progression && tid == 0) {
+    int ft_end = (int)(((unsigned)idx0 - (unsigned)N * (unsigned)k) & MASK);   // d == 0: k == 0
+    bool pieces = false;                                                     // indices come from the table
+    if (vote(check && first_bad < N)) {                                      // cold: a warp's groups go through it together
+        int j0 = 0, kk = k;
+        unsigned e0 = (unsigned)idx0;
+#pragma unroll 1
+        for (int seg = 1;; ++seg) {
+            const bool more = check && !serial && first_bad < N;
+            if (!vote(more)) break;
+            group_sync<T>();                                 // everyone has read the cell before it is reset
+
+            if (more && seg >= SEGMENTS) serial = true;
+            const bool go = more && !serial;
+            if (go) {
+#pragma unroll 1
+                for (int c = 0; c < P::R; ++c) {                             // the finished stretch j0 .. first_bad
+                    const int i = tid + T * c;
+                    if (i >= j0 && i <= first_bad) ftidx[i] = (int)((e0 - (unsigned)(i - j0) * (unsigned)kk) & MASK);
+                }
+                const int cb = (int)((e0 - (unsigned)(first_bad - j0) * (unsigned)kk) & MASK);
+                e0 = (unsigned)ft_step(cb, d, wrap);
+                j0 = first_bad + 1;
+                kk = (int)e0 - (int)fx::fsub((float)(int)e0, d);
+                pieces = true;
+            }
+            const int fb = group_min(go ? first_fail(j0, e0, kk) : N);
+            first_bad = go ? fb : N;
+        }
+        if (pieces && !serial) {                                             // the last piece, and where the index ends
+#pragma unroll 1
+            for (int c = 0; c < P::R; ++c) {
+                const int i = tid + T * c;
+                if (i >= j0) ftidx[i] = (int)((e0 - (unsigned)(i - j0) * (unsigned)kk) & MASK);
+            }
+            ft_end = (int)((e0 - (unsigned)(N - j0) * (unsigned)kk) & MASK);
+        }
+    }
+    // a warp may hold several groups: they enter the fallback together (a multi-warp group is alone in its domain)
+    if (vote(serial)) {                                      // literal recurrence on thread 0
+        if (serial && tid == 0) {
             int idx = idx0;
             for (int i = 0; i < N; ++i) {
                 ftidx[i] = idx;
@@ -183,25 +245,62 @@ __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const 
         }
         group_sync<T>();
     }
+    const bool progression = !serial && !pieces;
     if (tid == 0 && live) *ft_out = ft_end;
     cf v[P::R];
     // two copies of the load loop, so that the usual one has no shared-memory read between its global loads (a select on
     // `progression` inside ONE loop keeps the compiler from batching the 3 x R loads: measured 2x slower at SF7-9)
-    auto load = [&](auto from_table) {
+    // (the compensated variant likewise: a per-sample `if (comp)` around a call splits the loop into 16 basic blocks)
+    auto load = [&](auto from_table, auto comp) {
+        constexpr bool TABLE = decltype(from_table)::value, COMP = decltype(comp)::value;
+        if constexpr (EX && !COMP && T <= 32) {              // (multi-warp windows have warps to overlap with; there the plain loop is faster)
+            // Strided window (osr > 1 / bandwidth scale): the sample addresses are runtime products, not immediates, and the
+            // compiler then serialises the loop -- three loads, their arithmetic, the next three loads: 16 memory round
+            // trips per window on a walk that has nothing else to hide them behind.  Two explicit batches of eight.
+            const cf* src = view.iq + wpos + (size_t)tid * a.osr;
+            const size_t step = (size_t)T * a.osr;
+#pragma unroll
+            for (int h = 0; h < P::R; h += 8) {
+                cf raw[8], chv[8], fnv[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int c = h + q, i = tid + T * c;
+                    raw[q] = chv[q] = fnv[q] = fx::mk(0.0f, 0.0f);
+                    if (live) {
+                        const int ci = TABLE ? ftidx[i] : (int)((c0 - (unsigned)c * cstep) & MASK);
+                        raw[q] = ldg_cf(src + (size_t)c * step);
+                        chv[q] = ldg_cf(chirp + i);
+                        fnv[q] = ldg_cf(a.fine + ci);
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    v[h + q] = live ? fx::cmul(fx::cmul(raw[q], chv[q]), fnv[q]) : fx::mk(0.0f, 0.0f);
+            }
+            return;
+        }
 #pragma unroll
         for (int c = 0; c < P::R; ++c) {
             const int i = tid + T * c;
             cf x = fx::mk(0.0f, 0.0f);
             if (live) {
-                // EX: oversampled and / or compensated stream (osr > 1: phase 0 of every chip); else the plain one-sample-per-chip load
-                x = fx::cmul(EX ? stream_sample(view, wpos + (uint32_t)i * a.osr) : ldg_cf(view.iq + wpos + i), ldg_cf(chirp + i));
-                const int ci = decltype(from_table)::value ? ftidx[i] : (int)((c0 - (unsigned)c * cstep) & (unsigned)(wrap - 1));
+                // (pointer arithmetic, not a 32-bit sample index: `iq + wpos + i` folds i into the load's immediate offset;
+                //  `iq + (wpos + i)` in uint32 does not and measured 2x slower on the sub-warp walks)
+                const cf raw = COMP ? stream_sample_comp(view.iq, view.n, view.rate, view.offset, wpos + (uint32_t)i * a.osr)
+                             : EX   ? ldg_cf(view.iq + wpos + (size_t)i * a.osr)
+                                    : ldg_cf(view.iq + wpos + i);
+                x = fx::cmul(raw, ldg_cf(chirp + i));
+                const int ci = TABLE ? ftidx[i] : (int)((c0 - (unsigned)c * cstep) & MASK);
                 x = fx::cmul(x, ldg_cf(a.fine + ci));
             }
             v[c] = x;
         }
     };
-    if (progression) load(std::false_type{}); else load(std::true_type{});
+    if (EX && view.comp) {
+        if (progression) load(std::false_type{}, std::true_type{}); else load(std::true_type{}, std::true_type{});
+    } else {
+        if (progression) load(std::false_type{}, std::false_type{}); else load(std::true_type{}, std::false_type{});
+    }
     fft_group<SF, true>(v, tid, a.tw, a.ct, buf0, buf1, flip);
     const Peak pk = group_peak<SF>(local_peak<SF>(v, tid), red);
     double part = 0.0;
@@ -317,27 +416,33 @@ __global__ void __launch_bounds__(sync_cta<SF>(), sync_threads_per_sm<SF>() / sy
             }
         }
         const cf* chirp = ctl.down ? a.down : a.up;
-        int ft = ctl.ft;
-        DetectOut d = sync_window<SF, EX>(a, view, wpos, live, chirp, ctl.ft, &ft, ferr, tid, buf0, buf1, flip, red, redd,
-                                      &ctl.ok);
-        bool squelched = false, syncd = false, match0 = false;
-        if (tid == 0 && live) {
-            fine_idx = ft;
-            squelched = d.snr < a.thresh;
-            if (state == ST_FRAMESYNC) {                                       // :179-185
-                syncd = !squelched && (prev_value + 4) / 8 == 0;
-                match0 = (unsigned)(d.value + 4) / 8 == a.sync0;
-                if (syncd && match0) { ctl.need2 = 1; ctl.ft2 = ft; }
-            }
-        }
-        group_sync<T>();
-        const bool need2 = ctl.need2 != 0;
+        // ONE copy of the window code for the window itself (w = 0) and the look-ahead for sync word1 (w = 1, :188-205;
+        // it works on a copy of the fine-tune index: _fineTuneIndex itself is not advanced)
+        DetectOut d; d.value = 0; d.snr = 0.0f; d.findex = 0.0f;
+        bool squelched = false, syncd = false, match0 = false, need2 = false;
         int value1 = 0;
-        if (dom_any<T>(need2)) {                                         // look ahead one window for sync word1 (:188-205)
-            int ft2 = 0;                                                       // (a copy: _fineTuneIndex itself is not advanced)
-            DetectOut d1 = sync_window<SF, EX>(a, view, wpos + (uint32_t)N * osr, live && need2, chirp, ctl.ft2, &ft2, ferr, tid, buf0, buf1, flip,
-                                           red, redd, &ctl.ok);
-            if (tid == 0 && need2) { value1 = d1.value; d.findex = d1.findex; }
+#pragma unroll 1
+        for (int w = 0; w < 2; ++w) {
+            int ftv = 0;
+            const DetectOut o = sync_window<SF, EX>(a, view, wpos + (w ? (uint32_t)N * osr : 0u), live && (w == 0 || need2), chirp,
+                                                    w ? ctl.ft2 : ctl.ft, &ftv, ferr, tid, buf0, buf1, flip, red, redd, &ctl.ok);
+            if (w) {
+                if (tid == 0 && need2) { value1 = o.value; d.findex = o.findex; }
+                break;
+            }
+            d = o;
+            if (tid == 0 && live) {
+                fine_idx = ftv;
+                squelched = d.snr < a.thresh;
+                if (state == ST_FRAMESYNC) {                                   // :179-185
+                    syncd = !squelched && (prev_value + 4) / 8 == 0;
+                    match0 = (unsigned)(d.value + 4) / 8 == a.sync0;
+                    if (syncd && match0) { ctl.need2 = 1; ctl.ft2 = ftv; }
+                }
+            }
+            group_sync<T>();
+            need2 = ctl.need2 != 0;
+            if (!dom_any<T>(need2)) break;
         }
         if (tid == 0 && live) {
             uint32_t total = 0;
