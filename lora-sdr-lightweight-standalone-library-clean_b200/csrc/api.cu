@@ -345,6 +345,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     a.time_offset = d_to;
     a.status = d_status;
     a.force_exact = 0;
+    a.no_prune = 0;
     a.unit_scale = 0; a.skip_sync = 0; a.flagged = nullptr; a.only_flagged = nullptr; a.pmax = nullptr; a.n_flagged = nullptr;
     a.cert_stats = ctx->cert_stats;
     unsigned launches = 0;
@@ -352,6 +353,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     // teams of warps, then the streaming pruned transform with one warp per packet; it flags every packet it cannot
     // settle; (2) the certified kernel over the flagged packets.
     static const bool lean_off = getenv("LORA_PHY_NO_LEAN") != nullptr;
+    bool given_up = false;                                  // the lean route is skipped because it handed most packets over
     if (!lean_off && !(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&
         lk::lean_supported((int)cfg->sf, a) && lk::cert_supported((int)cfg->sf, a) && [&]() {
             // verdict of the previous call, if it has arrived: mostly handed over -> the certified kernel alone for a while
@@ -359,7 +361,7 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
                 ctx->flagged_pending = false;
                 if (ctx->flagged_of >= 64 && (size_t)*ctx->h_flagged * 3 > ctx->flagged_of) ctx->lean_skip = 7;
             }
-            if (ctx->lean_skip > 0) { --ctx->lean_skip; return false; }
+            if (ctx->lean_skip > 0) { --ctx->lean_skip; given_up = true; return false; }
             return true;
         }()) {
         CK(ctx->flag.reserve(((n_packets + 15) & ~(size_t)15) + 16));
@@ -394,6 +396,15 @@ static int demod_common(lora_phy_cuda_ctx* ctx, const lora_phy_cuda_cfg* cfg, in
     // windows that cannot be proven (demod_cert.cu)
     if (!(cfg->flags & (LORA_PHY_CUDA_F_ONLY_PREPASS | LORA_PHY_CUDA_F_ONLY_SYMBOLS | LORA_PHY_CUDA_F_TWO_KERNEL | LORA_PHY_CUDA_F_EXACT)) &&
         lk::cert_supported((int)cfg->sf, a)) {
+        // A batch the lean route gave up on is noisy.  For single-warp windows (SF7-9) the copy of the kernel without the
+        // pruned transform then runs: their full transform with tier 1 is as fast as the pruned one on clean windows
+        // (4.0 TB/s either way at SF7) and 18-27 % faster on noise once the pruned code is out of the walk loop
+        // (8 GB batches, SF7: 2 240 -> 2 643 GB/s at -6 dB, 2 235 -> 2 837 at +3 dB).  SF10-12 keep it: a packet fails the
+        // lean pass on ONE bad window of 66, while 77 % of SF12 windows at +3 dB still settle on one bin class (measured
+        // 2 998 GB/s with, 2 465 without).  Same results either way -- a pruned window is only ever accepted by the tier-1
+        // test the full transform applies first.
+        static const bool keep_prune = getenv("LORA_PHY_KEEP_PRUNE") != nullptr;       // A/B
+        a.no_prune = given_up && !keep_prune && cfg->sf <= 9;
         cudaError_t e = lk::launch_demod_cert((int)cfg->sf, a, ctx->sm_count, ctx->stream);
         ++ctx->launches;
         if (e != cudaSuccess) return fail(ctx, -EIO, "certified demodulator launch", e);

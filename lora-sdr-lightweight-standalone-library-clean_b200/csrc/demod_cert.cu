@@ -209,7 +209,10 @@ __device__ __forceinline__ float cert_scan_max(const cf* __restrict__ pkt, uint3
     return group_max<DT>(m, redf);
 }
 
-template <int SF, bool EXTRA, int CTA>
+// PR_ON = false: the copy without the pruned transform in its walk, for batches the lean route has given up on (noise:
+// no window passes tier 1 on one bin class, so the attempt is never made -- but its code sits in the walk loop, and the
+// walk then waits on instruction fetches: `no_instruction` 2.0 stalled warps per issue against 0.6 without it).
+template <int SF, bool EXTRA, int CTA, bool PR_ON = true>
 __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const DemodArgs a)
 {
     using C = CertCfg<SF, CTA>;
@@ -288,7 +291,7 @@ __global__ void __launch_bounds__(CTA, cert_ctas(SF)) demod_cert_kernel(const De
     }
     // pruned transform (fft_prune.cuh): tables and this thread's cross-warp twiddle W_T^{lane * warp}
     using PR = fp::Prune<SF>;
-    constexpr bool PRUNE = CERT_PRUNE != 0;
+    constexpr bool PRUNE = CERT_PRUNE != 0 && PR_ON;
     cf* pr_tws = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_tws);
     cf* pr_wr = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_wr);
     cf* pr_twn = reinterpret_cast<cf*>(smem_raw + C::pr_off + C::pr_twn);
@@ -1182,12 +1185,14 @@ static cudaError_t launch_cert_sf(const DemodArgs& a, int sm_count, cudaStream_t
     if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
         cudaFuncSetAttribute(demod_cert_kernel<SF, false, CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
         cudaFuncSetAttribute(demod_cert_kernel<SF, true, CTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
+        cudaFuncSetAttribute(demod_cert_kernel<SF, false, CTA, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
         attr_done[dev & 63].store(true, std::memory_order_release);
     }
     const unsigned max_ctas = (unsigned)sm_count * cert_ctas(SF);         // persistent grid: every CTA resident
     const unsigned need = (a.n_packets + C::DOMS - 1) / C::DOMS;
     const unsigned grid = need < max_ctas ? need : max_ctas;
     if (extra) demod_cert_kernel<SF, true, CTA><<<grid, CTA, C::bytes, stream>>>(a);
+    else if (a.no_prune) demod_cert_kernel<SF, false, CTA, false><<<grid, CTA, C::bytes, stream>>>(a);
     else demod_cert_kernel<SF, false, CTA><<<grid, CTA, C::bytes, stream>>>(a);
     return cudaGetLastError();
 }

@@ -53,6 +53,7 @@ struct DemodArgs {
     float* cfo;
     float* time_offset;
     int32_t* status;
+    int no_prune;                 // certified kernel: the copy without the pruned transform (noisy batches, api.cu)
     int unit_scale;               // prepass: assume no 1/max normalisation is needed (no max-abs scan); the lean pass checks
     int skip_sync;                // prepass: leave the two sync symbols to a later pass
     uint8_t* flagged;             // lean pass (demod_lean.cu): packets it hands to the certified kernel

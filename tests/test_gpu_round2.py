@@ -539,6 +539,47 @@ def test_lean_route_shifted_windows(phy, lp, oracle, sf):
     assert c1[5] - c0[5] <= 6, (got_toff, c0, c1)                   # (most of them) kept by the streaming pass
 
 
+@pytest.mark.parametrize("sf", [7, 8, 9, 11])
+def test_noisy_batches_switch_to_the_certified_kernel_without_pruning(phy, lp, oracle, sf):
+    """The adaptive route: a batch in which the streaming pass hands over more than a third of its packets makes the next
+    calls skip that pass -- the certified kernel alone, for SF7-9 its copy without the pruned transform.  96 noisy packets
+    (with a few clean and loud ones among them), five calls in a row: every call equals the oracle, the later calls hand
+    nothing over (the streaming pass did not run) and, at SF7-9, settle nothing by the pruned transform although a third
+    of the batch is clean."""
+    rng = np.random.default_rng(4100 + sf)
+    N = 1 << sf
+    S = 6 if sf <= 9 else 4
+    down = oracle.gen_chirp(N, 1, N, 0.0, True, 1.0, 0.0, 1.0)[0]
+    rows = []
+    for p in range(96):
+        syms = rng.integers(0, N, S - 2).astype(np.uint16)
+        amp = 1.0 if p % 3 else float(rng.uniform(0.4, 3.0))
+        d = (oracle.lora_modulate(syms, sf, 1, 125000, amp, 0x12).reshape(-1, N) * down[None, :]).astype(np.complex64).ravel()
+        if p % 3 != 1:                                            # two thirds noisy: -6 .. +2 dB per sample
+            sg = np.float32(amp * 10 ** (-rng.uniform(-6.0, 2.0) / 20) / np.sqrt(2))
+            d = (d + sg * (rng.standard_normal(d.size) + 1j * rng.standard_normal(d.size))).astype(np.complex64)
+        rows.append(d)
+    iq = np.stack(rows)
+    seen_alone = 0
+    for call in range(5):
+        c0 = phy.cert_stats()
+        check_legacy(phy, lp, oracle, iq, sf, 1, 0)
+        c1 = phy.cert_stats()
+        windows, pruned, handed = c1[0] - c0[0], c1[4] - c0[4], c1[5] - c0[5]
+        if call >= 2 and handed == 0:                             # the certified kernel alone (the verdict has arrived)
+            seen_alone += 1
+            assert windows >= 96 * S, (call, windows)
+            if sf <= 9:
+                assert pruned == 0, (call, pruned)
+            else:
+                assert pruned > 0, (call, pruned)
+    assert seen_alone >= 2, seen_alone
+    # a clean batch right after is still right (and, once the skip has run out, goes back to the streaming pass)
+    clean = np.stack([r for p, r in enumerate(rows) if p % 3 == 1])
+    for _ in range(8):
+        check_legacy(phy, lp, oracle, clean, sf, 1, 0)
+
+
 def test_every_kernel_family_small_cases():
     """tools/sanitize_driver.py (written for compute-sanitizer, which is closed on this pool) as a plain run: every kernel
     family on ragged / oversized / odd-aligned / loud / noise-only inputs must complete without a CUDA error."""
