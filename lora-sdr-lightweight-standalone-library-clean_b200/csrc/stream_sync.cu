@@ -12,9 +12,10 @@
 //   DOWNCHIRP0/1 signed bin error of the two down-chirps, averaged (the CFO estimate reported per frame)
 //   QUARTERCHIRP consume N/4 + err/2 (the STO correction), fold err/2 into the fine frequency error
 //   DATASYMBOLS emit symbols until mtu or squelch (snr < threshold), report the frame
-// Two pieces are serial on thread 0 because their order is observable in the results: the fine-tune index
-// recurrence (an int decremented by a float and truncated, per sample, :160-163) and the detector's
-// double-precision running total (LoRaDetector.hpp:45-52).
+// Two pieces of the reference are serial by construction, and their order is observable in the results: the fine-tune
+// index recurrence (an int decremented by a float and truncated, per sample, :160-163) and the detector's
+// double-precision running total (LoRaDetector.hpp:45-52).  Both run in parallel under a checked proof (sync_window)
+// and fall back to the literal loop on thread 0 when it fails; LORA_PHY_STREAM_SERIAL=1 forces the literal loops.
 //
 // Streams do not wait for each other: every barrier and vote of the walk spans one DOMAIN only -- the warp for
 // windows of up to 32 threads (SF7-9; the 4 / 2 / 1 streams of a warp step together), the stream's own thread
@@ -102,17 +103,6 @@ __device__ __forceinline__ double group_dsum(double x, double* redd)
     return x;
 }
 
-// one window at `src`: dechirp + fine tune (:157-166), FFT, detect (LoRaDetector.hpp:39-74).
-// thread 0 of the group returns the detector outputs and the fine-tune index advanced past the window.
-//
-// The two pieces of the reference that are serial by construction are run in parallel with a proof
-// obligation and fall back to the literal serial loop when the proof fails:
-//  * fine-tune index: inside one float binade the recurrence is a constant integer step k, so the
-//    sequence is idx0 - i*k (mod N*128).  Every thread checks ft_step(c_i) == c_{i+1} for its own
-//    samples; if all agree the arithmetic progression IS the recurrence (induction from idx0).
-//  * detector total: the ascending double sum differs from any other summation order by at most
-//    2(N-1)u * total.  If float(total - max) is the same at both ends of that interval (the map is
-//    monotone) the order cannot matter and the tree sum is used.
 // Sample m of the stream as the detector sees it.  Without compensation: iq[m].  With per-stream (cfo, time_offset)
 // (compensate_offsets, phy.cpp:150-180, fused into the load -- no temporary copy of the stream): the reference first
 // rotates sample n by exp(j*rate*n), rate = -2*pi*cfo/(N*osr), then shifts the buffer by round(time_offset) with zero fill,
@@ -135,6 +125,18 @@ __device__ __noinline__ cf stream_sample_comp(const cf* __restrict__ iq, uint32_
     gm::sincosf_g(fx::fmul(rate, (float)(uint32_t)idx), &sn, &cs);
     return fx::cmul(x, fx::mk(cs, sn));
 }
+// one window at wpos: dechirp + fine tune (:157-166), FFT, detect (LoRaDetector.hpp:39-74).
+// thread 0 of the group returns the detector outputs and the fine-tune index advanced past the window.
+//
+// The two pieces of the reference that are serial by construction are run in parallel with a proof
+// obligation and fall back to the literal serial loop when the proof fails:
+//  * fine-tune index: inside one float binade the recurrence is a constant integer step k, so the
+//    sequence is idx0 - i*k (mod N*128).  Every thread checks ft_step(c_i) == c_{i+1} for its own
+//    samples; if all agree the arithmetic progression IS the recurrence (induction from idx0).  Where the
+//    check fails the walk restarts from the literal next value (pieces, below).
+//  * detector total: the ascending double sum differs from any other summation order by at most
+//    2(N-1)u * total.  If float(total - max) is the same at both ends of that interval (the map is
+//    monotone) the order cannot matter and the tree sum is used.
 template <int SF, bool EX>
 __device__ __forceinline__ DetectOut sync_window(const StreamSyncArgs& a, const StreamView& view, uint32_t wpos, bool live,
                                                  const cf* __restrict__ chirp, int idx0, int* ft_out, float fine_err,
