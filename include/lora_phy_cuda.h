@@ -266,7 +266,9 @@ int lora_phy_cuda_detect_streams_mixed(lora_phy_cuda_ctx* ctx, const uint8_t* h_
  * so dechirp tables, sync-word targets and the bin->time conversions of the state machine scale with it and the
  * symbols come out as (bw_scale*s) mod N); h_osr[s] in 1..8 samples per chip (windows of N*osr samples, phase 0 of
  * every chip as LoRaDemod.cpp:94-99 takes it, slides in chips).  NULL h_bw_scale / h_osr = 1.  One launch per distinct
- * (sf, bw_scale, osr).  d_cfo / d_time_offset: NULL, or [n_streams] offsets applied to each stream exactly as
+ * (sf, bw_scale, osr); the launches run side by side on streams the context owns (they start after the work already
+ * queued on the context's stream and the context's stream waits for all of them: to the caller the call is ordered
+ * like any other).  d_cfo / d_time_offset: NULL, or [n_streams] offsets applied to each stream exactly as
  * compensate_offsets (phy.cpp:150-180: rotate by exp(-j*2*pi*cfo*n/(N*osr)), shift by round(time_offset) with zero
  * fill) INSIDE the window load -- no compensated copy of the stream is made.  frame_start / end_pos are in samples.
  * With bw_scale = osr = 1 and no offsets this is lora_phy_cuda_detect_streams_mixed.                                  */
