@@ -83,7 +83,14 @@ def bind_near_gpu(index):
     try:
         import pynvml
         pynvml.nvmlInit()
-        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        h = None
+        try:                                   # the CUDA device's own UUID: right whatever CUDA_VISIBLE_DEVICES says
+            import torch
+            h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(index).uuid))
+        except Exception:
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",")
+            tok = vis[index].strip() if index < len(vis) else ""
+            h = pynvml.nvmlDeviceGetHandleByIndex(int(tok) if tok.isdigit() else index)
         words = (os.cpu_count() + 63) // 64
         mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
         cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
