@@ -110,3 +110,36 @@ def test_a_quarter_bin_offset_wraps_every_eighth_window_and_needs_two_pieces():
         idx = end
     assert "serial" not in tags
     assert 3 <= sum(t.startswith("pieces") for t in tags) <= 8, tags
+
+
+def test_lean_pass_window_runs_equal_the_reference_window_bases():
+    """csrc/demod_lean.cu streams a packet with a time offset as ONE contiguous run of total-1 shifted windows plus one
+    unshifted window; LoRaDemod.cpp:143-150 (stream_common.cuh: shifted_base) states the bases window by window.  Pure
+    integer replay of both, every |t_off| < N and the packet lengths the route accepts (count == total * N)."""
+    def shifted_base(s, n, t_off, count):                   # the reference's rule
+        base = s * n
+        if t_off > 0:
+            if base + t_off + n <= count:
+                base += t_off
+        elif t_off < 0:
+            if -t_off <= base:
+                base += t_off
+        return base
+
+    for n in (128, 512):
+        for total in (2, 3, 7, 66):
+            count = total * n
+            for t_off in list(range(-n + 1, n, 7)) + [-1, 1, n // 2, -n // 2]:
+                want = {s: shifted_base(s, n, t_off, count) for s in range(total)}
+                got = {}
+                if t_off == 0:
+                    got = {s: s * n for s in range(total)}
+                else:
+                    run0 = t_off if t_off > 0 else n + t_off          # first sample of the run
+                    sym0 = 1 if t_off < 0 else 0                      # symbol of its first window
+                    for j in range(total - 1):
+                        got[sym0 + j] = run0 + j * n
+                    s_plain = total - 1 if t_off > 0 else 0           # the one unshifted window
+                    got[s_plain] = s_plain * n
+                assert got == want, (n, total, t_off)
+                assert all(0 <= b and b + n <= count for b in got.values())
